@@ -1,0 +1,224 @@
+// extern "C" surface of libgnnqc.so (declarations and reference citations: include/gnnqc.h).
+#include <cstring>
+#include <exception>
+#include <new>
+#include <string>
+
+#include "../../include/gnnqc.h"
+#include "device_model.cuh"
+#include "model_spec.h"
+
+using gnnqc::DeviceModel;
+
+struct gnnqc_model {
+  DeviceModel dm;
+};
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const std::string& msg) {
+  g_last_error = msg;
+  return code;
+}
+
+// Runs `fn`, translating exceptions into error codes + gnnqc_last_error().
+template <typename F>
+int guarded(F&& fn) {
+  try {
+    fn();
+    return GNNQC_OK;
+  } catch (const gnnqc::CudaError& e) {
+    return fail(GNNQC_ERR_CUDA, e.what());
+  } catch (const std::invalid_argument& e) {
+    return fail(GNNQC_ERR_ARG, e.what());
+  } catch (const std::bad_alloc&) {
+    return fail(GNNQC_ERR_STATE, "out of host memory");
+  } catch (const std::exception& e) {
+    return fail(GNNQC_ERR_CKPT, e.what());
+  }
+}
+
+void attach_device(DeviceModel& dm, int device) {
+  dm.device = device;
+  if (device < 0) return;
+  int count = 0;
+  cudaError_t err = cudaGetDeviceCount(&count);
+  if (err != cudaSuccess || count == 0)
+    throw gnnqc::CudaError(std::string("no usable CUDA device (") + cudaGetErrorString(err) + "); libgnnqc has no CPU fallback");
+  if (device >= count) throw std::invalid_argument("device index " + std::to_string(device) + " out of range");
+  GNNQC_CUDA(cudaSetDevice(device));
+  cudaDeviceProp prop;
+  GNNQC_CUDA(cudaGetDeviceProperties(&prop, device));
+  if (prop.major != 10)
+    throw gnnqc::CudaError(std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major * 10 + prop.minor) +
+                           "; libgnnqc is built for sm_100a (B200) only");
+  dm.sm_count = prop.multiProcessorCount;
+  dm.configure_kernels();
+  dm.upload();
+}
+
+int need_device(const gnnqc_model* m, const char* what) {
+  if (!m) return fail(GNNQC_ERR_ARG, std::string(what) + ": null model handle");
+  if (m->dm.device < 0) return fail(GNNQC_ERR_STATE, std::string(what) + ": handle was opened host-only (device < 0); there is no CPU path");
+  return GNNQC_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+int gnnqc_abi_version(void) { return GNNQC_ABI_VERSION; }
+
+const char* gnnqc_last_error(void) { return g_last_error.c_str(); }
+
+int gnnqc_model_load(const char* savedmodel_dir, int device, gnnqc_model** out) {
+  if (!savedmodel_dir || !out) return fail(GNNQC_ERR_ARG, "gnnqc_model_load: null argument");
+  *out = nullptr;
+  gnnqc_model* m = nullptr;
+  int rc = guarded([&] {
+    m = new gnnqc_model();
+    m->dm.host = gnnqc::load_saved_model(savedmodel_dir);
+    attach_device(m->dm, device);
+  });
+  if (rc != GNNQC_OK) {
+    delete m;
+    return rc;
+  }
+  *out = m;
+  return GNNQC_OK;
+}
+
+int gnnqc_model_create(int has_gcn, int soilnet, int filter_1_size, int n_stacks, int dense_units,
+                       const float* params_host, int64_t n_params, const int32_t* model_info, int n_model_info,
+                       const char* normalization, int device, gnnqc_model** out) {
+  if (!out) return fail(GNNQC_ERR_ARG, "gnnqc_model_create: null out");
+  *out = nullptr;
+  gnnqc_model* m = nullptr;
+  int rc = guarded([&] {
+    m = new gnnqc_model();
+    gnnqc::HostModel& h = m->dm.host;
+    h.spec.layout(has_gcn != 0, soilnet != 0, soilnet ? 3 : 2, filter_1_size, n_stacks, dense_units);
+    if (params_host && n_params != h.spec.n_params)
+      throw std::invalid_argument("gnnqc_model_create: expected " + std::to_string(h.spec.n_params) + " parameters, got " +
+                                  std::to_string(n_params));
+    h.params.assign(static_cast<size_t>(h.spec.n_params), 0.f);
+    if (params_host) std::memcpy(h.params.data(), params_host, sizeof(float) * h.spec.n_params);
+    if (model_info && n_model_info > 0) h.model_info.assign(model_info, model_info + n_model_info);
+    h.ds_type = soilnet ? "soilnet" : "cml";
+    h.normalization = normalization ? normalization : "";
+    attach_device(m->dm, device);
+  });
+  if (rc != GNNQC_OK) {
+    delete m;
+    return rc;
+  }
+  *out = m;
+  return GNNQC_OK;
+}
+
+int gnnqc_model_describe(const gnnqc_model* m, gnnqc_model_desc* out) {
+  if (!m || !out) return fail(GNNQC_ERR_ARG, "gnnqc_model_describe: null argument");
+  const gnnqc::HostModel& h = m->dm.host;
+  std::memset(out, 0, sizeof(*out));
+  out->has_gcn = h.spec.has_gcn;
+  out->soilnet = h.spec.soilnet;
+  out->n_features = h.spec.n_features;
+  out->n_lstm = h.spec.n_lstm;
+  for (int l = 0; l < h.spec.n_lstm; ++l) {
+    out->lstm_in[l] = h.spec.lstm_in[l];
+    out->lstm_hid[l] = h.spec.lstm_hid[l];
+  }
+  out->dense_units = h.spec.dense_units;
+  out->n_model_info = static_cast<int32_t>(std::min<size_t>(h.model_info.size(), 4));
+  for (int i = 0; i < out->n_model_info; ++i) out->model_info[i] = h.model_info[i];
+  if (out->n_model_info >= 2) {
+    // sequence_length = int((timestep_before + timestep_after)/freq + 1)  (create_model.py:12,
+    // :245); freq defaults to 1 for CML and 15 for SoilNet when model_info has 3 entries.
+    int freq = out->n_model_info >= 4 ? out->model_info[3] : (h.spec.soilnet ? 15 : 1);
+    if (freq < 1) freq = 1;
+    out->seq_len = (out->model_info[0] + out->model_info[1]) / freq + 1;
+  }
+  out->n_params = h.spec.n_params;
+  out->n_trainable = h.spec.n_trainable;
+  std::strncpy(out->ds_type, h.ds_type.c_str(), sizeof(out->ds_type) - 1);
+  std::strncpy(out->normalization, h.normalization.c_str(), sizeof(out->normalization) - 1);
+  return GNNQC_OK;
+}
+
+int gnnqc_model_get_params(const gnnqc_model* m, float* out_host, int64_t n) {
+  if (!m || !out_host) return fail(GNNQC_ERR_ARG, "gnnqc_model_get_params: null argument");
+  if (n != m->dm.host.spec.n_params) return fail(GNNQC_ERR_ARG, "gnnqc_model_get_params: wrong length");
+  std::memcpy(out_host, m->dm.host.params.data(), sizeof(float) * n);
+  return GNNQC_OK;
+}
+
+int gnnqc_model_set_params(gnnqc_model* m, const float* in_host, int64_t n) {
+  if (!m || !in_host) return fail(GNNQC_ERR_ARG, "gnnqc_model_set_params: null argument");
+  if (n != m->dm.host.spec.n_params) return fail(GNNQC_ERR_ARG, "gnnqc_model_set_params: wrong length");
+  return guarded([&] {
+    std::memcpy(m->dm.host.params.data(), in_host, sizeof(float) * n);
+    m->dm.upload();
+  });
+}
+
+int gnnqc_model_segment(const gnnqc_model* m, int idx, char path[128], int64_t* offset, int64_t shape[4], int32_t* rank,
+                        int32_t* trainable) {
+  if (!m) return fail(GNNQC_ERR_ARG, "gnnqc_model_segment: null model");
+  std::vector<gnnqc::ParamSegment> segs = gnnqc::param_segments(m->dm.host.spec);
+  if (idx < 0 || idx >= static_cast<int>(segs.size())) return fail(GNNQC_ERR_ARG, "gnnqc_model_segment: index past the last segment");
+  const gnnqc::ParamSegment& s = segs[idx];
+  if (path) {
+    std::memset(path, 0, 128);
+    std::strncpy(path, s.path.c_str(), 127);
+  }
+  if (offset) *offset = s.offset;
+  if (rank) *rank = static_cast<int32_t>(s.shape.size());
+  if (shape)
+    for (size_t i = 0; i < 4; ++i) shape[i] = i < s.shape.size() ? s.shape[i] : 1;
+  if (trainable) *trainable = s.trainable;
+  return GNNQC_OK;
+}
+
+int gnnqc_model_save(const gnnqc_model* m, const char* dir) {
+  if (!m || !dir) return fail(GNNQC_ERR_ARG, "gnnqc_model_save: null argument");
+  return guarded([&] { gnnqc::save_saved_model(m->dm.host, dir); });
+}
+
+void gnnqc_model_free(gnnqc_model* m) { delete m; }
+
+int gnnqc_score_seq(gnnqc_model* m, const float* x_dev, int64_t n_seq, int32_t T, float* scores_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_score_seq")) return rc;
+  if (n_seq < 0 || T <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_score_seq: bad n_seq / T");
+  if (n_seq > 0 && (!x_dev || !scores_dev)) return fail(GNNQC_ERR_ARG, "gnnqc_score_seq: null buffer");
+  return guarded([&] { m->dm.score_seq(x_dev, n_seq, T, scores_dev, static_cast<cudaStream_t>(stream)); });
+}
+
+int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom_dev, const int64_t* edges_dev,
+                    const int32_t* node_off_dev, const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
+                    float* scores_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_score_cml")) return rc;
+  if (!m->dm.host.spec.has_gcn || m->dm.host.spec.soilnet)
+    return fail(GNNQC_ERR_STATE, "gnnqc_score_cml: model is not a CML GCNClassifier");
+  if (B < 0 || T <= 0 || n_nodes_total < 0) return fail(GNNQC_ERR_ARG, "gnnqc_score_cml: bad B / T / n_nodes_total");
+  if (B > 0 && (!features_dev || !anom_dev || !edges_dev || !node_off_dev || !edge_off_dev || !scores_dev))
+    return fail(GNNQC_ERR_ARG, "gnnqc_score_cml: null buffer");
+  return guarded([&] {
+    m->dm.score_cml(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
+                    reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, scores_dev,
+                    static_cast<cudaStream_t>(stream));
+  });
+}
+
+int64_t gnnqc_score_scratch_bytes(const gnnqc_model* m, int64_t n_seq, int32_t T) {
+  if (!m || n_seq < 0 || T <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_score_scratch_bytes: bad argument");
+  int64_t bytes = 0;
+  int rc = guarded([&] {
+    gnnqc::StackPlan plan(m->dm.host.spec, T);
+    bytes = static_cast<int64_t>(plan.bytes_per_tile()) * ((n_seq + gnnqc::kTile - 1) / gnnqc::kTile);
+  });
+  return rc == GNNQC_OK ? bytes : rc;
+}
+
+}  // extern "C"

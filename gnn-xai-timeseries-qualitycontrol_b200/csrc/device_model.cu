@@ -1,0 +1,270 @@
+#include "device_model.cuh"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+
+#include "frontend.cuh"
+#include "lstm_fwd.cuh"
+
+namespace gnnqc {
+
+// ---------------------------------------------------------------------------------------------
+StackPlan::StackPlan(const ModelSpec& s, int T_) : T(T_) {
+  const int n_pairs = (s.n_lstm - 1) / 2;  // LSTM pairs, each followed by MaxPooling1D(3)
+  int t_last = T;
+  for (int p = 0; p < n_pairs; ++p) t_last /= 3;
+  if (t_last < 1) throw std::invalid_argument("sequence length " + std::to_string(T) + " is too short for this model's pooling stack");
+  // Walk back up: the pair feeding a stage with n steps must run 3n steps.
+  int need = t_last;
+  t_run[s.n_lstm - 1] = need;
+  t_out[s.n_lstm - 1] = 1;
+  for (int p = n_pairs - 1; p >= 0; --p) {
+    need *= 3;
+    t_run[2 * p] = t_run[2 * p + 1] = need;
+    t_out[2 * p] = need;          // full sequence to its partner
+    t_out[2 * p + 1] = need / 3;  // pooled
+  }
+  // Ping/pong: buffer A holds x1 and the outputs of odd layers (1,3,5), buffer B those of even
+  // layers (0,2,4,6).
+  size_t a = size_t(t_run[0]) * s.lstm_in[0], b = 0;
+  for (int l = 0; l < s.n_lstm; ++l) {
+    size_t sz = size_t(t_out[l]) * s.lstm_hid[l];
+    if (l % 2 == 0) b = std::max(b, sz); else a = std::max(a, sz);
+  }
+  bytes_a = a * kTile * sizeof(float);
+  bytes_b = b * kTile * sizeof(float);
+}
+
+// ---------------------------------------------------------------------------------------------
+DeviceModel::~DeviceModel() {
+  if (device >= 0) {
+    cudaSetDevice(device);
+    cudaFree(d_params);
+    cudaFree(d_packed);
+    cudaFree(d_scratch);
+  }
+}
+
+void DeviceModel::upload() {
+  if (device < 0) return;
+  const ModelSpec& s = host.spec;
+  GNNQC_CUDA(cudaSetDevice(device));
+  if (!d_params) GNNQC_CUDA(cudaMalloc(&d_params, size_t(s.n_params) * sizeof(float)));
+  GNNQC_CUDA(cudaMemcpy(d_params, host.params.data(), size_t(s.n_params) * sizeof(float), cudaMemcpyHostToDevice));
+  // Packed per-layer copy: wpk[k][unit][gate], k < in: kernel rows, then recurrent rows, then bias.
+  size_t total = 0;
+  for (int l = 0; l < s.n_lstm; ++l) {
+    packed_off[l] = total;
+    total += size_t(s.lstm_in[l] + s.lstm_hid[l] + 1) * s.lstm_hid[l] * 4;
+  }
+  std::vector<float> packed(total);
+  for (int l = 0; l < s.n_lstm; ++l) {
+    const int in = s.lstm_in[l], h = s.lstm_hid[l];
+    const float* W = host.params.data() + s.off_lstm_w[l];
+    const float* U = host.params.data() + s.off_lstm_u[l];
+    const float* bias = host.params.data() + s.off_lstm_b[l];
+    float* out = packed.data() + packed_off[l];
+    for (int k = 0; k < in + h; ++k) {
+      const float* row = (k < in) ? W + size_t(k) * 4 * h : U + size_t(k - in) * 4 * h;
+      for (int j = 0; j < h; ++j)
+        for (int g = 0; g < 4; ++g) out[(size_t(k) * h + j) * 4 + g] = row[g * h + j];
+    }
+    float* bo = out + size_t(in + h) * h * 4;
+    for (int j = 0; j < h; ++j)
+      for (int g = 0; g < 4; ++g) bo[j * 4 + g] = bias[g * h + j];
+  }
+  if (!d_packed) GNNQC_CUDA(cudaMalloc(&d_packed, total * sizeof(float)));
+  GNNQC_CUDA(cudaMemcpy(d_packed, packed.data(), total * sizeof(float), cudaMemcpyHostToDevice));
+}
+
+void* DeviceModel::scratch(size_t bytes) {
+  if (bytes > scratch_bytes) {
+    GNNQC_CUDA(cudaSetDevice(device));
+    if (d_scratch) {
+      GNNQC_CUDA(cudaDeviceSynchronize());
+      GNNQC_CUDA(cudaFree(d_scratch));
+      d_scratch = nullptr;
+      scratch_bytes = 0;
+    }
+    GNNQC_CUDA(cudaMalloc(&d_scratch, bytes));
+    scratch_bytes = bytes;
+  }
+  return d_scratch;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Per-layer tiling choice: RJ units x RB windows per thread, LJ lanes along the unit axis.
+namespace {
+
+template <int I, int H, bool POOL, bool LAST>
+struct LayerLaunch {
+  static constexpr bool WGLOBAL = (size_t(I + H) * H * 16 > 160 * 1024);
+  static constexpr int RJ = 2, RB = 8, LJ = 8;
+  using Cfg = LstmCfg<I, H, RJ, RB, LJ, WGLOBAL>;
+  static auto kernel() { return lstm_layer_kernel<I, H, RJ, RB, LJ, POOL, LAST, WGLOBAL>; }
+  static void configure() {
+    GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+  }
+  static void launch(const float* x, float* y, const float* wpk, int T, int t_in, int t_out, long long n_tiles,
+                     int sm_count, cudaStream_t st) {
+    int per_sm = 1;
+    GNNQC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel(), Cfg::NT, Cfg::SMEM_BYTES));
+    if (per_sm < 1) throw CudaError("lstm_layer_kernel does not fit on an SM");
+    long long grid = std::min<long long>(n_tiles, static_cast<long long>(sm_count) * per_sm);
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles));
+    GNNQC_CUDA(cudaGetLastError());
+  }
+};
+
+template <bool CONFIGURE_ONLY, int I, int H, bool POOL, bool LAST>
+void layer_op(const float* x, float* y, const float* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count,
+              cudaStream_t st) {
+  if (CONFIGURE_ONLY) LayerLaunch<I, H, POOL, LAST>::configure();
+  else LayerLaunch<I, H, POOL, LAST>::launch(x, y, wpk, T, t_in, t_out, n_tiles, sm_count, st);
+}
+
+// Dispatch on the (input width, hidden width, role) combinations the reference's models use.
+template <bool CFG>
+void layer_dispatch(int in, int hid, bool pool, bool last, const float* x, float* y, const float* wpk, int T, int t_in,
+                    int t_out, long long n_tiles, int sm_count, cudaStream_t st) {
+#define GNNQC_CASE(I_, H_, POOL_, LAST_)                                                            \
+  if (in == I_ && hid == H_ && pool == POOL_ && last == LAST_) {                                    \
+    layer_op<CFG, I_, H_, POOL_, LAST_>(x, y, wpk, T, t_in, t_out, n_tiles, sm_count, st);          \
+    return;                                                                                         \
+  }
+  GNNQC_CASE(2, 16, false, false)    // model_cml_baseline time1
+  GNNQC_CASE(3, 16, false, false)    // model_soilnet_baseline time1
+  GNNQC_CASE(18, 16, false, false)   // model_cml time1
+  GNNQC_CASE(19, 16, false, false)   // model_soilnet time1
+  GNNQC_CASE(16, 16, true, false)    // time2 + pool
+  GNNQC_CASE(16, 32, false, false)   // time_layers[0]
+  GNNQC_CASE(32, 32, true, false)    // time_layers[1] + pool
+  GNNQC_CASE(32, 64, false, false)   // time_layers[2]
+  GNNQC_CASE(64, 64, true, false)    // time_layers[3] + pool
+  GNNQC_CASE(64, 128, false, true)   // time4 (last state only)
+#undef GNNQC_CASE
+  throw std::invalid_argument("no kernel for an LSTM layer with input width " + std::to_string(in) + " and " +
+                              std::to_string(hid) + " units (supported: the filter_1_size=16, n_stacks=2 stack)");
+}
+
+}  // namespace
+
+void DeviceModel::configure_kernels() {
+  const ModelSpec& s = host.spec;
+  for (int l = 0; l < s.n_lstm; ++l) {
+    const bool last = (l == s.n_lstm - 1);
+    const bool pool = !last && (l % 2 == 1);
+    layer_dispatch<true>(s.lstm_in[l], s.lstm_hid[l], pool, last, nullptr, nullptr, nullptr, 0, 0, 0, 0, 0, nullptr);
+  }
+  if (s.lstm_hid[s.n_lstm - 1] != 128 || s.dense_units != 64)
+    throw std::invalid_argument("head kernel supports a 128 -> 64 -> 64 -> 1 head only");
+}
+
+void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, long long n_tiles, long long n_seq,
+                            float* scores, cudaStream_t st) {
+  const ModelSpec& s = host.spec;
+  const float* in = buf_a;
+  int t_in = plan.t_run[0];
+  for (int l = 0; l < s.n_lstm; ++l) {
+    const bool last = (l == s.n_lstm - 1);
+    const bool pool = !last && (l % 2 == 1);
+    float* out = (l % 2 == 0) ? buf_b : buf_a;
+    layer_dispatch<false>(s.lstm_in[l], s.lstm_hid[l], pool, last, in, out, d_packed + packed_off[l], plan.t_run[l], t_in,
+                          plan.t_out[l], n_tiles, sm_count, st);
+    in = out;
+    t_in = plan.t_out[l];
+  }
+  const float* p = d_params;
+  head_kernel<128, 64><<<static_cast<unsigned>(n_tiles), 256, 0, st>>>(in, p + s.off_d1_w, p + s.off_d1_b, p + s.off_d2_w,
+                                                                       p + s.off_d2_b, p + s.off_out_w, p + s.off_out_b,
+                                                                       s.leaky_alpha, scores, n_seq);
+  GNNQC_CUDA(cudaGetLastError());
+}
+
+static size_t scratch_budget_bytes() {
+  const char* env = std::getenv("GNNQC_SCRATCH_MB");
+  size_t mb = env ? std::strtoull(env, nullptr, 10) : 2048;
+  return std::max<size_t>(mb, 16) << 20;
+}
+
+static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+void DeviceModel::score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t st) {
+  if (n_seq <= 0) return;
+  const ModelSpec& s = host.spec;
+  GNNQC_CUDA(cudaSetDevice(device));
+  StackPlan plan(s, T);
+  const long long n_tiles = (n_seq + kTile - 1) / kTile;
+  const size_t sa = align_up(plan.bytes_a, 256), sb = align_up(plan.bytes_b, 256);
+  const long long chunk = std::max<long long>(1, std::min<long long>(n_tiles, static_cast<long long>(scratch_budget_bytes() / (sa + sb))));
+  char* base = static_cast<char*>(scratch(size_t(chunk) * (sa + sb)));
+  float* buf_a = reinterpret_cast<float*>(base);
+  float* buf_b = reinterpret_cast<float*>(base + size_t(chunk) * sa);
+  const int c_in = s.lstm_in[0];
+  for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
+    const long long nt = std::min(chunk, n_tiles - t0);
+    const long long seq0 = t0 * kTile, ns = std::min<long long>(n_seq - seq0, nt * kTile);
+    dim3 grid(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
+    const float* xs = x + seq0 * T * c_in;
+    if (c_in == 2) seq_to_tiles_kernel<2><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
+    else if (c_in == 3) seq_to_tiles_kernel<3><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
+    else if (c_in == 18) seq_to_tiles_kernel<18><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
+    else if (c_in == 19) seq_to_tiles_kernel<19><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
+    else throw std::invalid_argument("unsupported sequence width");
+    GNNQC_CUDA(cudaGetLastError());
+    run_stack(plan, buf_a, buf_b, nt, ns, scores + seq0, st);
+  }
+}
+
+static GcnFolded fold_gcn(const HostModel& m) {
+  const ModelSpec& s = m.spec;
+  const float* p = m.params.data();
+  GcnFolded f;
+  std::memset(&f, 0, sizeof(f));
+  for (int c = 0; c < kGcnChannels; ++c) {
+    const float scale = p[s.off_bn_gamma + c] / std::sqrt(p[s.off_bn_var + c] + s.bn_eps);
+    for (int k = 0; k < s.n_features; ++k) f.a[k][c] = p[s.off_gcn_kernel + k * kGcnChannels + c] * scale;
+    f.c[c] = (p[s.off_gcn_bias + c] - p[s.off_bn_mean + c]) * scale + p[s.off_bn_beta + c];
+    f.alpha[c] = p[s.off_prelu + c];
+  }
+  return f;
+}
+
+void DeviceModel::score_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
+                            const long long* edge_off, long long B, int T, long long n_nodes, float* scores,
+                            cudaStream_t st) {
+  if (B <= 0) return;
+  const ModelSpec& s = host.spec;
+  GNNQC_CUDA(cudaSetDevice(device));
+  StackPlan plan(s, T);
+  const long long n_tiles = (B + kTile - 1) / kTile;
+  const size_t sa = align_up(plan.bytes_a, 256), sb = align_up(plan.bytes_b, 256);
+  const size_t coef_bytes = align_up(size_t(n_nodes) * sizeof(float), 256);
+  const long long chunk = std::max<long long>(1, std::min<long long>(n_tiles, static_cast<long long>(scratch_budget_bytes() / (sa + sb))));
+  char* base = static_cast<char*>(scratch(2 * coef_bytes + size_t(chunk) * (sa + sb)));
+  int* deg = reinterpret_cast<int*>(base);
+  float* coef = reinterpret_cast<float*>(base + coef_bytes);
+  float* buf_a = reinterpret_cast<float*>(base + 2 * coef_bytes);
+  float* buf_b = reinterpret_cast<float*>(base + 2 * coef_bytes + size_t(chunk) * sa);
+
+  GNNQC_CUDA(cudaMemsetAsync(deg, 0, size_t(n_nodes) * sizeof(int), st));
+  {
+    const long long threads = B * 32;
+    cml_node_coef_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(edges, node_off, edge_off, deg, coef, B);
+    GNNQC_CUDA(cudaGetLastError());
+  }
+  const GcnFolded folded = fold_gcn(host);
+  for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
+    const long long nt = std::min(chunk, n_tiles - t0);
+    const long long win0 = t0 * kTile, nw = std::min<long long>(B - win0, nt * kTile);
+    dim3 grid(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
+    cml_frontend_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), reinterpret_cast<const float2*>(anom) + win0 * T,
+                                              coef, node_off + win0, folded, buf_a, nw, T, plan.t_run[0]);
+    GNNQC_CUDA(cudaGetLastError());
+    run_stack(plan, buf_a, buf_b, nt, nw, scores + win0, st);
+  }
+}
+
+}  // namespace gnnqc

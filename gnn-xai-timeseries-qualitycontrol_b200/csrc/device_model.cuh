@@ -1,0 +1,62 @@
+// Device-resident model: uploaded weights (flat + per-layer packed copies), scratch arena,
+// and the host-side launch plan of the scoring pipeline.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+#include "model_spec.h"
+
+namespace gnnqc {
+
+struct CudaError : std::runtime_error {
+  using std::runtime_error::runtime_error;
+};
+
+#define GNNQC_CUDA(expr)                                                                        \
+  do {                                                                                          \
+    cudaError_t err__ = (expr);                                                                 \
+    if (err__ != cudaSuccess)                                                                   \
+      throw ::gnnqc::CudaError(std::string(#expr) + ": " + cudaGetErrorString(err__));          \
+  } while (0)
+
+// Number of steps each stage of the TimeLayer actually has to run for a T-step input.
+// MaxPooling1D(3, 'valid') floors, and only the last state of the final LSTM is used
+// (libs/create_model.py:68,76,78-79), so steps past 27*T7 (first pair), 9*T7 (second pair)
+// and 3*T7 (third pair) cannot influence the score and are not computed.
+struct StackPlan {
+  int T = 0;
+  int t_run[kMaxLstmLayers] = {0};  // steps executed per layer
+  int t_out[kMaxLstmLayers] = {0};  // time extent of each layer's stored output
+  size_t bytes_a = 0, bytes_b = 0;  // per-tile ping/pong buffer sizes
+  explicit StackPlan(const ModelSpec& s, int T);
+  size_t bytes_per_tile() const { return bytes_a + bytes_b; }
+};
+
+struct DeviceModel {
+  HostModel host;
+  int device = -1;              // < 0: host-only handle
+  int sm_count = 0;
+  float* d_params = nullptr;    // flat vector, layout of ModelSpec
+  float* d_packed = nullptr;    // per-layer [k][unit][gate] + bias[unit][gate]
+  size_t packed_off[kMaxLstmLayers] = {0};
+  void* d_scratch = nullptr;
+  size_t scratch_bytes = 0;
+
+  ~DeviceModel();
+  void upload();                // host.params -> d_params, d_packed
+  void* scratch(size_t bytes);  // grow-only arena
+  void configure_kernels();     // opt-in shared memory sizes, once per handle
+
+  // x1: sequence tiles [n_tiles][plan.t_run[0]][lstm_in[0]][64] already in `buf_a`.
+  void run_stack(const StackPlan& plan, float* buf_a, float* buf_b, long long n_tiles, long long n_seq,
+                 float* scores, cudaStream_t stream);
+  void score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t stream);
+  void score_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
+                 const long long* edge_off, long long B, int T, long long n_nodes, float* scores,
+                 cudaStream_t stream);
+};
+
+}  // namespace gnnqc

@@ -1,0 +1,161 @@
+"""Handle-level Python wrapper over the C ABI.  torch is used only to own device buffers and
+streams; all arithmetic happens inside libgnnqc.so."""
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import check, lib
+
+
+def _torch():
+    import torch
+
+    return torch
+
+
+class NativeModel:
+    """One gnnqc_model handle (one GPU, or host-only when device is None / < 0)."""
+
+    def __init__(self, handle):
+        self._h = C.c_void_p(handle)
+        d = _lib.ModelDesc()
+        check(lib.gnnqc_model_describe(self._h, C.byref(d)))
+        self.desc = d
+        self.has_gcn = bool(d.has_gcn)
+        self.soilnet = bool(d.soilnet)
+        self.ds_type = d.ds_type.decode()
+        self.normalization = d.normalization.decode()
+        self.n_features = d.n_features
+        self.n_params = d.n_params
+        self.n_trainable = d.n_trainable
+        self.lstm_in = list(d.lstm_in[: d.n_lstm])
+        self.lstm_hid = list(d.lstm_hid[: d.n_lstm])
+        self.model_info = np.array(list(d.model_info[: d.n_model_info]), dtype=np.int32)
+        self.seq_len = d.seq_len
+
+    # ---- construction ------------------------------------------------------------------
+    @classmethod
+    def load(cls, savedmodel_dir, device=0):
+        h = C.c_void_p()
+        dev = -1 if device is None else int(device)
+        check(lib.gnnqc_model_load(str(savedmodel_dir).encode(), dev, C.byref(h)))
+        m = cls(h.value)
+        m.device = dev
+        return m
+
+    @classmethod
+    def create(cls, has_gcn, soilnet, params=None, filter_1_size=16, n_stacks=2, dense_units=64, model_info=None,
+               normalization="", device=0):
+        h = C.c_void_p()
+        dev = -1 if device is None else int(device)
+        p = None
+        n = 0
+        if params is not None:
+            params = np.ascontiguousarray(params, dtype=np.float32)
+            p = params.ctypes.data_as(C.POINTER(C.c_float))
+            n = params.size
+        mi = None
+        n_mi = 0
+        if model_info is not None:
+            mi_arr = np.ascontiguousarray(model_info, dtype=np.int32)
+            mi = mi_arr.ctypes.data_as(C.POINTER(C.c_int32))
+            n_mi = mi_arr.size
+        check(lib.gnnqc_model_create(int(has_gcn), int(soilnet), filter_1_size, n_stacks, dense_units, p, n, mi, n_mi,
+                                     normalization.encode(), dev, C.byref(h)))
+        m = cls(h.value)
+        m.device = dev
+        return m
+
+    def close(self):
+        if self._h:
+            lib.gnnqc_model_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- parameters --------------------------------------------------------------------
+    def get_params(self):
+        out = np.empty(self.n_params, dtype=np.float32)
+        check(lib.gnnqc_model_get_params(self._h, out.ctypes.data_as(C.POINTER(C.c_float)), out.size))
+        return out
+
+    def set_params(self, params):
+        params = np.ascontiguousarray(params, dtype=np.float32)
+        check(lib.gnnqc_model_set_params(self._h, params.ctypes.data_as(C.POINTER(C.c_float)), params.size))
+
+    def segments(self):
+        """[(path, offset, shape, trainable)] of the flat parameter vector."""
+        out = []
+        idx = 0
+        while True:
+            path = (C.c_char * 128)()
+            off = C.c_int64()
+            shape = (C.c_int64 * 4)()
+            rank = C.c_int32()
+            tr = C.c_int32()
+            rc = lib.gnnqc_model_segment(self._h, idx, path, C.byref(off), shape, C.byref(rank), C.byref(tr))
+            if rc != _lib.OK:
+                break
+            out.append((path.value.decode(), off.value, tuple(shape[: rank.value]), bool(tr.value)))
+            idx += 1
+        return out
+
+    def named_params(self):
+        flat = self.get_params()
+        return {p: flat[o : o + int(np.prod(s))].reshape(s) for p, o, s, _ in self.segments()}
+
+    def save(self, directory):
+        check(lib.gnnqc_model_save(self._h, str(directory).encode()))
+
+    # ---- device entry points -----------------------------------------------------------
+    def _stream(self):
+        torch = _torch()
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def _dev_tensor(self, t, dtype, name):
+        torch = _torch()
+        if not isinstance(t, torch.Tensor) or not t.is_cuda or t.device.index != self.device:
+            raise ValueError("%s must be a CUDA tensor on device %d" % (name, self.device))
+        if t.dtype != dtype:
+            raise ValueError("%s must have dtype %s, got %s" % (name, dtype, t.dtype))
+        return t.contiguous()
+
+    def score_seq(self, x):
+        """x: cuda f32 [n_seq, T, C] -> cuda f32 [n_seq]."""
+        torch = _torch()
+        x = self._dev_tensor(x, torch.float32, "x")
+        if x.dim() != 3 or x.shape[2] != self.lstm_in[0]:
+            raise ValueError("x must be [n_seq, T, %d], got %s" % (self.lstm_in[0], tuple(x.shape)))
+        out = torch.empty(x.shape[0], dtype=torch.float32, device=x.device)
+        check(lib.gnnqc_score_seq(self._h, x.data_ptr(), x.shape[0], x.shape[1], out.data_ptr(), self._stream()))
+        return out
+
+    def score_cml(self, features, anom, edges, node_off, edge_off, n_nodes_total=None):
+        """Arguments as documented for gnnqc_score_cml in include/gnnqc.h (all CUDA tensors)."""
+        torch = _torch()
+        features = self._dev_tensor(features, torch.float32, "features")
+        anom = self._dev_tensor(anom, torch.float32, "anom")
+        edges = self._dev_tensor(edges, torch.int64, "edges")
+        node_off = self._dev_tensor(node_off, torch.int32, "node_off")
+        edge_off = self._dev_tensor(edge_off, torch.int64, "edge_off")
+        B, T = anom.shape[0], anom.shape[1]
+        if anom.dim() != 3 or anom.shape[2] != 2 or features.dim() != 2 or features.shape[1] != 2:
+            raise ValueError("expected features [Ntot,2] and anom [B,T,2]")
+        if node_off.numel() != B + 1 or edge_off.numel() != B + 1:
+            raise ValueError("node_off / edge_off must have B+1 entries")
+        if n_nodes_total is None:
+            n_nodes_total = int(node_off[-1].item())
+        if features.shape[0] != n_nodes_total * T:
+            raise ValueError("features has %d rows, expected sum(N_b)*T = %d" % (features.shape[0], n_nodes_total * T))
+        out = torch.empty(B, dtype=torch.float32, device=anom.device)
+        check(lib.gnnqc_score_cml(self._h, features.data_ptr(), anom.data_ptr(), edges.data_ptr(), node_off.data_ptr(),
+                                  edge_off.data_ptr(), B, T, n_nodes_total, out.data_ptr(), self._stream()))
+        return out
+
+    def scratch_bytes(self, n_seq, T):
+        return int(lib.gnnqc_score_scratch_bytes(self._h, n_seq, T))

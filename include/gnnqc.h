@@ -1,0 +1,141 @@
+/* gnnqc.h - C ABI of libgnnqc.so: B200 (sm_100a) scoring / attribution / training of the
+ * sensor-window anomaly models of timohouben/GNN-XAI-TimeSeries-QualityControl.
+ *
+ * The reference has no FFI layer: its boundary is the Keras Model object.  Each entry point
+ * below names the reference call it stands in for (paths relative to the reference root).
+ * INTEGRATION.md shows the ctypes binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *  - Every function returns 0 on success or a negative GNNQC_ERR_* code; the message for the
+ *    calling thread's last failure is gnnqc_last_error().
+ *  - Pointers named *_dev are device pointers on the model's GPU, owned by the caller.
+ *    Pointers named *_host are host pointers.  `stream` is a cudaStream_t passed as void*
+ *    (NULL = the legacy default stream).  Device entry points only enqueue work; they do not
+ *    synchronise the stream.
+ *  - A handle is bound to one GPU and is not thread-safe; use one handle per GPU / rank.
+ *  - There is no CPU fallback: device entry points fail with GNNQC_ERR_STATE on a handle that
+ *    was opened with device < 0 (host-only inspection handle), and with GNNQC_ERR_CUDA when
+ *    no usable GPU is present.
+ */
+#ifndef GNNQC_H_
+#define GNNQC_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GNNQC_ABI_VERSION 1
+
+#define GNNQC_OK 0
+#define GNNQC_ERR_ARG (-1)    /* bad argument / shape */
+#define GNNQC_ERR_CKPT (-2)   /* unreadable or unsupported checkpoint */
+#define GNNQC_ERR_CUDA (-3)   /* CUDA runtime error */
+#define GNNQC_ERR_NCCL (-4)   /* NCCL error */
+#define GNNQC_ERR_STATE (-5)  /* call not valid for this handle */
+
+typedef struct gnnqc_model gnnqc_model;
+
+/* Architecture + metadata of a loaded model.  Mirrors the attributes the reference reads
+ * off the Keras model: model.model_info (libs/test_model.py:22-25, libs/visualize.py:160-163),
+ * model_type / model_normalization (libs/create_model.py:163-165). */
+typedef struct gnnqc_model_desc {
+  int32_t has_gcn;        /* 1 = GCNClassifier, 0 = BaselineClassifier */
+  int32_t soilnet;        /* 1 = ds_type 'soilnet', 0 = 'cml' */
+  int32_t n_features;     /* 2 (cml) or 3 (soilnet) */
+  int32_t n_lstm;         /* 7 for every shipped model */
+  int32_t lstm_in[8];
+  int32_t lstm_hid[8];
+  int32_t dense_units;
+  int32_t n_model_info;   /* 3 or 4 */
+  int32_t model_info[4];  /* timestep_before, timestep_after, batch_size, freq */
+  int32_t seq_len;        /* (timestep_before + timestep_after) / freq + 1 */
+  int64_t n_params;       /* floats in the flat parameter vector */
+  int64_t n_trainable;
+  char ds_type[16];
+  char normalization[32];
+} gnnqc_model_desc;
+
+int gnnqc_abi_version(void);
+const char* gnnqc_last_error(void);
+
+/* ---- model lifetime ------------------------------------------------------------------- */
+
+/* Replaces tf.keras.models.load_model(model_path, compile=False) (notebooks/pipeline.ipynb:202,
+ * :436; xai/libs/integrated_gradients.py:199-201).  `savedmodel_dir` is a Keras SavedModel
+ * directory (model_cml, model_cml_baseline, model_soilnet, model_soilnet_baseline); only its
+ * variables/variables.{index,data-00000-of-00001} are read.  device >= 0 uploads the weights to
+ * that GPU; device < 0 opens a host-only handle (inspection, save). */
+int gnnqc_model_load(const char* savedmodel_dir, int device, gnnqc_model** out);
+
+/* Replaces the constructors GCNClassifier(model_config, preproc_config) /
+ * BaselineClassifier(...) (libs/create_model.py:140-213, :261-341): builds a model of the
+ * given architecture from a caller-supplied flat parameter vector (layout: see
+ * gnnqc_model_segment).  model_info may be NULL. */
+int gnnqc_model_create(int has_gcn, int soilnet, int filter_1_size, int n_stacks, int dense_units,
+                       const float* params_host, int64_t n_params, const int32_t* model_info,
+                       int n_model_info, const char* normalization, int device, gnnqc_model** out);
+
+int gnnqc_model_describe(const gnnqc_model* m, gnnqc_model_desc* out);
+
+/* Flat parameter vector (host copies).  Stands in for model.get_weights()/set_weights(). */
+int gnnqc_model_get_params(const gnnqc_model* m, float* out_host, int64_t n);
+int gnnqc_model_set_params(gnnqc_model* m, const float* in_host, int64_t n);
+
+/* Segment `idx` of the flat vector: the variable's attribute path in the reference's object
+ * graph (e.g. "time_layer/time1/cell/kernel"), its offset, shape and trainability.
+ * Returns GNNQC_ERR_ARG once idx is past the last segment. */
+int gnnqc_model_segment(const gnnqc_model* m, int idx, char path[128], int64_t* offset,
+                        int64_t shape[4], int32_t* rank, int32_t* trainable);
+
+/* Replaces model.save(model_config.model_path) (notebooks/pipeline.ipynb cell 14): writes
+ * <dir>/variables/variables.{index,data-00000-of-00001} in TF tensor-bundle format with the
+ * reference's checkpoint keys and object-graph paths. */
+int gnnqc_model_save(const gnnqc_model* m, const char* dir);
+
+void gnnqc_model_free(gnnqc_model* m);
+
+/* ---- scoring -------------------------------------------------------------------------- */
+
+/* Replaces BaselineClassifier.call on a CML batch (libs/create_model.py:343-377, driven by
+ * model.predict at libs/test_model.py:29 with wrapper_batch_mapping_baseline_cml,
+ * libs/preprocessing_functions.py:756-760), and the LSTM-stack + head half of every other
+ * model.  x_dev: f32 [n_seq, T, C] row-major, C = the model's first LSTM input width
+ * (2 for model_cml_baseline, 3 for model_soilnet_baseline after graph_reshape).
+ * scores_dev: f32 [n_seq]. */
+int gnnqc_score_seq(gnnqc_model* m, const float* x_dev, int64_t n_seq, int32_t T,
+                    float* scores_dev, void* stream);
+
+/* Replaces GCNClassifier.call for ds_type 'cml' (libs/create_model.py:215-223,233-240), i.e.
+ * model.predict on batches from prepare_batch_cml / wrapper_batch_mapping_cml
+ * (libs/preprocessing_functions.py:638-666, :744-746).
+ *   features_dev  f32 [sum_b T*N_b, 2], rows in (window, timestep, node) order   (:640-641)
+ *   anom_dev      f32 [B, T, 2]  the target sensor's own series                  (:642)
+ *   edges_dev     i64 [E_total, 2] per-window edge list (row = receiving node, col = sending
+ *                 node, both local to the window), NOT tiled over timesteps      (:221, :651-661)
+ *   node_off_dev  i32 [B+1] prefix sums of N_b;  edge_off_dev i64 [B+1] prefix sums of E_b
+ *   n_nodes_total = node_off[B] (host copy, so the call needs no device->host read)
+ *   scores_dev    f32 [B]
+ * Every window gets a score (the reference silently drops windows whose pooled features sum
+ * to exactly 0, libs/create_model.py:30-36). */
+int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom_dev,
+                    const int64_t* edges_dev, const int32_t* node_off_dev,
+                    const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
+                    float* scores_dev, void* stream);
+
+/* Bytes of device scratch the scoring entry points keep inside the handle for `n_seq`
+ * sequences of length T (grown on demand with cudaMalloc, freed by gnnqc_model_free). */
+int64_t gnnqc_score_scratch_bytes(const gnnqc_model* m, int64_t n_seq, int32_t T);
+
+/* ---- measurement helpers -------------------------------------------------------------- */
+
+/* No reference counterpart (measurement only): sustained FP32 FMA throughput of `device` in
+ * TFLOP/s, mode 0 = scalar FFMA, mode 1 = packed fma.rn.f32x2.  bench.py uses it as the
+ * roofline denominator of the fp32 LSTM kernels. */
+int gnnqc_probe_fp32_peak(int device, int mode, double* tflops_out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GNNQC_H_ */
