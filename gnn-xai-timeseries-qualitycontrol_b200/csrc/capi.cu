@@ -211,6 +211,46 @@ int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom
   });
 }
 
+int64_t gnnqc_launch_count(const gnnqc_model* m) { return m ? m->dm.launches : 0; }
+
+int gnnqc_profile_enable(gnnqc_model* m, int on) {
+  if (int rc = need_device(m, "gnnqc_profile_enable")) return rc;
+  return guarded([&] {
+    GNNQC_CUDA(cudaSetDevice(m->dm.device));
+    m->dm.profile_reset();
+    m->dm.profiling = on != 0;
+  });
+}
+
+int gnnqc_profile_read(gnnqc_model* m, int max_entries, char (*names)[32], double* total_ms, int64_t* counts, int* n_out) {
+  if (int rc = need_device(m, "gnnqc_profile_read")) return rc;
+  if (!names || !total_ms || !counts || !n_out || max_entries <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_profile_read: null argument");
+  return guarded([&] {
+    GNNQC_CUDA(cudaSetDevice(m->dm.device));
+    GNNQC_CUDA(cudaDeviceSynchronize());
+    int n = 0;
+    for (const gnnqc::LaunchRecord& r : m->dm.records) {
+      float ms = 0.f;
+      GNNQC_CUDA(cudaEventElapsedTime(&ms, r.start, r.stop));
+      int slot = -1;
+      for (int i = 0; i < n; ++i)
+        if (std::strncmp(names[i], r.name, 31) == 0) slot = i;
+      if (slot < 0) {
+        if (n >= max_entries) continue;
+        slot = n++;
+        std::memset(names[slot], 0, 32);
+        std::strncpy(names[slot], r.name, 31);
+        total_ms[slot] = 0.0;
+        counts[slot] = 0;
+      }
+      total_ms[slot] += ms;
+      counts[slot] += 1;
+    }
+    *n_out = n;
+    m->dm.profile_reset();
+  });
+}
+
 int64_t gnnqc_score_scratch_bytes(const gnnqc_model* m, int64_t n_seq, int32_t T) {
   if (!m || n_seq < 0 || T <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_score_scratch_bytes: bad argument");
   int64_t bytes = 0;

@@ -38,9 +38,35 @@ StackPlan::StackPlan(const ModelSpec& s, int T_) : T(T_) {
 }
 
 // ---------------------------------------------------------------------------------------------
+void DeviceModel::mark_begin(const char* name, cudaStream_t st) {
+  ++launches;
+  if (!profiling) return;
+  auto get = [&]() {
+    if (!event_pool.empty()) { cudaEvent_t e = event_pool.back(); event_pool.pop_back(); return e; }
+    cudaEvent_t e;
+    GNNQC_CUDA(cudaEventCreate(&e));
+    return e;
+  };
+  LaunchRecord r{name, get(), get()};
+  GNNQC_CUDA(cudaEventRecord(r.start, st));
+  records.push_back(r);
+}
+
+void DeviceModel::mark_end(cudaStream_t st) {
+  if (!profiling) return;
+  GNNQC_CUDA(cudaEventRecord(records.back().stop, st));
+}
+
+void DeviceModel::profile_reset() {
+  for (LaunchRecord& r : records) { event_pool.push_back(r.start); event_pool.push_back(r.stop); }
+  records.clear();
+}
+
 DeviceModel::~DeviceModel() {
   if (device >= 0) {
     cudaSetDevice(device);
+    profile_reset();
+    for (cudaEvent_t e : event_pool) cudaEventDestroy(e);
     cudaFree(d_params);
     cudaFree(d_packed);
     cudaFree(d_scratch);
@@ -171,16 +197,21 @@ void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, l
     const bool last = (l == s.n_lstm - 1);
     const bool pool = !last && (l % 2 == 1);
     float* out = (l % 2 == 0) ? buf_b : buf_a;
+    static const char* const kNames[kMaxLstmLayers] = {"lstm_l1", "lstm_l2", "lstm_l3", "lstm_l4", "lstm_l5", "lstm_l6", "lstm_l7"};
+    mark_begin(kNames[l], st);
     layer_dispatch<false>(s.lstm_in[l], s.lstm_hid[l], pool, last, in, out, d_packed + packed_off[l], plan.t_run[l], t_in,
                           plan.t_out[l], n_tiles, sm_count, st);
+    mark_end(st);
     in = out;
     t_in = plan.t_out[l];
   }
   const float* p = d_params;
+  mark_begin("head", st);
   head_kernel<128, 64><<<static_cast<unsigned>(n_tiles), 256, 0, st>>>(in, p + s.off_d1_w, p + s.off_d1_b, p + s.off_d2_w,
                                                                        p + s.off_d2_b, p + s.off_out_w, p + s.off_out_b,
                                                                        s.leaky_alpha, scores, n_seq);
   GNNQC_CUDA(cudaGetLastError());
+  mark_end(st);
 }
 
 static size_t scratch_budget_bytes() {
@@ -208,12 +239,14 @@ void DeviceModel::score_seq(const float* x, long long n_seq, int T, float* score
     const long long seq0 = t0 * kTile, ns = std::min<long long>(n_seq - seq0, nt * kTile);
     dim3 grid(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
     const float* xs = x + seq0 * T * c_in;
+    mark_begin("seq_to_tiles", st);
     if (c_in == 2) seq_to_tiles_kernel<2><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
     else if (c_in == 3) seq_to_tiles_kernel<3><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
     else if (c_in == 18) seq_to_tiles_kernel<18><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
     else if (c_in == 19) seq_to_tiles_kernel<19><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
     else throw std::invalid_argument("unsupported sequence width");
     GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
     run_stack(plan, buf_a, buf_b, nt, ns, scores + seq0, st);
   }
 }
@@ -252,17 +285,21 @@ void DeviceModel::score_cml(const float* feat, const float* anom, const long lon
   GNNQC_CUDA(cudaMemsetAsync(deg, 0, size_t(n_nodes) * sizeof(int), st));
   {
     const long long threads = B * 32;
+    mark_begin("cml_node_coef", st);
     cml_node_coef_kernel<<<static_cast<unsigned>((threads + 255) / 256), 256, 0, st>>>(edges, node_off, edge_off, deg, coef, B);
     GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
   }
   const GcnFolded folded = fold_gcn(host);
   for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
     const long long nt = std::min(chunk, n_tiles - t0);
     const long long win0 = t0 * kTile, nw = std::min<long long>(B - win0, nt * kTile);
     dim3 grid(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
+    mark_begin("cml_frontend", st);
     cml_frontend_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), reinterpret_cast<const float2*>(anom) + win0 * T,
                                               coef, node_off + win0, folded, buf_a, nw, T, plan.t_run[0]);
     GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
     run_stack(plan, buf_a, buf_b, nt, nw, scores + win0, st);
   }
 }

@@ -35,6 +35,12 @@ struct StackPlan {
   size_t bytes_per_tile() const { return bytes_a + bytes_b; }
 };
 
+// Optional per-launch timing (CUDA events on the launching stream) + an always-on launch counter.
+struct LaunchRecord {
+  const char* name;
+  cudaEvent_t start, stop;
+};
+
 struct DeviceModel {
   HostModel host;
   int device = -1;              // < 0: host-only handle
@@ -44,6 +50,14 @@ struct DeviceModel {
   size_t packed_off[kMaxLstmLayers] = {0};
   void* d_scratch = nullptr;
   size_t scratch_bytes = 0;
+
+  long long launches = 0;       // kernels enqueued by this handle since creation
+  bool profiling = false;
+  std::vector<LaunchRecord> records;
+  std::vector<cudaEvent_t> event_pool;
+  void mark_begin(const char* name, cudaStream_t st);
+  void mark_end(cudaStream_t st);
+  void profile_reset();
 
   ~DeviceModel();
   void upload();                // host.params -> d_params, d_packed

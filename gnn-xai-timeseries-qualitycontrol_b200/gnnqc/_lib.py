@@ -62,6 +62,9 @@ def _load():
         "gnnqc_score_seq": (C.c_int, [vp, vp, i64, i32, vp, vp]),
         "gnnqc_score_cml": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, vp, vp]),
         "gnnqc_score_scratch_bytes": (i64, [vp, i64, i32]),
+        "gnnqc_launch_count": (i64, [vp]),
+        "gnnqc_profile_enable": (C.c_int, [vp, C.c_int]),
+        "gnnqc_profile_read": (C.c_int, [vp, C.c_int, vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(C.c_int)]),
         "gnnqc_probe_fp32_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double)]),
     }
     for name, (res, args) in sigs.items():

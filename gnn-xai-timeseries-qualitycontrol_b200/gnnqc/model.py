@@ -157,5 +157,21 @@ class NativeModel:
                                   edge_off.data_ptr(), B, T, n_nodes_total, out.data_ptr(), self._stream()))
         return out
 
+    # ---- measurement ---------------------------------------------------------------------
+    def launch_count(self):
+        return int(lib.gnnqc_launch_count(self._h))
+
+    def profile(self, on=True):
+        check(lib.gnnqc_profile_enable(self._h, int(on)))
+
+    def profile_read(self, max_entries=64):
+        """{kernel name: (total ms, launches)} since the last read; synchronises the device."""
+        names = ((C.c_char * 32) * max_entries)()
+        ms = (C.c_double * max_entries)()
+        cnt = (C.c_int64 * max_entries)()
+        n = C.c_int()
+        check(lib.gnnqc_profile_read(self._h, max_entries, C.cast(names, C.c_void_p), ms, cnt, C.byref(n)))
+        return {names[i].value.decode(): (ms[i], cnt[i]) for i in range(n.value)}
+
     def scratch_bytes(self, n_seq, T):
         return int(lib.gnnqc_score_scratch_bytes(self._h, n_seq, T))

@@ -57,13 +57,13 @@ def make_cml_batch(n_windows, seed=44, n_nodes=23, ragged=False, T=181, device="
     x = _ar1(0.5 * math.sqrt(1 - 0.95 ** 2) * torch.randn((B, T, N, 2), generator=g, device=dev), 0.95)
     rain = torch.rand((B,), generator=g, device=dev) < 0.10
     amp = 1.0 + 7.0 * torch.rand((B,), generator=g, device=dev)
-    centre = torch.randint(20, T - 20, (B,), generator=g, device=dev)
+    centre = torch.randint(min(20, T // 4), max(T - 20, T // 4 + 1), (B,), generator=g, device=dev)
     width = 5.0 + 25.0 * torch.rand((B,), generator=g, device=dev)
     tt = torch.arange(T, device=dev, dtype=torch.float32)[None, :]
     bump = amp[:, None] * torch.exp(-0.5 * ((tt - centre[:, None]) / width[:, None]) ** 2)
     x = x + (rain[:, None] * bump)[:, :, None, None]
     anomalous = torch.rand((B,), generator=g, device=dev) < 0.05
-    jump_at = torch.randint(90, 150, (B,), generator=g, device=dev)
+    jump_at = torch.randint(T // 2, max(T // 2 + 1, (5 * T) // 6), (B,), generator=g, device=dev)
     jump = (2.0 + 8.0 * torch.rand((B,), generator=g, device=dev))[:, None] * (tt >= jump_at[:, None])
     sel = torch.arange(B, device=dev)
     x[sel, :, target] = x[sel, :, target] + (anomalous[:, None] * jump)[:, :, None]

@@ -135,6 +135,16 @@ int64_t gnnqc_score_scratch_bytes(const gnnqc_model* m, int64_t n_seq, int32_t T
  * roofline denominator of the fp32 LSTM kernels. */
 int gnnqc_probe_fp32_peak(int device, int mode, double* tflops_out);
 
+/* No reference counterpart (measurement only).  gnnqc_launch_count: kernels this handle has
+ * enqueued since it was created.  gnnqc_profile_enable(1) makes every later launch record a
+ * pair of CUDA events on its stream; gnnqc_profile_read synchronises the device, sums the
+ * elapsed time per kernel name into the caller's arrays (at most max_entries names of 31
+ * chars) and clears the records. */
+int64_t gnnqc_launch_count(const gnnqc_model* m);
+int gnnqc_profile_enable(gnnqc_model* m, int on);
+int gnnqc_profile_read(gnnqc_model* m, int max_entries, char (*names)[32], double* total_ms,
+                       int64_t* counts, int* n_out);
+
 #ifdef __cplusplus
 }
 #endif
