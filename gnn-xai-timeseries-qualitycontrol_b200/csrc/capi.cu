@@ -5,14 +5,11 @@
 #include <string>
 
 #include "../../include/gnnqc.h"
+#include "capi_internal.h"
 #include "device_model.cuh"
 #include "model_spec.h"
 
 using gnnqc::DeviceModel;
-
-struct gnnqc_model {
-  DeviceModel dm;
-};
 
 namespace {
 
@@ -66,6 +63,8 @@ int need_device(const gnnqc_model* m, const char* what) {
 }
 
 }  // namespace
+
+int gnnqc_internal_fail(int code, const std::string& msg) { return fail(code, msg); }
 
 extern "C" {
 

@@ -39,7 +39,7 @@ __global__ void __launch_bounds__(256) seq_to_tiles_kernel(const float* __restri
 //   pooled[t] = sum_j coef_j * z_j[t],   coef_j = (1/N) * sum_{(i,j) in E} 1/deg_i,
 // with deg_i the number of edges received by node i.  One warp per window; `deg` is integer
 // scratch that must be zero on entry.
-__global__ void __launch_bounds__(256) cml_node_coef_kernel(const long long* __restrict__ edges,
+static __global__ void __launch_bounds__(256) cml_node_coef_kernel(const long long* __restrict__ edges,
                                                             const int* __restrict__ node_off,
                                                             const long long* __restrict__ edge_off,
                                                             int* __restrict__ deg, float* __restrict__ coef,
@@ -76,7 +76,7 @@ struct GcnFolded {
 // ---- CML front-end: features (b,t,n) + coef + target series -> x1 tiles [tile][t][18][64] --
 // Restates GCNClassifier.call for 'cml' up to the Concatenate (libs/create_model.py:217-223):
 // channels 0..1 = anomalous_sensor_features, 2..17 = pooled GeneralConv output.
-__global__ void __launch_bounds__(256) cml_frontend_kernel(const float2* __restrict__ feat, const float2* __restrict__ anom,
+static __global__ void __launch_bounds__(256) cml_frontend_kernel(const float2* __restrict__ feat, const float2* __restrict__ anom,
                                                            const float* __restrict__ coef, const int* __restrict__ node_off,
                                                            const GcnFolded p, float* __restrict__ out,
                                                            long long n_windows, int T, int t_run) {

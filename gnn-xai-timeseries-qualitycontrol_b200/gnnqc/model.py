@@ -135,6 +135,18 @@ class NativeModel:
         check(lib.gnnqc_score_seq(self._h, x.data_ptr(), x.shape[0], x.shape[1], out.data_ptr(), self._stream()))
         return out
 
+    def score_seq_noalloc(self, x, out):
+        """gnnqc_score_seq_noalloc: like score_seq, but the library allocates nothing, so the
+        caller also supplies `out` (cuda f32 [n_seq]).  For callers that must not allocate on
+        the scoring path; see include/gnnqc.h for the size limit and the sharing rules."""
+        torch = _torch()
+        x = self._dev_tensor(x, torch.float32, "x")
+        out = self._dev_tensor(out, torch.float32, "out")
+        if x.dim() != 3 or x.shape[2] != self.lstm_in[0] or out.numel() != x.shape[0]:
+            raise ValueError("x must be [n_seq, T, %d] and out [n_seq]" % self.lstm_in[0])
+        check(lib.gnnqc_score_seq_noalloc(self._h, x.data_ptr(), x.shape[0], x.shape[1], out.data_ptr(), self._stream()))
+        return out
+
     def score_cml(self, features, anom, edges, node_off, edge_off, n_nodes_total=None):
         """Arguments as documented for gnnqc_score_cml in include/gnnqc.h (all CUDA tensors)."""
         torch = _torch()

@@ -124,6 +124,25 @@ int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom
                     const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
                     float* scores_dev, void* stream);
 
+/* gnnqc_score_seq for callers that are not allowed to allocate.  It has no counterpart in the
+ * reference.  Some users of this library cannot call cudaMalloc where they score: a
+ * fixed-budget real-time loop, a process whose device memory is all owned by another
+ * framework's pool, a callback that must not take allocator locks.  gnnqc_score_seq grows an
+ * arena with cudaMalloc when a larger batch arrives; this variant keeps the inter-layer tiles
+ * in a 32 MiB array that is part of the library image (each GPU that loads the library holds
+ * those 32 MiB until the process exits), performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine.  Same arguments and results as gnnqc_score_seq.
+ *  - Limit: the tiles of one call must fit the array - about 2,300 sequences of 181 steps or
+ *    1,150 of 337 steps; larger calls fail with GNNQC_ERR_ARG and a message naming the limit.
+ *  - The first call on a device looks up the array's device address (cudaGetSymbolAddress);
+ *    make that first call before starting any stream capture.
+ *  - All calls on a device share the array, which keeps the previous call's contents.  Nothing
+ *    in it needs to start at zero (every tile is fully written before it is read), but calls
+ *    that overlap on the GPU - other streams, handles or threads - race; serialise them.
+ *  - Per-launch profiling (gnnqc_profile_enable) must be off, because it creates CUDA events. */
+int gnnqc_score_seq_noalloc(gnnqc_model* m, const float* x_dev, int64_t n_seq, int32_t T,
+                            float* scores_dev, void* stream);
+
 /* Bytes of device scratch the scoring entry points keep inside the handle for `n_seq`
  * sequences of length T (grown on demand with cudaMalloc, freed by gnnqc_model_free). */
 int64_t gnnqc_score_scratch_bytes(const gnnqc_model* m, int64_t n_seq, int32_t T);
