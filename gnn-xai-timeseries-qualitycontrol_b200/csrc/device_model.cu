@@ -124,12 +124,12 @@ void* DeviceModel::scratch(size_t bytes) {
 // Per-layer tiling choice: RJ units x RB windows per thread, LJ lanes along the unit axis.
 namespace {
 
-template <int I, int H, bool POOL, bool LAST>
+template <int I, int H, bool POOL, bool LAST, int VAR>
 struct LayerLaunch {
   static constexpr bool WGLOBAL = (size_t(I + H) * H * 16 > 160 * 1024);
-  static constexpr int RJ = 2, RB = 8, LJ = 8;
-  using Cfg = LstmCfg<I, H, RJ, RB, LJ, WGLOBAL>;
-  static auto kernel() { return lstm_layer_kernel<I, H, RJ, RB, LJ, POOL, LAST, WGLOBAL>; }
+  static constexpr int RJ = 2, RB = 8, LJ = (VAR & 8) ? 4 : 8, NST = 2;
+  using Cfg = LstmCfg<I, H, RJ, RB, LJ, WGLOBAL, NST>;
+  static auto kernel() { return lstm_layer_kernel<I, H, RJ, RB, LJ, POOL, LAST, WGLOBAL, (VAR & 7), NST>; }
   static void configure() {
     GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
   }
@@ -144,11 +144,38 @@ struct LayerLaunch {
   }
 };
 
+// Kernel variant (bit 0: packed FFMA2 accumulation, bit 1: merged-reciprocal cell update,
+// bit 2: software-pipelined k-loop, bit 3: 4x8 instead of 8x4 lane layout).
+// GNNQC_LSTM_VARIANT (0, 3, 7, 11, 15) overrides the default for A/B measurements.
+int lstm_variant() {
+  static const int v = [] {
+    const char* e = std::getenv("GNNQC_LSTM_VARIANT");
+    return e ? (std::atoi(e) & 15) : -1;
+  }();
+  return v;
+}
+
 template <bool CONFIGURE_ONLY, int I, int H, bool POOL, bool LAST>
 void layer_op(const float* x, float* y, const float* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count,
               cudaStream_t st) {
-  if (CONFIGURE_ONLY) LayerLaunch<I, H, POOL, LAST>::configure();
-  else LayerLaunch<I, H, POOL, LAST>::launch(x, y, wpk, T, t_in, t_out, n_tiles, sm_count, st);
+  if (CONFIGURE_ONLY) {
+    LayerLaunch<I, H, POOL, LAST, 0>::configure();
+    LayerLaunch<I, H, POOL, LAST, 3>::configure();
+    LayerLaunch<I, H, POOL, LAST, 7>::configure();
+    LayerLaunch<I, H, POOL, LAST, 11>::configure();
+    LayerLaunch<I, H, POOL, LAST, 15>::configure();
+    return;
+  }
+  // Default (no override): measured best per role on B200 - pooled layers like the software-
+  // pipelined loop (variant 7), the others the 4x8 lane layout (variant 11); profiles/README.md.
+  const int variant = lstm_variant() >= 0 ? lstm_variant() : (POOL ? 7 : 11);
+  switch (variant) {
+    case 0: LayerLaunch<I, H, POOL, LAST, 0>::launch(x, y, wpk, T, t_in, t_out, n_tiles, sm_count, st); break;
+    case 7: LayerLaunch<I, H, POOL, LAST, 7>::launch(x, y, wpk, T, t_in, t_out, n_tiles, sm_count, st); break;
+    case 11: LayerLaunch<I, H, POOL, LAST, 11>::launch(x, y, wpk, T, t_in, t_out, n_tiles, sm_count, st); break;
+    case 15: LayerLaunch<I, H, POOL, LAST, 15>::launch(x, y, wpk, T, t_in, t_out, n_tiles, sm_count, st); break;
+    default: LayerLaunch<I, H, POOL, LAST, 3>::launch(x, y, wpk, T, t_in, t_out, n_tiles, sm_count, st); break;
+  }
 }
 
 // Dispatch on the (input width, hidden width, role) combinations the reference's models use.
