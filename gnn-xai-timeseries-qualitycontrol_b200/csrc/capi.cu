@@ -53,6 +53,7 @@ void attach_device(DeviceModel& dm, int device) {
                            "; libgnnqc is built for sm_100a (B200) only");
   dm.sm_count = prop.multiProcessorCount;
   dm.configure_kernels();
+  dm.configure_ig_kernels();
   dm.upload();
 }
 
@@ -207,6 +208,21 @@ int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom
     m->dm.score_cml(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
                     reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, scores_dev,
                     static_cast<cudaStream_t>(stream));
+  });
+}
+
+int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_dev, const int64_t* edges_dev,
+                 const int32_t* node_off_dev, const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
+                 int32_t m_steps, float* attr_features_dev, float* attr_anom_dev, float* scores_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_ig_cml")) return rc;
+  if (!m->dm.host.spec.has_gcn || m->dm.host.spec.soilnet) return fail(GNNQC_ERR_STATE, "gnnqc_ig_cml: model is not a CML GCNClassifier");
+  if (B < 0 || T <= 0 || n_nodes_total < 0 || m_steps < 1) return fail(GNNQC_ERR_ARG, "gnnqc_ig_cml: bad B / T / n_nodes_total / m_steps");
+  if (B > 0 && (!features_dev || !anom_dev || !edges_dev || !node_off_dev || !edge_off_dev || !attr_features_dev || !attr_anom_dev || !scores_dev))
+    return fail(GNNQC_ERR_ARG, "gnnqc_ig_cml: null buffer");
+  return guarded([&] {
+    m->dm.ig_cml(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
+                 reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, m_steps, attr_features_dev, attr_anom_dev,
+                 scores_dev, static_cast<cudaStream_t>(stream));
   });
 }
 

@@ -69,6 +69,7 @@ DeviceModel::~DeviceModel() {
     for (cudaEvent_t e : event_pool) cudaEventDestroy(e);
     cudaFree(d_params);
     cudaFree(d_packed);
+    cudaFree(d_packed_t);
     cudaFree(d_scratch);
   }
 }
@@ -103,6 +104,27 @@ void DeviceModel::upload() {
   }
   if (!d_packed) GNNQC_CUDA(cudaMalloc(&d_packed, total * sizeof(float)));
   GNNQC_CUDA(cudaMemcpy(d_packed, packed.data(), total * sizeof(float), cudaMemcpyHostToDevice));
+
+  // Transposed copy for the backward contraction: wT[col][Kpad], col = gate*H + unit (Keras
+  // column order), row k < in: kernel, then recurrent, zero padded to a multiple of 16 rows.
+  size_t total_t = 0;
+  for (int l = 0; l < s.n_lstm; ++l) {
+    packed_t_off[l] = total_t;
+    const int kpad = (s.lstm_in[l] + s.lstm_hid[l] + 15) / 16 * 16;
+    total_t += size_t(4) * s.lstm_hid[l] * kpad;
+  }
+  std::vector<float> packed_t(total_t, 0.f);
+  for (int l = 0; l < s.n_lstm; ++l) {
+    const int in = s.lstm_in[l], h = s.lstm_hid[l], kpad = (in + h + 15) / 16 * 16;
+    const float* W = host.params.data() + s.off_lstm_w[l];
+    const float* U = host.params.data() + s.off_lstm_u[l];
+    float* out = packed_t.data() + packed_t_off[l];
+    for (int col = 0; col < 4 * h; ++col)
+      for (int k = 0; k < in + h; ++k)
+        out[size_t(col) * kpad + k] = (k < in) ? W[size_t(k) * 4 * h + col] : U[size_t(k - in) * 4 * h + col];
+  }
+  if (!d_packed_t) GNNQC_CUDA(cudaMalloc(&d_packed_t, total_t * sizeof(float)));
+  GNNQC_CUDA(cudaMemcpy(d_packed_t, packed_t.data(), total_t * sizeof(float), cudaMemcpyHostToDevice));
 }
 
 void* DeviceModel::scratch(size_t bytes) {
@@ -139,7 +161,7 @@ struct LayerLaunch {
     GNNQC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel(), Cfg::NT, Cfg::SMEM_BYTES));
     if (per_sm < 1) throw CudaError("lstm_layer_kernel does not fit on an SM");
     long long grid = std::min<long long>(n_tiles, static_cast<long long>(sm_count) * per_sm);
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles));
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), nullptr, nullptr);
     GNNQC_CUDA(cudaGetLastError());
   }
 };

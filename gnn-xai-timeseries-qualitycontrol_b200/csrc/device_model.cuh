@@ -48,6 +48,8 @@ struct DeviceModel {
   float* d_params = nullptr;    // flat vector, layout of ModelSpec
   float* d_packed = nullptr;    // per-layer [k][unit][gate] + bias[unit][gate]
   size_t packed_off[kMaxLstmLayers] = {0};
+  float* d_packed_t = nullptr;  // per-layer transposed copy wT[col][Kpad] for the backward kernels
+  size_t packed_t_off[kMaxLstmLayers] = {0};
   void* d_scratch = nullptr;
   size_t scratch_bytes = 0;
 
@@ -68,6 +70,11 @@ struct DeviceModel {
   void run_stack(const StackPlan& plan, float* buf_a, float* buf_b, long long n_tiles, long long n_seq,
                  float* scores, cudaStream_t stream);
   void score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t stream);
+  // Integrated gradients for the CML GCN model (csrc/ig.cu).
+  void configure_ig_kernels();
+  void ig_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
+              const long long* edge_off, long long B, int T, long long n_nodes, int m_steps, float* attr_feat,
+              float* attr_anom, float* scores, cudaStream_t stream);
   void score_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
                  const long long* edge_off, long long B, int T, long long n_nodes, float* scores,
                  cudaStream_t stream);

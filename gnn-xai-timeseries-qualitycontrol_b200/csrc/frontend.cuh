@@ -39,23 +39,54 @@ __global__ void __launch_bounds__(256) seq_to_tiles_kernel(const float* __restri
 //   pooled[t] = sum_j coef_j * z_j[t],   coef_j = (1/N) * sum_{(i,j) in E} 1/deg_i,
 // with deg_i the number of edges received by node i.  One warp per window; `deg` is integer
 // scratch that must be zero on entry.
+constexpr int kCoefDenseMax = 32;  // windows with at most this many nodes use the shared-memory path
+
 static __global__ void __launch_bounds__(256) cml_node_coef_kernel(const long long* __restrict__ edges,
-                                                            const int* __restrict__ node_off,
-                                                            const long long* __restrict__ edge_off,
-                                                            int* __restrict__ deg, float* __restrict__ coef,
-                                                            long long n_windows) {
+                                                                   const int* __restrict__ node_off,
+                                                                   const long long* __restrict__ edge_off,
+                                                                   int* __restrict__ deg, float* __restrict__ coef,
+                                                                   long long n_windows) {
+  __shared__ int mult_s[8][kCoefDenseMax * kCoefDenseMax];  // per warp: edge multiplicity M[row][col]
   const long long w = (static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
+  const int lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   if (w >= n_windows) return;
   const int n0 = node_off[w], nn = node_off[w + 1] - n0;
   const long long e0 = edge_off[w], ne = edge_off[w + 1] - e0;
+  const float inv_n = nn > 0 ? 1.f / static_cast<float>(nn) : 0.f;
+  if (nn <= kCoefDenseMax) {
+    // Small graph (the CML case, N_b <= 23): count edges into a dense N x N table with integer
+    // shared-memory atomics (order-independent), then lane j sums column j in row order, so the
+    // result is bit-reproducible whatever order the edge list is in.
+    int* M = mult_s[wib];
+    for (int i = lane; i < nn * nn; i += 32) M[i] = 0;
+    __syncwarp();
+    for (long long e = lane; e < ne; e += 32) {
+      const longlong2 rc = *reinterpret_cast<const longlong2*>(edges + 2 * (e0 + e));
+      if (rc.x >= 0 && rc.x < nn && rc.y >= 0 && rc.y < nn) atomicAdd(&M[static_cast<int>(rc.x) * nn + static_cast<int>(rc.y)], 1);
+    }
+    __syncwarp();
+    // deg_i = row sum; every lane needs all of them: lane i computes deg_i, shuffle to share.
+    int my_deg = 0;
+    if (lane < nn)
+      for (int j = 0; j < nn; ++j) my_deg += M[lane * nn + j];
+    float s = 0.f;
+    for (int i = 0; i < nn; ++i) {
+      const int d = __shfl_sync(0xffffffffu, my_deg, i);
+      if (lane < nn && d > 0) {
+        const int m = M[i * nn + lane];
+        if (m) s += static_cast<float>(m) / static_cast<float>(d);
+      }
+    }
+    if (lane < nn) coef[n0 + lane] = s * inv_n;
+    return;
+  }
+  // General path (any graph size): degree counts in global scratch `deg` (zero on entry).
   for (long long e = lane; e < ne; e += 32) {
     const long long row = edges[2 * (e0 + e)];
     if (row >= 0 && row < nn) atomicAdd(&deg[n0 + row], 1);
   }
   __syncwarp();
   __threadfence_block();
-  const float inv_n = nn > 0 ? 1.f / static_cast<float>(nn) : 0.f;
   for (int j = lane; j < nn; j += 32) {
     float s = 0.f;
     for (long long e = 0; e < ne; ++e) {
@@ -79,7 +110,7 @@ struct GcnFolded {
 static __global__ void __launch_bounds__(256) cml_frontend_kernel(const float2* __restrict__ feat, const float2* __restrict__ anom,
                                                            const float* __restrict__ coef, const int* __restrict__ node_off,
                                                            const GcnFolded p, float* __restrict__ out,
-                                                           long long n_windows, int T, int t_run) {
+                                                           long long n_windows, int T, int t_run, float alpha = 1.f) {
   const int b = threadIdx.x & 63, tq = threadIdx.x >> 6;
   const long long tile = blockIdx.x;
   const long long win = tile * kTile + b;
@@ -97,7 +128,8 @@ static __global__ void __launch_bounds__(256) cml_frontend_kernel(const float2* 
     for (int c = 0; c < kGcnChannelsDev; ++c) acc[c] = 0.f;
     const float2* row = feat + (static_cast<long long>(n0) * T + static_cast<long long>(t) * nn);
     for (int n = 0; n < nn; ++n) {
-      const float2 v = __ldg(row + n);
+      float2 v = __ldg(row + n);
+      v.x *= alpha; v.y *= alpha;   // integrated-gradients path scaling; exact no-op for alpha == 1
       const float cf = __ldg(coef + n0 + n);
 #pragma unroll
       for (int c = 0; c < kGcnChannelsDev; ++c) {
@@ -108,8 +140,8 @@ static __global__ void __launch_bounds__(256) cml_frontend_kernel(const float2* 
     }
     const float2 av = live ? __ldg(anom + win * T + t) : make_float2(0.f, 0.f);
     float* o = out + ((tile * t_run + t) * CH) * kTile + b;
-    o[0] = av.x;
-    o[kTile] = av.y;
+    o[0] = av.x * alpha;
+    o[kTile] = av.y * alpha;
 #pragma unroll
     for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc[c];
   }
@@ -154,6 +186,142 @@ __global__ void __launch_bounds__(256) head_kernel(const float* __restrict__ y7,
     for (int k = 0; k < D; ++k) z = fmaf(d2_s[k * kTile + b], __ldg(wo + k), z);
     const long long seq = tile * kTile + b;
     if (seq < n_seq) scores[seq] = 1.f / (1.f + expf(-z));
+  }
+}
+
+// ---- integrated gradients: backward through the CML front-end ---------------------------------
+// One interpolation step of xai/libs/integrated_gradients.py:955-1012 for the graph half of the
+// model: given dx1 = d(sum_b p_b)/d(x1 tile) at the input alpha*x, accumulates
+//   attr_feat[row][f] (+)= wk * x[row][f] * coef_n * sum_c dx1[2+c] * prelu'(z_c) * a[f][c]
+//   attr_anom[b][t][c] (+)= wk * anom[b][t][c] * dx1[c]
+// where wk is the trapezoid weight of this alpha (1/m, or 1/(2m) at the two ends; :1006-1012)
+// and the factor x is the "(x - baseline) * IG" scaling (:1185-1191, zero baseline).
+// `first` assigns instead of accumulating.  Steps t >= t_run cannot influence the score: their
+// attribution is exactly 0 and is written as such.
+static __global__ void __launch_bounds__(256) cml_frontend_bwd_kernel(const float2* __restrict__ feat, const float2* __restrict__ anom,
+                                                                      const float* __restrict__ coef, const int* __restrict__ node_off,
+                                                                      const GcnFolded p, const float* __restrict__ dx1,
+                                                                      float2* __restrict__ attr_feat, float2* __restrict__ attr_anom,
+                                                                      long long n_windows, int T, int t_run, float alpha, float wk,
+                                                                      int first) {
+  const int b = threadIdx.x & 63, tq = threadIdx.x >> 6;
+  const long long tile = blockIdx.x;
+  const long long win = tile * kTile + b;
+  const int t0 = blockIdx.y * 32 + tq * 8;
+  if (win >= n_windows) return;
+  const int n0 = node_off[win];
+  const int nn = node_off[win + 1] - n0;
+  constexpr int CH = 2 + kGcnChannelsDev;
+#pragma unroll 1
+  for (int dt = 0; dt < 8; ++dt) {
+    const int t = t0 + dt;
+    if (t >= T) break;
+    const long long row0 = static_cast<long long>(n0) * T + static_cast<long long>(t) * nn;
+    if (t >= t_run) {
+      if (first) {
+        for (int n = 0; n < nn; ++n) attr_feat[row0 + n] = make_float2(0.f, 0.f);
+        attr_anom[win * T + t] = make_float2(0.f, 0.f);
+      }
+      continue;
+    }
+    const float* g = dx1 + ((tile * t_run + t) * CH) * kTile + b;
+    float dp[kGcnChannelsDev];
+#pragma unroll
+    for (int c = 0; c < kGcnChannelsDev; ++c) dp[c] = g[(2 + c) * kTile];
+    for (int n = 0; n < nn; ++n) {
+      const float2 v = __ldg(feat + row0 + n);
+      const float cf = __ldg(coef + n0 + n);
+      float gx = 0.f, gy = 0.f;
+#pragma unroll
+      for (int c = 0; c < kGcnChannelsDev; ++c) {
+        const float z = fmaf(alpha * v.x, p.a[0][c], fmaf(alpha * v.y, p.a[1][c], p.c[c]));
+        const float s = dp[c] * (z > 0.f ? 1.f : p.alpha[c]);
+        gx = fmaf(s, p.a[0][c], gx);
+        gy = fmaf(s, p.a[1][c], gy);
+      }
+      float2 a = first ? make_float2(0.f, 0.f) : attr_feat[row0 + n];
+      a.x = fmaf(wk * v.x * cf, gx, a.x);
+      a.y = fmaf(wk * v.y * cf, gy, a.y);
+      attr_feat[row0 + n] = a;
+    }
+    const float2 av = __ldg(anom + win * T + t);
+    float2 a = first ? make_float2(0.f, 0.f) : attr_anom[win * T + t];
+    a.x = fmaf(wk * av.x, g[0], a.x);
+    a.y = fmaf(wk * av.y, g[kTile], a.y);
+    attr_anom[win * T + t] = a;
+  }
+}
+
+// ---- head forward + gradient of the score w.r.t. the last LSTM state ------------------------------
+// dy7[k] = d p / d h7[k] through Dense-LeakyReLU-Dense-LeakyReLU-Dense(sigmoid)
+// (libs/create_model.py:235-239).  Writes the scores too when `scores` is not null.
+template <int HL, int D>
+__global__ void __launch_bounds__(256) head_grad_kernel(const float* __restrict__ y7, const float* __restrict__ w1,
+                                                        const float* __restrict__ b1, const float* __restrict__ w2,
+                                                        const float* __restrict__ b2, const float* __restrict__ wo,
+                                                        const float* __restrict__ bo, float leaky, float* __restrict__ dy7,
+                                                        float* __restrict__ scores, long long n_seq) {
+  __shared__ float d1_s[D * kTile];   // post-activation dense 1, later its gradient
+  __shared__ float d2_s[D * kTile];   // post-activation dense 2, later its gradient
+  __shared__ float m1_s[D * kTile];   // LeakyReLU slopes of dense 1
+  const long long tile = blockIdx.x;
+  const int b = threadIdx.x & 63, q = threadIdx.x >> 6;
+  constexpr int DQ = D / 4;
+  float acc[DQ];
+#pragma unroll
+  for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b1 + q * DQ + o);
+  for (int k = 0; k < HL; ++k) {
+    const float h = __ldg(y7 + (tile * HL + k) * kTile + b);
+#pragma unroll
+    for (int o = 0; o < DQ; ++o) acc[o] = fmaf(h, __ldg(w1 + k * D + q * DQ + o), acc[o]);
+  }
+#pragma unroll
+  for (int o = 0; o < DQ; ++o) {
+    d1_s[(q * DQ + o) * kTile + b] = acc[o] > 0.f ? acc[o] : leaky * acc[o];
+    m1_s[(q * DQ + o) * kTile + b] = acc[o] > 0.f ? 1.f : leaky;
+  }
+  __syncthreads();
+#pragma unroll
+  for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b2 + q * DQ + o);
+  for (int k = 0; k < D; ++k) {
+    const float h = d1_s[k * kTile + b];
+#pragma unroll
+    for (int o = 0; o < DQ; ++o) acc[o] = fmaf(h, __ldg(w2 + k * D + q * DQ + o), acc[o]);
+  }
+  float m2[DQ];
+#pragma unroll
+  for (int o = 0; o < DQ; ++o) {
+    d2_s[(q * DQ + o) * kTile + b] = acc[o] > 0.f ? acc[o] : leaky * acc[o];
+    m2[o] = acc[o] > 0.f ? 1.f : leaky;
+  }
+  __syncthreads();
+  float z = __ldg(bo);
+  for (int k = 0; k < D; ++k) z = fmaf(d2_s[k * kTile + b], __ldg(wo + k), z);
+  const float pr = 1.f / (1.f + expf(-z));
+  const long long seq = tile * kTile + b;
+  if (q == 0 && scores != nullptr && seq < n_seq) scores[seq] = pr;
+  const float dz3 = pr * (1.f - pr);
+  __syncthreads();   // all reads of d2_s done
+#pragma unroll
+  for (int o = 0; o < DQ; ++o) d2_s[(q * DQ + o) * kTile + b] = dz3 * __ldg(wo + q * DQ + o) * m2[o];   // grad at dense-2 pre-activation
+  __syncthreads();
+  // grad at dense-1 pre-activation: sum_o dd2[o] * w2[k][o] * slope1[k]
+#pragma unroll
+  for (int kk = 0; kk < DQ; ++kk) {
+    const int k = q * DQ + kk;
+    float s = 0.f;
+    for (int o = 0; o < D; ++o) s = fmaf(d2_s[o * kTile + b], __ldg(w2 + k * D + o), s);
+    acc[kk] = s * m1_s[k * kTile + b];
+  }
+  __syncthreads();   // all reads of d1_s (none pending) - reuse it for the dense-1 gradients
+#pragma unroll
+  for (int kk = 0; kk < DQ; ++kk) d1_s[(q * DQ + kk) * kTile + b] = acc[kk];
+  __syncthreads();
+  for (int kk = 0; kk < HL / 4; ++kk) {
+    const int k = q * (HL / 4) + kk;
+    float s = 0.f;
+    for (int o = 0; o < D; ++o) s = fmaf(d1_s[o * kTile + b], __ldg(w1 + k * D + o), s);
+    dy7[(tile * HL + k) * kTile + b] = s;
   }
 }
 

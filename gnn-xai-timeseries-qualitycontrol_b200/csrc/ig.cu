@@ -1,0 +1,250 @@
+// Integrated gradients for the CML GCN model on the GPU (gnnqc_ig_cml).
+//
+// Restates xai/libs/integrated_gradients.py (reference):
+//   :898-917   zero baseline
+//   :919-942   alphas = linspace(0, 1, m_steps+1); both inputs interpolated with the same alpha
+//   :955-1004  per alpha: forward of the whole batch, gradient of the (summed) prediction w.r.t.
+//              the interpolated node features and target series
+//   :1006-1012 trapezoid: mean over k of (g_k + g_{k+1})/2
+//   :1185-1191 scale by (x - baseline)
+//   :1229      prediction of the un-interpolated batch
+// Per alpha the device runs: front-end (inputs scaled by alpha) -> 7 x LSTM forward with saved
+// gates -> head forward+gradient -> 7 x LSTM input-gradient backward -> front-end backward, which
+// accumulates w_k * x * grad straight into the caller's attribution buffers, so nothing but the
+// inputs is read from and nothing but the attributions is written to caller memory.
+#include <algorithm>
+#include <cstdlib>
+#include <cstring>
+#include <cmath>
+
+#include "device_model.cuh"
+#include "frontend.cuh"
+#include "lstm_bwd.cuh"
+#include "lstm_fwd.cuh"
+
+namespace gnnqc {
+namespace {
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+size_t ig_scratch_budget_bytes() {
+  const char* env = std::getenv("GNNQC_IG_SCRATCH_MB");
+  size_t mb = env ? std::strtoull(env, nullptr, 10) : 24576;
+  return std::max<size_t>(mb, 64) << 20;
+}
+
+// Forward with SAVE: packed FFMA2 accumulation, plain cell (the gates are needed individually).
+template <int I, int H, bool POOL, bool LAST>
+struct FwdSave {
+  static constexpr bool WGLOBAL = (size_t(I + H) * H * 16 > 160 * 1024);
+  static constexpr int RJ = 2, RB = 8, LJ = 8, NST = 2, VAR = kVarPacked;
+  using Cfg = LstmCfg<I, H, RJ, RB, LJ, WGLOBAL, NST>;
+  static auto kernel() { return lstm_layer_kernel<I, H, RJ, RB, LJ, POOL, LAST, WGLOBAL, VAR, NST, true>; }
+  static void configure() {
+    GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+  }
+  static void launch(const float* x, float* y, const float* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count,
+                     float* save, float* amax, cudaStream_t st) {
+    int per_sm = 1;
+    GNNQC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel(), Cfg::NT, Cfg::SMEM_BYTES));
+    if (per_sm < 1) throw CudaError("lstm_layer_kernel<SAVE> does not fit on an SM");
+    long long grid = std::min<long long>(n_tiles, static_cast<long long>(sm_count) * per_sm);
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax);
+    GNNQC_CUDA(cudaGetLastError());
+  }
+};
+
+template <int I, int H, bool POOL, bool LAST>
+struct Bwd {
+  static constexpr bool WGLOBAL = (size_t(4 * H) * ((I + H + 15) / 16 * 16) * 4 > 150 * 1024);
+  using Cfg = BwdCfg<I, H, WGLOBAL>;
+  static auto kernel() { return lstm_layer_bwd_kernel<I, H, POOL, LAST, WGLOBAL>; }
+  static void configure() {
+    GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+  }
+  static void launch(const float* dy, const float* save, const float* amax, const float* wT, float* dx, int T, long long n_tiles,
+                     int sm_count, cudaStream_t st) {
+    int per_sm = 1;
+    GNNQC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel(), Cfg::NT, Cfg::SMEM_BYTES));
+    if (per_sm < 1) throw CudaError("lstm_layer_bwd_kernel does not fit on an SM");
+    long long grid = std::min<long long>(n_tiles, static_cast<long long>(sm_count) * per_sm);
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wT, dx, T, static_cast<int>(n_tiles));
+    GNNQC_CUDA(cudaGetLastError());
+  }
+};
+
+enum class Op { Configure, Forward, Backward };
+
+struct LayerArgs {
+  const float* in = nullptr;   // forward: x tile; backward: dy
+  float* out = nullptr;        // forward: y tile; backward: dx
+  const float* w = nullptr;    // forward: packed; backward: transposed
+  float* save = nullptr;
+  float* amax = nullptr;
+  int T = 0, t_in = 0, t_out = 0;
+  long long n_tiles = 0;
+  int sm_count = 0;
+  cudaStream_t st = nullptr;
+};
+
+template <int I, int H, bool POOL, bool LAST>
+void layer_op(Op op, const LayerArgs& a) {
+  if (op == Op::Configure) {
+    FwdSave<I, H, POOL, LAST>::configure();
+    Bwd<I, H, POOL, LAST>::configure();
+  } else if (op == Op::Forward) {
+    FwdSave<I, H, POOL, LAST>::launch(a.in, a.out, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.save, a.amax, a.st);
+  } else {
+    Bwd<I, H, POOL, LAST>::launch(a.in, a.save, a.amax, a.w, a.out, a.T, a.n_tiles, a.sm_count, a.st);
+  }
+}
+
+void dispatch(Op op, int in, int hid, bool pool, bool last, const LayerArgs& a) {
+#define GNNQC_CASE(I_, H_, POOL_, LAST_) \
+  if (in == I_ && hid == H_ && pool == POOL_ && last == LAST_) return layer_op<I_, H_, POOL_, LAST_>(op, a);
+  GNNQC_CASE(18, 16, false, false)
+  GNNQC_CASE(16, 16, true, false)
+  GNNQC_CASE(16, 32, false, false)
+  GNNQC_CASE(32, 32, true, false)
+  GNNQC_CASE(32, 64, false, false)
+  GNNQC_CASE(64, 64, true, false)
+  GNNQC_CASE(64, 128, false, true)
+#undef GNNQC_CASE
+  throw std::invalid_argument("integrated gradients: no kernel for this LSTM layer shape");
+}
+
+GcnFolded fold_gcn_params(const HostModel& m) {
+  const ModelSpec& s = m.spec;
+  const float* p = m.params.data();
+  GcnFolded f;
+  std::memset(&f, 0, sizeof(f));
+  for (int c = 0; c < kGcnChannels; ++c) {
+    const float scale = p[s.off_bn_gamma + c] / std::sqrt(p[s.off_bn_var + c] + s.bn_eps);
+    for (int k = 0; k < s.n_features; ++k) f.a[k][c] = p[s.off_gcn_kernel + k * kGcnChannels + c] * scale;
+    f.c[c] = (p[s.off_gcn_bias + c] - p[s.off_bn_mean + c]) * scale + p[s.off_bn_beta + c];
+    f.alpha[c] = p[s.off_prelu + c];
+  }
+  return f;
+}
+
+}  // namespace
+
+void DeviceModel::configure_ig_kernels() {
+  const ModelSpec& s = host.spec;
+  if (!s.has_gcn || s.soilnet) return;
+  LayerArgs none;
+  for (int l = 0; l < s.n_lstm; ++l) {
+    const bool last = (l == s.n_lstm - 1);
+    dispatch(Op::Configure, s.lstm_in[l], s.lstm_hid[l], !last && (l % 2 == 1), last, none);
+  }
+}
+
+void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
+                         const long long* edge_off, long long B, int T, long long n_nodes, int m_steps, float* attr_feat,
+                         float* attr_anom, float* scores, cudaStream_t st) {
+  if (B <= 0) return;
+  const ModelSpec& s = host.spec;
+  GNNQC_CUDA(cudaSetDevice(device));
+  StackPlan plan(s, T);
+  const int L = s.n_lstm;
+  const long long n_tiles = (B + kTile - 1) / kTile;
+
+  // Per-tile scratch: forward ping/pong, gradient ping/pong, dy7, saved gates and pool argmax.
+  const size_t sa = align_up(plan.bytes_a, 256), sb = align_up(plan.bytes_b, 256);
+  size_t sg = 0;
+  for (int l = 0; l < L; ++l) sg = std::max(sg, size_t(plan.t_run[l]) * s.lstm_in[l] * kTile * sizeof(float));
+  sg = align_up(sg, 256);
+  size_t save_off[kMaxLstmLayers], amax_off[kMaxLstmLayers], per_tile_save = 0;
+  for (int l = 0; l < L; ++l) {
+    save_off[l] = per_tile_save;
+    per_tile_save += size_t(plan.t_run[l]) * s.lstm_hid[l] * 5 * kTile * sizeof(float);
+    amax_off[l] = per_tile_save;
+    if (l % 2 == 1 && l != L - 1) per_tile_save += size_t(plan.t_out[l]) * s.lstm_hid[l] * kTile * sizeof(float);
+  }
+  const size_t s7 = size_t(s.lstm_hid[L - 1]) * kTile * sizeof(float);
+  const size_t per_tile = sa + sb + 2 * sg + s7 + per_tile_save;
+  const size_t coef_bytes = align_up(size_t(n_nodes) * sizeof(float), 256);
+  const long long chunk = std::max<long long>(1, std::min<long long>(n_tiles, static_cast<long long>(ig_scratch_budget_bytes() / per_tile)));
+  char* base = static_cast<char*>(scratch(2 * coef_bytes + size_t(chunk) * per_tile));
+  int* deg = reinterpret_cast<int*>(base);
+  float* coef = reinterpret_cast<float*>(base + coef_bytes);
+  char* p = base + 2 * coef_bytes;
+  float* buf_a = reinterpret_cast<float*>(p); p += size_t(chunk) * sa;
+  float* buf_b = reinterpret_cast<float*>(p); p += size_t(chunk) * sb;
+  float* g0 = reinterpret_cast<float*>(p); p += size_t(chunk) * sg;
+  float* g1 = reinterpret_cast<float*>(p); p += size_t(chunk) * sg;
+  float* dy7 = reinterpret_cast<float*>(p); p += size_t(chunk) * s7;
+  char* saves = p;   // layer l of the chunk: saves + chunk*save_off[l] (layer-major, then tile)
+
+  GNNQC_CUDA(cudaMemsetAsync(deg, 0, size_t(n_nodes) * sizeof(int), st));
+  mark_begin("cml_node_coef", st);
+  cml_node_coef_kernel<<<static_cast<unsigned>((B * 32 + 255) / 256), 256, 0, st>>>(edges, node_off, edge_off, deg, coef, B);
+  GNNQC_CUDA(cudaGetLastError());
+  mark_end(st);
+
+  const GcnFolded folded = fold_gcn_params(host);
+  const float* prm = d_params;
+  static const char* const kFwd[kMaxLstmLayers] = {"ig_fwd_l1", "ig_fwd_l2", "ig_fwd_l3", "ig_fwd_l4", "ig_fwd_l5", "ig_fwd_l6", "ig_fwd_l7"};
+  static const char* const kBwd[kMaxLstmLayers] = {"ig_bwd_l1", "ig_bwd_l2", "ig_bwd_l3", "ig_bwd_l4", "ig_bwd_l5", "ig_bwd_l6", "ig_bwd_l7"};
+
+  for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
+    const long long nt = std::min(chunk, n_tiles - t0);
+    const long long win0 = t0 * kTile, nw = std::min<long long>(B - win0, nt * kTile);
+    const dim3 grid_fe(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
+    const dim3 grid_fb(static_cast<unsigned>(nt), static_cast<unsigned>((T + 31) / 32));
+    const float2* feat2 = reinterpret_cast<const float2*>(feat);
+    const float2* anom2 = reinterpret_cast<const float2*>(anom) + win0 * T;
+    for (int k = 0; k <= m_steps; ++k) {
+      const float alpha = static_cast<float>(k) / static_cast<float>(m_steps);
+      const float wk = ((k == 0 || k == m_steps) ? 0.5f : 1.0f) / static_cast<float>(m_steps);
+      mark_begin("ig_frontend", st);
+      cml_frontend_kernel<<<grid_fe, 256, 0, st>>>(feat2, anom2, coef, node_off + win0, folded, buf_a, nw, T, plan.t_run[0], alpha);
+      GNNQC_CUDA(cudaGetLastError());
+      mark_end(st);
+      // forward, saving gates
+      const float* in = buf_a;
+      int t_in = plan.t_run[0];
+      for (int l = 0; l < L; ++l) {
+        const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
+        LayerArgs a;
+        a.in = in; a.out = (l % 2 == 0) ? buf_b : buf_a; a.w = d_packed + packed_off[l];
+        a.save = reinterpret_cast<float*>(saves + size_t(chunk) * save_off[l]);
+        a.amax = pool ? reinterpret_cast<float*>(saves + size_t(chunk) * amax_off[l]) : nullptr;
+        a.T = plan.t_run[l]; a.t_in = t_in; a.t_out = plan.t_out[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
+        mark_begin(kFwd[l], st);
+        dispatch(Op::Forward, s.lstm_in[l], s.lstm_hid[l], pool, last, a);
+        mark_end(st);
+        in = a.out;
+        t_in = plan.t_out[l];
+      }
+      mark_begin("ig_head", st);
+      head_grad_kernel<128, 64><<<static_cast<unsigned>(nt), 256, 0, st>>>(in, prm + s.off_d1_w, prm + s.off_d1_b, prm + s.off_d2_w,
+                                                                            prm + s.off_d2_b, prm + s.off_out_w, prm + s.off_out_b,
+                                                                            s.leaky_alpha, dy7, (k == m_steps) ? scores + win0 : nullptr, nw);
+      GNNQC_CUDA(cudaGetLastError());
+      mark_end(st);
+      // backward
+      const float* dy = dy7;
+      for (int l = L - 1; l >= 0; --l) {
+        const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
+        LayerArgs a;
+        a.in = dy; a.out = (l % 2 == 0) ? g0 : g1; a.w = d_packed_t + packed_t_off[l];
+        a.save = reinterpret_cast<float*>(saves + size_t(chunk) * save_off[l]);
+        a.amax = pool ? reinterpret_cast<float*>(saves + size_t(chunk) * amax_off[l]) : nullptr;
+        a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
+        mark_begin(kBwd[l], st);
+        dispatch(Op::Backward, s.lstm_in[l], s.lstm_hid[l], pool, last, a);
+        mark_end(st);
+        dy = a.out;
+      }
+      mark_begin("ig_frontend_bwd", st);
+      cml_frontend_bwd_kernel<<<grid_fb, 256, 0, st>>>(feat2, anom2, coef, node_off + win0, folded, dy,
+                                                       reinterpret_cast<float2*>(attr_feat), reinterpret_cast<float2*>(attr_anom) + win0 * T,
+                                                       nw, T, plan.t_run[0], alpha, wk, k == 0 ? 1 : 0);
+      GNNQC_CUDA(cudaGetLastError());
+      mark_end(st);
+    }
+  }
+}
+
+}  // namespace gnnqc

@@ -93,15 +93,20 @@ struct LstmCfg {
   static_assert(XBYTES % 16 == 0, "bulk copies need 16-byte multiples");
 };
 
-template <int I, int H, int RJ, int RB, int LJ, bool POOL, bool LAST, bool WGLOBAL, int VAR = 0, int NST_ = 0>
+// SAVE (used by the attribution / training paths): additionally stores, per step and cell, the
+// gate activations i, f, g, o and the cell state c as save[tile][t][unit][5][64], and for pooled
+// layers which of the three pooled steps held the maximum (amax[tile][t/3][unit][64], first
+// maximum wins like TF's MaxPoolGrad).
+template <int I, int H, int RJ, int RB, int LJ, bool POOL, bool LAST, bool WGLOBAL, int VAR = 0, int NST_ = 0, bool SAVE = false>
 __global__ void __launch_bounds__((LstmCfg<I, H, RJ, RB, LJ, WGLOBAL, NST_>::NT))
 lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][64]
                   float* __restrict__ yout,        // [n_tiles][t_out_stride][H][64], LAST: [n_tiles][H][64]
                   const float* __restrict__ wpk,   // packed weights + bias
-                  int T, int t_in_stride, int t_out_stride, int n_tiles) {
+                  int T, int t_in_stride, int t_out_stride, int n_tiles,
+                  float* __restrict__ save = nullptr, float* __restrict__ amax = nullptr) {
   using C = LstmCfg<I, H, RJ, RB, LJ, WGLOBAL, NST_>;
   constexpr bool PACKED = (VAR & kVarPacked) != 0;
-  constexpr bool FUSED = (VAR & kVarFusedCell) != 0;
+  constexpr bool FUSED = (VAR & kVarFusedCell) != 0 && !SAVE;
   constexpr bool PIPE = (VAR & kVarPipelined) != 0;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* wsm = reinterpret_cast<float*>(smem_raw);
@@ -152,6 +157,7 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
 
   float cst[RJ][RB];
   float pmax[RJ][RB];
+  float pidx[SAVE ? RJ : 1][SAVE ? RB : 1];
   int n = 0, t = 0;
   for (long long q = 0; q < total; ++q) {
     const long long tile = static_cast<long long>(blockIdx.x) + static_cast<long long>(n) * gridDim.x;
@@ -274,22 +280,36 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
     for (int r = 0; r < RJ; ++r) {
       const int unit = unit0 + r * LJ;
       float hv[RB];
+      float sv[SAVE ? 5 : 1][SAVE ? RB : 1];
 #pragma unroll
       for (int i = 0; i < RB; ++i) {
         float zi, zf, zg, zo;
         if (PACKED) {
-          if (i & 1) continue;
-          float zi1, zf1, zg1, zo1;
-          unpack2(acc2[r][0][i / 2], zi, zi1);
-          unpack2(acc2[r][1][i / 2], zf, zf1);
-          unpack2(acc2[r][2][i / 2], zg, zg1);
-          unpack2(acc2[r][3][i / 2], zo, zo1);
-          hv[i] = FUSED ? lstm_cell_fused(zi, zf, zg, zo, cst[r][i]) : lstm_cell_plain(zi, zf, zg, zo, cst[r][i]);
-          hv[i + 1] = FUSED ? lstm_cell_fused(zi1, zf1, zg1, zo1, cst[r][i + 1]) : lstm_cell_plain(zi1, zf1, zg1, zo1, cst[r][i + 1]);
+          float lo, hi;
+          unpack2(acc2[r][0][i / 2], lo, hi); zi = (i & 1) ? hi : lo;
+          unpack2(acc2[r][1][i / 2], lo, hi); zf = (i & 1) ? hi : lo;
+          unpack2(acc2[r][2][i / 2], lo, hi); zg = (i & 1) ? hi : lo;
+          unpack2(acc2[r][3][i / 2], lo, hi); zo = (i & 1) ? hi : lo;
         } else {
           zi = acc[r][0][i]; zf = acc[r][1][i]; zg = acc[r][2][i]; zo = acc[r][3][i];
+        }
+        if (SAVE) {
+          const float ig = sigmoid_fast(zi), fg = sigmoid_fast(zf), gg = tanh_fast(zg), og = sigmoid_fast(zo);
+          const float cn = fmaf(fg, cst[r][i], ig * gg);
+          cst[r][i] = cn;
+          hv[i] = og * tanh_fast(cn);
+          sv[0][i] = ig; sv[1][i] = fg; sv[2][i] = gg; sv[3][i] = og; sv[4][i] = cn;
+        } else {
           hv[i] = FUSED ? lstm_cell_fused(zi, zf, zg, zo, cst[r][i]) : lstm_cell_plain(zi, zf, zg, zo, cst[r][i]);
         }
+      }
+      if (SAVE) {
+        float4* so = reinterpret_cast<float4*>(save + (((tile * T + t) * H + unit) * 5) * kTile);
+#pragma unroll
+        for (int v = 0; v < 5; ++v)
+#pragma unroll
+          for (int qq = 0; qq < C::NQ; ++qq)
+            so[v * (kTile / 4) + b4 + qq * C::LB] = make_float4(sv[v][4 * qq], sv[v][4 * qq + 1], sv[v][4 * qq + 2], sv[v][4 * qq + 3]);
       }
 #pragma unroll
       for (int qq = 0; qq < C::NQ; ++qq)
@@ -297,8 +317,20 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
       if (POOL) {
         const int ph = t % 3;
 #pragma unroll
-        for (int i = 0; i < RB; ++i) pmax[r][i] = (ph == 0) ? hv[i] : fmaxf(pmax[r][i], hv[i]);
+        for (int i = 0; i < RB; ++i) {
+          if (SAVE) {
+            if (ph == 0) pidx[r][i] = 0.f;
+            else if (hv[i] > pmax[r][i]) pidx[r][i] = static_cast<float>(ph);
+          }
+          pmax[r][i] = (ph == 0) ? hv[i] : fmaxf(pmax[r][i], hv[i]);
+        }
         if (ph == 2) {
+          if (SAVE) {
+            float4* ao = reinterpret_cast<float4*>(amax + ((tile * t_out_stride + t / 3) * H + unit) * kTile);
+#pragma unroll
+            for (int qq = 0; qq < C::NQ; ++qq)
+              ao[b4 + qq * C::LB] = make_float4(pidx[r][4 * qq], pidx[r][4 * qq + 1], pidx[r][4 * qq + 2], pidx[r][4 * qq + 3]);
+          }
           float4* yo = reinterpret_cast<float4*>(yout + ((tile * t_out_stride + t / 3) * H + unit) * kTile);
 #pragma unroll
           for (int qq = 0; qq < C::NQ; ++qq)

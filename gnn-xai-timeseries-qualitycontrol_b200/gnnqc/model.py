@@ -169,6 +169,28 @@ class NativeModel:
                                   edge_off.data_ptr(), B, T, n_nodes_total, out.data_ptr(), self._stream()))
         return out
 
+    def ig_cml(self, features, anom, edges, node_off, edge_off, m_steps=50, n_nodes_total=None):
+        """Integrated gradients (zero baseline, trapezoid, scaled by the input) for the CML GCN
+        model.  Returns (attr_features [Ntot,2], attr_anom [B,T,2], scores [B]) as CUDA tensors."""
+        torch = _torch()
+        features = self._dev_tensor(features, torch.float32, "features")
+        anom = self._dev_tensor(anom, torch.float32, "anom")
+        edges = self._dev_tensor(edges, torch.int64, "edges")
+        node_off = self._dev_tensor(node_off, torch.int32, "node_off")
+        edge_off = self._dev_tensor(edge_off, torch.int64, "edge_off")
+        B, T = anom.shape[0], anom.shape[1]
+        if n_nodes_total is None:
+            n_nodes_total = int(node_off[-1].item())
+        if features.shape[0] != n_nodes_total * T:
+            raise ValueError("features has %d rows, expected sum(N_b)*T = %d" % (features.shape[0], n_nodes_total * T))
+        attr_f = torch.empty_like(features)
+        attr_a = torch.empty_like(anom)
+        scores = torch.empty(B, dtype=torch.float32, device=anom.device)
+        check(lib.gnnqc_ig_cml(self._h, features.data_ptr(), anom.data_ptr(), edges.data_ptr(), node_off.data_ptr(),
+                               edge_off.data_ptr(), B, T, n_nodes_total, int(m_steps), attr_f.data_ptr(), attr_a.data_ptr(),
+                               scores.data_ptr(), self._stream()))
+        return attr_f, attr_a, scores
+
     # ---- measurement ---------------------------------------------------------------------
     def launch_count(self):
         return int(lib.gnnqc_launch_count(self._h))

@@ -124,6 +124,25 @@ int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom
                     const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
                     float* scores_dev, void* stream);
 
+/* ---- attribution ---------------------------------------------------------------------- */
+
+/* Replaces IntegratedGradientsExplainer._get_gradients_single_batch for the CML GCN model
+ * (xai/libs/integrated_gradients.py:1133-1234: zero baseline :898-917, interpolation :919-942,
+ * per-alpha tape.gradient :955-1004, trapezoid :1006-1012, scaling by the input :1185-1191,
+ * final prediction :1229).  Inputs as gnnqc_score_cml.  m_steps interpolation intervals
+ * (reference default 100, xai_config_20240318.yml:12; BASELINE.json uses 50) = m_steps+1
+ * forward+backward passes.
+ *   attr_features_dev f32 [sum_b T*N_b, 2]  attribution of every node feature, same row order
+ *                                           as features_dev (the per-sample [N_b,T,2] unwrap of
+ *                                           :1017-1030 is a strided view of it)
+ *   attr_anom_dev     f32 [B, T, 2]         attribution of the target series input
+ *   scores_dev        f32 [B]               model output at alpha = 1
+ * negative_values handling (:1193-1207) is 'keep'; abs/clip are one elementwise op for the caller. */
+int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_dev,
+                 const int64_t* edges_dev, const int32_t* node_off_dev, const int64_t* edge_off_dev,
+                 int64_t B, int32_t T, int64_t n_nodes_total, int32_t m_steps,
+                 float* attr_features_dev, float* attr_anom_dev, float* scores_dev, void* stream);
+
 /* gnnqc_score_seq for callers that are not allowed to allocate.  It has no counterpart in the
  * reference.  Some users of this library cannot call cudaMalloc where they score: a
  * fixed-budget real-time loop, a process whose device memory is all owned by another

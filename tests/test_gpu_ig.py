@@ -1,0 +1,73 @@
+"""GPU parity of integrated gradients (gnnqc_ig_cml) against the CPU oracle (torch autograd through
+the literal model restatement).  Tolerance: attributions within 1e-4 absolute + 1e-3 relative of
+the float64 oracle (they are sums of ~50 gradient products of magnitude <= 1); scores 1e-4."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import gnnqc_oracle as O
+from conftest import MODELS
+from gnnqc import NativeModel, synth
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def model():
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    yield m
+    m.close()
+
+
+def run_gpu(model, batch, m_steps):
+    b = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+    af, aa, p = model.ig_cml(b["features"], b["anom"], b["edges"], b["node_off"], b["edge_off"], m_steps=m_steps)
+    return af.cpu().numpy(), aa.cpu().numpy(), p.cpu().numpy()
+
+
+def run_oracle(model, batch, m_steps):
+    feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 2)
+    w = O.to_torch_weights(model.named_params(), torch.float64)
+    af, aa, p = O.integrated_gradients_cml(torch.tensor(feat).double(), batch["anom"].double(), torch.tensor(idx), torch.tensor(samp), w, m_steps=m_steps)
+    return af.numpy(), aa.numpy(), p.numpy()
+
+
+def close(got, want, atol, rtol):
+    err = np.abs(got.astype(np.float64) - want)
+    bad = err > atol + rtol * np.abs(want)
+    assert not bad.any(), "max abs err %.3e (|want| there %.3e, max |want| %.3e), %d bad of %d" % (
+        err.max(), np.abs(want).flat[err.argmax()], np.abs(want).max(), bad.sum(), bad.size)
+
+
+@pytest.mark.parametrize("n,ragged,m_steps", [(3, False, 4), (70, True, 3)])
+def test_ig_matches_oracle(model, n, ragged, m_steps):
+    batch = synth.make_cml_batch(n, seed=500 + n, ragged=ragged, n_nodes=9)
+    gf, ga, gp = run_gpu(model, batch, m_steps)
+    of, oa, op = run_oracle(model, batch, m_steps)
+    close(gp, op, 1e-4, 1e-4)
+    close(ga, oa, 1e-4, 1e-3)
+    close(gf, of, 1e-4, 1e-3)
+
+
+def test_ig_completeness_and_dead_steps(model):
+    """Low-amplitude inputs: sum of attributions ~= f(x) - f(0); steps past 162 get exactly 0."""
+    batch = synth.make_cml_batch(64, seed=9, n_nodes=6)
+    batch["features"] = batch["features"] * 0.05
+    batch["anom"] = batch["anom"] * 0.05
+    gf, ga, gp = run_gpu(model, batch, 32)
+    zero = {k: (torch.zeros_like(v) if k in ("features", "anom") else v) for k, v in batch.items()}
+    b0 = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in zero.items()}
+    f0 = model.score_cml(b0["features"], b0["anom"], b0["edges"], b0["node_off"], b0["edge_off"]).cpu().numpy()
+    T, N = 181, 6
+    tot = gf.reshape(64, T, N, 2).sum(axis=(1, 2, 3)) + ga.sum(axis=(1, 2))
+    want = gp - f0
+    smooth = np.abs(want) < 1e-2   # windows with an injected jump need far more than 32 steps to converge
+    assert smooth.sum() > 32
+    assert np.all(np.abs(tot - want)[smooth] <= 2e-2 * np.abs(want)[smooth] + 1e-6), np.abs(tot - want)[smooth].max()
+    assert np.all(gf.reshape(64, T, N, 2)[:, 162:] == 0) and np.all(ga[:, 162:] == 0)
+    # scores returned by the IG call are the plain scores
+    b = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+    p = model.score_cml(b["features"], b["anom"], b["edges"], b["node_off"], b["edge_off"]).cpu().numpy()
+    np.testing.assert_allclose(gp, p, rtol=1e-5, atol=1e-6)

@@ -148,6 +148,12 @@ def test_isolated_node_and_duplicate_edges(models):
     close(score_cml(m, batch), oracle_cml(m.named_params(), batch))
 
 
+def test_large_graph_uses_general_coefficient_path(models):
+    """More than 32 nodes per window: the node-coefficient kernel's global-scratch path."""
+    batch = synth.make_cml_batch(5, seed=77, n_nodes=40)
+    close(score_cml(models["model_cml"], batch), oracle_cml(models["model_cml"].named_params(), batch))
+
+
 def test_roc_auc_matches_oracle_to_3_decimals(models):
     from sklearn.metrics import roc_auc_score
     batch = synth.make_cml_batch(400, seed=21, ragged=True)
