@@ -211,6 +211,23 @@ int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom
   });
 }
 
+int gnnqc_score_soilnet(gnnqc_model* m, const float* features_dev, const int64_t* edges_dev, const int32_t* node_off_dev,
+                        const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total, int64_t n_edges_total,
+                        float* scores_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_score_soilnet")) return rc;
+  if (!m->dm.host.spec.has_gcn || !m->dm.host.spec.soilnet) return fail(GNNQC_ERR_STATE, "gnnqc_score_soilnet: model is not a SoilNet GCNClassifier");
+  if (B < 0 || T <= 0 || n_nodes_total < 0 || n_edges_total < 0) return fail(GNNQC_ERR_ARG, "gnnqc_score_soilnet: bad B / T / totals");
+  if (n_nodes_total >= (int64_t(1) << 31) - 1 || n_edges_total >= (int64_t(1) << 31) - 1)
+    return fail(GNNQC_ERR_ARG, "gnnqc_score_soilnet: more than 2^31 nodes or edges in one call; split the batch");
+  if (B > 0 && (!features_dev || !edges_dev || !node_off_dev || !edge_off_dev || !scores_dev))
+    return fail(GNNQC_ERR_ARG, "gnnqc_score_soilnet: null buffer");
+  return guarded([&] {
+    m->dm.score_soilnet(features_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
+                        reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, n_edges_total, scores_dev,
+                        static_cast<cudaStream_t>(stream));
+  });
+}
+
 int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_dev, const int64_t* edges_dev,
                  const int32_t* node_off_dev, const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
                  int32_t m_steps, float* attr_features_dev, float* attr_anom_dev, float* scores_dev, void* stream) {

@@ -70,6 +70,9 @@ struct DeviceModel {
   void run_stack(const StackPlan& plan, float* buf_a, float* buf_b, long long n_tiles, long long n_seq,
                  float* scores, cudaStream_t stream);
   void score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t stream);
+  // SoilNet GCN (csrc/soilnet.cu): scores [n_nodes], one per (window, sensor).
+  void score_soilnet(const float* feat, const long long* edges, const int* node_off, const long long* edge_off, long long B,
+                     int T, long long n_nodes, long long n_edges, float* scores, cudaStream_t stream);
   // Integrated gradients for the CML GCN model (csrc/ig.cu).
   void configure_ig_kernels();
   void ig_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,

@@ -62,6 +62,7 @@ def _load():
         "gnnqc_score_seq": (C.c_int, [vp, vp, i64, i32, vp, vp]),
         "gnnqc_score_seq_noalloc": (C.c_int, [vp, vp, i64, i32, vp, vp]),
         "gnnqc_score_cml": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, vp, vp]),
+        "gnnqc_score_soilnet": (C.c_int, [vp, vp, vp, vp, vp, i64, i32, i64, i64, vp, vp]),
         "gnnqc_ig_cml": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, i32, vp, vp, vp, vp]),
         "gnnqc_score_scratch_bytes": (i64, [vp, i64, i32]),
         "gnnqc_launch_count": (i64, [vp]),

@@ -169,6 +169,23 @@ class NativeModel:
                                   edge_off.data_ptr(), B, T, n_nodes_total, out.data_ptr(), self._stream()))
         return out
 
+    def score_soilnet(self, features, edges, node_off, edge_off, T, n_nodes_total=None):
+        """SoilNet GCN: features cuda f32 [sum N_b*T, 3] -> scores cuda f32 [sum N_b]."""
+        torch = _torch()
+        features = self._dev_tensor(features, torch.float32, "features")
+        edges = self._dev_tensor(edges, torch.int64, "edges")
+        node_off = self._dev_tensor(node_off, torch.int32, "node_off")
+        edge_off = self._dev_tensor(edge_off, torch.int64, "edge_off")
+        B = node_off.numel() - 1
+        if n_nodes_total is None:
+            n_nodes_total = int(node_off[-1].item())
+        if features.dim() != 2 or features.shape[1] != 3 or features.shape[0] != n_nodes_total * T:
+            raise ValueError("features must be [sum(N_b)*T, 3]")
+        out = torch.empty(n_nodes_total, dtype=torch.float32, device=features.device)
+        check(lib.gnnqc_score_soilnet(self._h, features.data_ptr(), edges.data_ptr(), node_off.data_ptr(), edge_off.data_ptr(),
+                                      B, int(T), n_nodes_total, edges.shape[0], out.data_ptr(), self._stream()))
+        return out
+
     def ig_cml(self, features, anom, edges, node_off, edge_off, m_steps=50, n_nodes_total=None):
         """Integrated gradients (zero baseline, trapezoid, scaled by the input) for the CML GCN
         model.  Returns (attr_features [Ntot,2], attr_anom [B,T,2], scores [B]) as CUDA tensors."""

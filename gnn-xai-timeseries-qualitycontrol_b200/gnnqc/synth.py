@@ -97,6 +97,59 @@ def cml_batch_to_windows(batch):
     return out
 
 
+def make_soilnet_batch(n_windows, seed=44, n_nodes=210, ragged=False, T=337, device="cpu", min_nodes=20):
+    """SoilNet-shaped batch in the layout gnnqc_score_soilnet takes: features [sum N_b*T, 3] rows
+    (window, t, node), edges [sum E_b, 2] window-local (row = receiving node), node_off, edge_off.
+    Sensors sit in boxes of up to 6 depths; edges follow libs/preprocessing_functions.py:475-478:
+    (distance <= 20 m and same depth) or (same box and depth difference <= 0.1 m)."""
+    g = torch.Generator(device=device)
+    g.manual_seed(int(seed))
+    B, N = int(n_windows), int(n_nodes)
+    dev = torch.device(device)
+    if ragged:
+        counts = torch.randint(min(min_nodes, N), N + 1, (B,), generator=g, device=dev)
+    else:
+        counts = torch.full((B,), N, dtype=torch.int64, device=dev)
+    node_mask = torch.arange(N, device=dev)[None, :] < counts[:, None]
+    depths = torch.tensor([0.05, 0.1, 0.2, 0.3, 0.4, 0.5], device=dev)
+    idx = torch.arange(N, device=dev)
+    box, depth = idx // 6, depths[idx % 6]
+    n_box = (N + 5) // 6
+    box_xy = 120.0 * torch.rand((B, n_box, 2), generator=g, device=dev)
+    xy = box_xy[:, box]                                                 # [B,N,2]
+    dist = torch.cdist(xy, xy)
+    same_depth = (depth[:, None] == depth[None, :])[None]
+    same_box = (box[:, None] == box[None, :])[None]
+    near_depth = ((depth[:, None] - depth[None, :]).abs() <= 0.1 + 1e-6)[None]
+    adj = ((dist <= 20.0) & same_depth) | (same_box & near_depth)
+    adj = adj & node_mask[:, :, None] & node_mask[:, None, :]
+    bij = adj.nonzero()
+    edges = bij[:, 1:].contiguous()
+    edge_counts = torch.bincount(bij[:, 0], minlength=B)
+
+    t = torch.arange(T, device=dev, dtype=torch.float32)[None, :, None]
+    moist = 0.45 + 0.1 * torch.randn((B, 1, N), generator=g, device=dev) + _ar1(0.01 * torch.randn((B, T, N), generator=g, device=dev), 0.99)
+    temp = 0.5 + 0.1 * torch.sin(2 * math.pi * t / 96.0 + 6.28 * torch.rand((B, 1, 1), generator=g, device=dev)) \
+        + 0.01 * torch.randn((B, T, N), generator=g, device=dev)
+    batt = 0.8 - 0.2 * torch.rand((B, 1, N), generator=g, device=dev) * (t / T)
+    x = torch.stack([moist.clamp(0.1, 0.8), temp, batt.expand(B, T, N)], dim=-1)      # [B,T,N,3]
+    # a few sensors with a step anomaly in the moisture channel
+    anomalous = torch.rand((B, N), generator=g, device=dev) < 0.03
+    step = (t[:, :, 0] >= (T * 0.6)).float()[:, :, None] * 0.25
+    x[..., 0] = x[..., 0] + anomalous[:, None, :] * step
+    if ragged:
+        features = x[node_mask[:, None, :].expand(B, T, N)].reshape(-1, 3).contiguous()
+        labels = anomalous[node_mask]
+    else:
+        features = x.reshape(-1, 3)
+        labels = anomalous.reshape(-1)
+    node_off = torch.zeros(B + 1, dtype=torch.int32, device=dev)
+    node_off[1:] = torch.cumsum(counts, 0).to(torch.int32)
+    edge_off = torch.zeros(B + 1, dtype=torch.int64, device=dev)
+    edge_off[1:] = torch.cumsum(edge_counts, 0)
+    return {"features": features, "edges": edges, "node_off": node_off, "edge_off": edge_off, "labels": labels.long(), "T": T}
+
+
 def make_seq_batch(n_seq, n_features, T, seed=44, device="cpu"):
     """Plain [n_seq, T, F] sequences for the baseline models (CML: the target series)."""
     g = torch.Generator(device=device)

@@ -139,9 +139,20 @@ class GCNClassifier(_Classifier):
         return isinstance(batch, (tuple, list)) and len(batch) == 2 and isinstance(batch[0], (tuple, list, dict))
 
     def _forward(self, inputs):
-        if self.ds_type != "cml":
-            raise NotImplementedError("SoilNet GCN scoring is not built yet")
         dev = self.device
+        if self.ds_type == "soilnet":
+            T = self.sequence_length
+            if isinstance(inputs, dict):
+                return self.native.score_soilnet(_as_device(inputs["features"], dev, torch.float32), _as_device(inputs["edges"], dev, torch.int64),
+                                                 _as_device(inputs["node_off"], dev, torch.int32), _as_device(inputs["edge_off"], dev, torch.int64),
+                                                 inputs.get("T", T), inputs.get("n_nodes_total"))
+            # reference layout: (features, adjacency, sample_indices)
+            features = _as_device(inputs[0], dev, torch.float32)
+            idx = _as_device(_layout.adjacency_indices(inputs[1]), dev, torch.int64)
+            samp = _as_device(inputs[2], dev)
+            n_windows = int(samp.max().item()) + 1 if samp.numel() else 0
+            edges, node_off, edge_off, n_nodes = _layout.disjoint_to_offsets(idx, samp, n_windows, T)
+            return self.native.score_soilnet(features, edges, node_off, edge_off, T, n_nodes)
         if isinstance(inputs, dict):     # offsets layout, see include/gnnqc.h
             return self.native.score_cml(_as_device(inputs["features"], dev, torch.float32), _as_device(inputs["anom"], dev, torch.float32),
                                          _as_device(inputs["edges"], dev, torch.int64), _as_device(inputs["node_off"], dev, torch.int32),

@@ -162,6 +162,17 @@ int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_de
 int gnnqc_score_seq_noalloc(gnnqc_model* m, const float* x_dev, int64_t n_seq, int32_t T,
                             float* scores_dev, void* stream);
 
+/* Replaces GCNClassifier.call for ds_type 'soilnet' (libs/create_model.py:224-240), i.e.
+ * model.predict on batches from prepare_batch_soilnet / wrapper_batch_mapping_soilnet
+ * (libs/preprocessing_functions.py:861-897).
+ *   features_dev  f32 [sum_b T*N_b, 3], rows in (window, timestep, node) order
+ *   edges_dev / node_off_dev / edge_off_dev   as for gnnqc_score_cml (untiled, window-local)
+ *   scores_dev    f32 [sum_b N_b]: one score per (window, sensor) in (window, node) order -
+ *                 the order graph_reshape produces (libs/create_model.py:242-258) */
+int gnnqc_score_soilnet(gnnqc_model* m, const float* features_dev, const int64_t* edges_dev,
+                        const int32_t* node_off_dev, const int64_t* edge_off_dev, int64_t B, int32_t T,
+                        int64_t n_nodes_total, int64_t n_edges_total, float* scores_dev, void* stream);
+
 /* Bytes of device scratch the scoring entry points keep inside the handle for `n_seq`
  * sequences of length T (grown on demand with cudaMalloc, freed by gnnqc_model_free). */
 int64_t gnnqc_score_scratch_bytes(const gnnqc_model* m, int64_t n_seq, int32_t T);

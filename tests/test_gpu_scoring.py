@@ -79,6 +79,38 @@ def test_baseline_vs_oracle(models, model, F, T, n):
     close(models[model].score_seq(x.cuda()).cpu().numpy(), want)
 
 
+def oracle_soilnet(named, batch, dtype=torch.float32):
+    feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 3)
+    w = O.to_torch_weights(named, dtype)
+    B = batch["node_off"].numel() - 1
+    p = O.gcn_forward_soilnet(torch.tensor(feat).to(dtype), torch.tensor(idx), torch.tensor(samp), B, batch["T"], w)
+    return p.reshape(-1).numpy()
+
+
+@pytest.mark.parametrize("n,nodes,ragged", [(2, 14, False), (5, 40, True)])
+def test_soilnet_gcn_vs_oracle(models, n, nodes, ragged):
+    batch = synth.make_soilnet_batch(n, seed=31 + n, n_nodes=nodes, ragged=ragged, min_nodes=7)
+    b = cuda(batch)
+    got = models["model_soilnet"].score_soilnet(b["features"], b["edges"], b["node_off"], b["edge_off"], batch["T"]).cpu().numpy()
+    close(got, oracle_soilnet(models["model_soilnet"].named_params(), batch))
+
+
+def test_soilnet_edge_order_does_not_matter(models):
+    """The CSR build sorts neighbour lists: shuffling the caller's edge list changes nothing."""
+    batch = synth.make_soilnet_batch(3, seed=5, n_nodes=30)
+    b = cuda(batch)
+    m = models["model_soilnet"]
+    base = m.score_soilnet(b["features"], b["edges"], b["node_off"], b["edge_off"], batch["T"])
+    eo = batch["edge_off"].numpy()
+    g = torch.Generator().manual_seed(0)
+    parts = []
+    for w in range(3):
+        e = batch["edges"][eo[w]: eo[w + 1]]
+        parts.append(e[torch.randperm(e.shape[0], generator=g)])
+    shuffled = torch.cat(parts).cuda()
+    assert torch.equal(m.score_soilnet(b["features"], shuffled, b["node_off"], b["edge_off"], batch["T"]), base)
+
+
 def test_other_sequence_lengths(models):
     """T is a runtime argument (the reference bakes it into the graph)."""
     for T in (27, 100, 243):
