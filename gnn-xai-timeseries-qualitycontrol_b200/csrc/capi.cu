@@ -54,6 +54,7 @@ void attach_device(DeviceModel& dm, int device) {
   dm.sm_count = prop.multiProcessorCount;
   dm.configure_kernels();
   dm.configure_ig_kernels();
+  dm.configure_train_kernels();
   dm.upload();
 }
 
@@ -150,6 +151,7 @@ int gnnqc_model_describe(const gnnqc_model* m, gnnqc_model_desc* out) {
 int gnnqc_model_get_params(const gnnqc_model* m, float* out_host, int64_t n) {
   if (!m || !out_host) return fail(GNNQC_ERR_ARG, "gnnqc_model_get_params: null argument");
   if (n != m->dm.host.spec.n_params) return fail(GNNQC_ERR_ARG, "gnnqc_model_get_params: wrong length");
+  if (int rc = guarded([&] { const_cast<gnnqc_model*>(m)->dm.sync_host_params(); })) return rc;
   std::memcpy(out_host, m->dm.host.params.data(), sizeof(float) * n);
   return GNNQC_OK;
 }
@@ -183,7 +185,10 @@ int gnnqc_model_segment(const gnnqc_model* m, int idx, char path[128], int64_t* 
 
 int gnnqc_model_save(const gnnqc_model* m, const char* dir) {
   if (!m || !dir) return fail(GNNQC_ERR_ARG, "gnnqc_model_save: null argument");
-  return guarded([&] { gnnqc::save_saved_model(m->dm.host, dir); });
+  return guarded([&] {
+    const_cast<gnnqc_model*>(m)->dm.sync_host_params();
+    gnnqc::save_saved_model(m->dm.host, dir);
+  });
 }
 
 void gnnqc_model_free(gnnqc_model* m) { delete m; }
@@ -205,6 +210,7 @@ int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom
   if (B > 0 && (!features_dev || !anom_dev || !edges_dev || !node_off_dev || !edge_off_dev || !scores_dev))
     return fail(GNNQC_ERR_ARG, "gnnqc_score_cml: null buffer");
   return guarded([&] {
+    m->dm.sync_host_params();
     m->dm.score_cml(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
                     reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, scores_dev,
                     static_cast<cudaStream_t>(stream));
@@ -222,6 +228,7 @@ int gnnqc_score_soilnet(gnnqc_model* m, const float* features_dev, const int64_t
   if (B > 0 && (!features_dev || !edges_dev || !node_off_dev || !edge_off_dev || !scores_dev))
     return fail(GNNQC_ERR_ARG, "gnnqc_score_soilnet: null buffer");
   return guarded([&] {
+    m->dm.sync_host_params();
     m->dm.score_soilnet(features_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
                         reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, n_edges_total, scores_dev,
                         static_cast<cudaStream_t>(stream));
@@ -237,10 +244,52 @@ int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_de
   if (B > 0 && (!features_dev || !anom_dev || !edges_dev || !node_off_dev || !edge_off_dev || !attr_features_dev || !attr_anom_dev || !scores_dev))
     return fail(GNNQC_ERR_ARG, "gnnqc_ig_cml: null buffer");
   return guarded([&] {
+    m->dm.sync_host_params();
     m->dm.ig_cml(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
                  reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, m_steps, attr_features_dev, attr_anom_dev,
                  scores_dev, static_cast<cudaStream_t>(stream));
   });
+}
+
+int64_t gnnqc_train_vector_len(const gnnqc_model* m) { return m ? m->dm.host.spec.n_params + 81 : 0; }
+
+int gnnqc_train_moments_cml(gnnqc_model* m, const float* features_dev, int64_t n_rows, double* moments_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_train_moments_cml")) return rc;
+  if (!features_dev || !moments_dev || n_rows <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_train_moments_cml: bad argument");
+  return guarded([&] { m->dm.train_moments(features_dev, n_rows, moments_dev, static_cast<cudaStream_t>(stream)); });
+}
+
+int gnnqc_train_grads_cml(gnnqc_model* m, const float* features_dev, const float* anom_dev, const int64_t* edges_dev,
+                          const int32_t* node_off_dev, const int64_t* edge_off_dev, const int64_t* labels_dev, int64_t B, int32_t T,
+                          int64_t n_nodes_total, const double* moments_dev, float class_weight_0, float class_weight_1,
+                          int64_t global_batch, float* rvec_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_train_grads_cml")) return rc;
+  if (!m->dm.host.spec.has_gcn || m->dm.host.spec.soilnet) return fail(GNNQC_ERR_STATE, "gnnqc_train_grads_cml: model is not a CML GCNClassifier");
+  if (B <= 0 || T <= 0 || n_nodes_total <= 0 || global_batch <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_train_grads_cml: bad sizes");
+  if (!features_dev || !anom_dev || !edges_dev || !node_off_dev || !edge_off_dev || !labels_dev || !moments_dev || !rvec_dev)
+    return fail(GNNQC_ERR_ARG, "gnnqc_train_grads_cml: null buffer");
+  return guarded([&] {
+    m->dm.train_grads(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
+                      reinterpret_cast<const long long*>(edge_off_dev), nullptr, reinterpret_cast<const long long*>(labels_dev), B, T,
+                      n_nodes_total, moments_dev, class_weight_0, class_weight_1, global_batch, rvec_dev, static_cast<cudaStream_t>(stream));
+  });
+}
+
+int gnnqc_train_grads_seq(gnnqc_model* m, const float* x_dev, const int64_t* labels_dev, int64_t n_seq, int32_t T, float class_weight_0,
+                          float class_weight_1, int64_t global_batch, float* rvec_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_train_grads_seq")) return rc;
+  if (m->dm.host.spec.has_gcn || m->dm.host.spec.soilnet) return fail(GNNQC_ERR_STATE, "gnnqc_train_grads_seq: model is not a CML BaselineClassifier");
+  if (n_seq <= 0 || T <= 0 || global_batch <= 0 || !x_dev || !labels_dev || !rvec_dev) return fail(GNNQC_ERR_ARG, "gnnqc_train_grads_seq: bad argument");
+  return guarded([&] {
+    m->dm.train_grads(nullptr, nullptr, nullptr, nullptr, nullptr, x_dev, reinterpret_cast<const long long*>(labels_dev), n_seq, T, 0, nullptr,
+                      class_weight_0, class_weight_1, global_batch, rvec_dev, static_cast<cudaStream_t>(stream));
+  });
+}
+
+int gnnqc_train_apply(gnnqc_model* m, float* rvec_dev, const double* moments_dev, float learning_rate, void* stream) {
+  if (int rc = need_device(m, "gnnqc_train_apply")) return rc;
+  if (!rvec_dev || !(learning_rate > 0.f)) return fail(GNNQC_ERR_ARG, "gnnqc_train_apply: bad argument");
+  return guarded([&] { m->dm.train_apply(rvec_dev, moments_dev, learning_rate, static_cast<cudaStream_t>(stream)); });
 }
 
 int64_t gnnqc_launch_count(const gnnqc_model* m) { return m ? m->dm.launches : 0; }

@@ -65,6 +65,7 @@ void DeviceModel::profile_reset() {
 DeviceModel::~DeviceModel() {
   if (device >= 0) {
     cudaSetDevice(device);
+    free_train_state();
     profile_reset();
     for (cudaEvent_t e : event_pool) cudaEventDestroy(e);
     cudaFree(d_params);

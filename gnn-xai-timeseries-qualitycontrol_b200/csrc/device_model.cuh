@@ -41,6 +41,8 @@ struct LaunchRecord {
   cudaEvent_t start, stop;
 };
 
+struct TrainState;   // optimizer slots and per-step BN state (csrc/train.cu)
+
 struct DeviceModel {
   HostModel host;
   int device = -1;              // < 0: host-only handle
@@ -70,6 +72,19 @@ struct DeviceModel {
   void run_stack(const StackPlan& plan, float* buf_a, float* buf_b, long long n_tiles, long long n_seq,
                  float* scores, cudaStream_t stream);
   void score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t stream);
+  // Training (csrc/train.cu).  After train_apply the device copy of the parameters is the
+  // authoritative one; sync_host_params() brings host.params up to date on demand.
+  TrainState* train = nullptr;
+  bool params_dirty = false;
+  void configure_train_kernels();
+  TrainState* train_state();
+  void free_train_state();
+  void sync_host_params();
+  void train_moments(const float* feat, long long n_rows, double* moments, cudaStream_t stream);
+  void train_grads(const float* feat, const float* anom, const long long* edges, const int* node_off, const long long* edge_off,
+                   const float* x_seq, const long long* labels, long long B, int T, long long n_nodes, const double* moments,
+                   float cw0, float cw1, long long global_batch, float* rvec, cudaStream_t stream);
+  void train_apply(float* rvec, const double* moments, float lr, cudaStream_t stream);
   // SoilNet GCN (csrc/soilnet.cu): scores [n_nodes], one per (window, sensor).
   void score_soilnet(const float* feat, const long long* edges, const int* node_off, const long long* edge_off, long long B,
                      int T, long long n_nodes, long long n_edges, float* scores, cudaStream_t stream);

@@ -107,10 +107,10 @@ struct GcnFolded {
 // ---- CML front-end: features (b,t,n) + coef + target series -> x1 tiles [tile][t][18][64] --
 // Restates GCNClassifier.call for 'cml' up to the Concatenate (libs/create_model.py:217-223):
 // channels 0..1 = anomalous_sensor_features, 2..17 = pooled GeneralConv output.
-static __global__ void __launch_bounds__(256) cml_frontend_kernel(const float2* __restrict__ feat, const float2* __restrict__ anom,
+__device__ __forceinline__ void cml_frontend_body(const float2* __restrict__ feat, const float2* __restrict__ anom,
                                                            const float* __restrict__ coef, const int* __restrict__ node_off,
-                                                           const GcnFolded p, float* __restrict__ out,
-                                                           long long n_windows, int T, int t_run, float alpha = 1.f) {
+                                                           const GcnFolded& p, float* __restrict__ out,
+                                                           long long n_windows, int T, int t_run, float alpha) {
   const int b = threadIdx.x & 63, tq = threadIdx.x >> 6;
   const long long tile = blockIdx.x;
   const long long win = tile * kTile + b;
@@ -145,6 +145,25 @@ static __global__ void __launch_bounds__(256) cml_frontend_kernel(const float2* 
 #pragma unroll
     for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc[c];
   }
+}
+
+static __global__ void __launch_bounds__(256) cml_frontend_kernel(const float2* __restrict__ feat, const float2* __restrict__ anom,
+                                                                  const float* __restrict__ coef, const int* __restrict__ node_off,
+                                                                  const GcnFolded p, float* __restrict__ out, long long n_windows,
+                                                                  int T, int t_run, float alpha = 1.f) {
+  cml_frontend_body(feat, anom, coef, node_off, p, out, n_windows, T, t_run, alpha);
+}
+
+// Same, with the folded projection read from device memory (training: it depends on the batch
+// statistics computed on the device a moment earlier).
+static __global__ void __launch_bounds__(256) cml_frontend_devparam_kernel(const float2* __restrict__ feat, const float2* __restrict__ anom,
+                                                                           const float* __restrict__ coef, const int* __restrict__ node_off,
+                                                                           const GcnFolded* __restrict__ pp, float* __restrict__ out,
+                                                                           long long n_windows, int T, int t_run) {
+  __shared__ GcnFolded p;
+  if (threadIdx.x < sizeof(GcnFolded) / 4) reinterpret_cast<float*>(&p)[threadIdx.x] = reinterpret_cast<const float*>(pp)[threadIdx.x];
+  __syncthreads();
+  cml_frontend_body(feat, anom, coef, node_off, p, out, n_windows, T, t_run, 1.f);
 }
 
 // ---- dense head: [tile][128][64] -> sigmoid(Dense(LeakyReLU(Dense(LeakyReLU(Dense))))) ------

@@ -39,7 +39,7 @@ struct FwdSave {
   static constexpr bool WGLOBAL = (size_t(I + H) * H * 16 > 160 * 1024);
   static constexpr int RJ = 2, RB = 8, LJ = 8, NST = 2, VAR = kVarPacked;
   using Cfg = LstmCfg<I, H, RJ, RB, LJ, WGLOBAL, NST>;
-  static auto kernel() { return lstm_layer_kernel<I, H, RJ, RB, LJ, POOL, LAST, WGLOBAL, VAR, NST, true>; }
+  static auto kernel() { return lstm_layer_kernel<I, H, RJ, RB, LJ, POOL, LAST, WGLOBAL, VAR, NST, 5>; }
   static void configure() {
     GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
   }
@@ -68,7 +68,7 @@ struct Bwd {
     GNNQC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel(), Cfg::NT, Cfg::SMEM_BYTES));
     if (per_sm < 1) throw CudaError("lstm_layer_bwd_kernel does not fit on an SM");
     long long grid = std::min<long long>(n_tiles, static_cast<long long>(sm_count) * per_sm);
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wT, dx, T, static_cast<int>(n_tiles));
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wT, dx, T, static_cast<int>(n_tiles), nullptr);
     GNNQC_CUDA(cudaGetLastError());
   }
 };

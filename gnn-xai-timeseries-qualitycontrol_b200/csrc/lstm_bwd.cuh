@@ -34,14 +34,17 @@ struct BwdCfg {
   static constexpr size_t SMEM_BYTES = (W_FLOATS + size_t(COLS) * kTile + size_t(H) * kTile) * 4;
 };
 
-template <int I, int H, bool POOL, bool LAST, bool WGLOBAL>
+// NSAVE: quantities per step in `save` (5 for attribution, 6 for training).  dz_out (training):
+// when not null the gate pre-activation gradients are also written as dz_out[tile][t][4H][64] for
+// the weight-gradient kernel.
+template <int I, int H, bool POOL, bool LAST, bool WGLOBAL, int NSAVE = 5>
 __global__ void __launch_bounds__((BwdCfg<I, H, WGLOBAL>::NT))
 lstm_layer_bwd_kernel(const float* __restrict__ dy,    // grad wrt this layer's output (see header)
-                      const float* __restrict__ save,  // [n_tiles][T][H][5][64]
+                      const float* __restrict__ save,  // [n_tiles][T][NSAVE][H][64]
                       const float* __restrict__ amax,  // POOL: [n_tiles][T/3][H][64]
                       const float* __restrict__ wT,    // [4H][KPAD]
                       float* __restrict__ dx,          // [n_tiles][T][I][64]
-                      int T, int n_tiles) {
+                      int T, int n_tiles, float* __restrict__ dz_out) {
   using C = BwdCfg<I, H, WGLOBAL>;
   extern __shared__ __align__(128) unsigned char smem_raw[];
   float* wsm = reinterpret_cast<float*>(smem_raw);
@@ -72,12 +75,12 @@ lstm_layer_bwd_kernel(const float* __restrict__ dy,    // grad wrt this layer's 
         const int g = tid + n * C::NT;
         if (g < C::GROUPS) {
           const int u = g / (kTile / 4), c4 = g % (kTile / 4);
-          const float4* sv = reinterpret_cast<const float4*>(save + (((tile * T + t) * H + u) * 5) * kTile);
-          const float4 ig = __ldg(sv + 0 * (kTile / 4) + c4), fg = __ldg(sv + 1 * (kTile / 4) + c4),
-                       gg = __ldg(sv + 2 * (kTile / 4) + c4), og = __ldg(sv + 3 * (kTile / 4) + c4),
-                       ct = __ldg(sv + 4 * (kTile / 4) + c4);
+          constexpr int QS = H * kTile / 4;   // float4 stride between saved quantities
+          const float4* sv = reinterpret_cast<const float4*>(save + (((tile * T + t) * NSAVE) * H + u) * kTile);
+          const float4 ig = __ldg(sv + 0 * QS + c4), fg = __ldg(sv + 1 * QS + c4), gg = __ldg(sv + 2 * QS + c4),
+                       og = __ldg(sv + 3 * QS + c4), ct = __ldg(sv + 4 * QS + c4);
           float4 cp = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (t > 0) cp = __ldg(reinterpret_cast<const float4*>(save + (((tile * T + t - 1) * H + u) * 5 + 4) * kTile) + c4);
+          if (t > 0) cp = __ldg(reinterpret_cast<const float4*>(save + (((tile * T + t - 1) * NSAVE + 4) * H + u) * kTile) + c4);
           float4 dh = make_float4(0.f, 0.f, 0.f, 0.f);
           if (t < T - 1) dh = reinterpret_cast<const float4*>(dhs)[u * (kTile / 4) + c4];
           if (POOL) {
@@ -114,6 +117,13 @@ lstm_layer_bwd_kernel(const float* __restrict__ dy,    // grad wrt this layer's 
           dz4[(1 * H + u) * (kTile / 4) + c4] = zf;
           dz4[(2 * H + u) * (kTile / 4) + c4] = zg;
           dz4[(3 * H + u) * (kTile / 4) + c4] = zo;
+          if (dz_out != nullptr) {
+            float4* go = reinterpret_cast<float4*>(dz_out + (tile * T + t) * (C::COLS * kTile));
+            go[(0 * H + u) * (kTile / 4) + c4] = zi;
+            go[(1 * H + u) * (kTile / 4) + c4] = zf;
+            go[(2 * H + u) * (kTile / 4) + c4] = zg;
+            go[(3 * H + u) * (kTile / 4) + c4] = zo;
+          }
         }
       }
       __syncthreads();

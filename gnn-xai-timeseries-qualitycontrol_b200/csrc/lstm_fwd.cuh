@@ -93,11 +93,11 @@ struct LstmCfg {
   static_assert(XBYTES % 16 == 0, "bulk copies need 16-byte multiples");
 };
 
-// SAVE (used by the attribution / training paths): additionally stores, per step and cell, the
-// gate activations i, f, g, o and the cell state c as save[tile][t][unit][5][64], and for pooled
-// layers which of the three pooled steps held the maximum (amax[tile][t/3][unit][64], first
-// maximum wins like TF's MaxPoolGrad).
-template <int I, int H, int RJ, int RB, int LJ, bool POOL, bool LAST, bool WGLOBAL, int VAR = 0, int NST_ = 0, bool SAVE = false>
+// NSAVE > 0 (used by the attribution / training paths): additionally stores, per step, the gate
+// activations i, f, g, o, the cell state c and (NSAVE == 6) the output h as
+// save[tile][t][quantity][unit][64], and for pooled layers which of the three pooled steps held
+// the maximum (amax[tile][t/3][unit][64], first maximum wins like TF's MaxPoolGrad).
+template <int I, int H, int RJ, int RB, int LJ, bool POOL, bool LAST, bool WGLOBAL, int VAR = 0, int NST_ = 0, int NSAVE = 0>
 __global__ void __launch_bounds__((LstmCfg<I, H, RJ, RB, LJ, WGLOBAL, NST_>::NT))
 lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][64]
                   float* __restrict__ yout,        // [n_tiles][t_out_stride][H][64], LAST: [n_tiles][H][64]
@@ -106,6 +106,7 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
                   float* __restrict__ save = nullptr, float* __restrict__ amax = nullptr) {
   using C = LstmCfg<I, H, RJ, RB, LJ, WGLOBAL, NST_>;
   constexpr bool PACKED = (VAR & kVarPacked) != 0;
+  constexpr bool SAVE = NSAVE > 0;
   constexpr bool FUSED = (VAR & kVarFusedCell) != 0 && !SAVE;
   constexpr bool PIPE = (VAR & kVarPipelined) != 0;
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -280,7 +281,7 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
     for (int r = 0; r < RJ; ++r) {
       const int unit = unit0 + r * LJ;
       float hv[RB];
-      float sv[SAVE ? 5 : 1][SAVE ? RB : 1];
+      float sv[SAVE ? NSAVE : 1][SAVE ? RB : 1];
 #pragma unroll
       for (int i = 0; i < RB; ++i) {
         float zi, zf, zg, zo;
@@ -299,17 +300,18 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
           cst[r][i] = cn;
           hv[i] = og * tanh_fast(cn);
           sv[0][i] = ig; sv[1][i] = fg; sv[2][i] = gg; sv[3][i] = og; sv[4][i] = cn;
+          if (NSAVE > 5) sv[NSAVE > 5 ? 5 : 0][i] = hv[i];
         } else {
           hv[i] = FUSED ? lstm_cell_fused(zi, zf, zg, zo, cst[r][i]) : lstm_cell_plain(zi, zf, zg, zo, cst[r][i]);
         }
       }
       if (SAVE) {
-        float4* so = reinterpret_cast<float4*>(save + (((tile * T + t) * H + unit) * 5) * kTile);
+        float4* so = reinterpret_cast<float4*>(save + (((tile * T + t) * NSAVE) * H + unit) * kTile);
 #pragma unroll
-        for (int v = 0; v < 5; ++v)
+        for (int v = 0; v < NSAVE; ++v)
 #pragma unroll
           for (int qq = 0; qq < C::NQ; ++qq)
-            so[v * (kTile / 4) + b4 + qq * C::LB] = make_float4(sv[v][4 * qq], sv[v][4 * qq + 1], sv[v][4 * qq + 2], sv[v][4 * qq + 3]);
+            so[v * (H * kTile / 4) + b4 + qq * C::LB] = make_float4(sv[v][4 * qq], sv[v][4 * qq + 1], sv[v][4 * qq + 2], sv[v][4 * qq + 3]);
       }
 #pragma unroll
       for (int qq = 0; qq < C::NQ; ++qq)

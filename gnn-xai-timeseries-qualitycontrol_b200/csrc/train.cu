@@ -1,0 +1,353 @@
+// Training step on the GPU (gnnqc_train_*), restating libs/fit_model.py:61-112 as Keras executes it:
+//   forward in training mode (BatchNormalization of the GeneralConv uses the batch statistics over
+//   all node rows), loss = sum_b class_weight[y_b] * BCE(logit_b, y_b) / batch_size, backward through
+//   head, the seven LSTM layers (BPTT), max-pooling, node pooling and the GeneralConv, Adam update,
+//   moving-average update of the BN statistics.
+// Split in three calls so that data-parallel ranks can sum across GPUs in between (the only
+// exchange steps of the whole path):
+//   gnnqc_train_moments_cml   local feature moments (6 doubles)     -> all-reduce (sum)
+//   gnnqc_train_grads_*       local reduction vector (grads, raw GCN sums, loss) -> all-reduce (sum)
+//   gnnqc_train_apply         BN-backward closure, Adam, BN moving statistics, weight re-packing
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "device_model.cuh"
+#include "lstm_bwd.cuh"
+#include "train_kernels.cuh"
+
+namespace gnnqc {
+namespace {
+
+inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+template <int I, int H, bool POOL, bool LAST>
+struct TrainFwd {
+  static constexpr bool WGLOBAL = (size_t(I + H) * H * 16 > 160 * 1024);
+  static constexpr int RJ = 2, RB = 8, LJ = 8, NST = 2, VAR = kVarPacked;
+  using Cfg = LstmCfg<I, H, RJ, RB, LJ, WGLOBAL, NST>;
+  static auto kernel() { return lstm_layer_kernel<I, H, RJ, RB, LJ, POOL, LAST, WGLOBAL, VAR, NST, 6>; }
+  static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
+  static void launch(const float* x, float* y, const float* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, float* save,
+                     float* amax, cudaStream_t st) {
+    int per_sm = 1;
+    GNNQC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel(), Cfg::NT, Cfg::SMEM_BYTES));
+    long long grid = std::min<long long>(n_tiles, static_cast<long long>(sm_count) * std::max(per_sm, 1));
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax);
+    GNNQC_CUDA(cudaGetLastError());
+  }
+};
+
+template <int I, int H, bool POOL, bool LAST>
+struct TrainBwd {
+  static constexpr bool WGLOBAL = (size_t(4 * H) * ((I + H + 15) / 16 * 16) * 4 > 150 * 1024);
+  using Cfg = BwdCfg<I, H, WGLOBAL>;
+  static auto kernel() { return lstm_layer_bwd_kernel<I, H, POOL, LAST, WGLOBAL, 6>; }
+  static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
+  static void launch(const float* dy, const float* save, const float* amax, const float* wT, float* dx, int T, long long n_tiles,
+                     int sm_count, float* dz_out, cudaStream_t st) {
+    int per_sm = 1;
+    GNNQC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel(), Cfg::NT, Cfg::SMEM_BYTES));
+    long long grid = std::min<long long>(n_tiles, static_cast<long long>(sm_count) * std::max(per_sm, 1));
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wT, dx, T, static_cast<int>(n_tiles), dz_out);
+    GNNQC_CUDA(cudaGetLastError());
+  }
+};
+
+enum class Op { Configure, Forward, Backward };
+struct LayerArgs {
+  const float* in = nullptr;
+  float* out = nullptr;
+  const float* w = nullptr;
+  float* save = nullptr;
+  float* amax = nullptr;
+  float* dz = nullptr;
+  int T = 0, t_in = 0, t_out = 0;
+  long long n_tiles = 0;
+  int sm_count = 0;
+  cudaStream_t st = nullptr;
+};
+
+template <int I, int H, bool POOL, bool LAST>
+void layer_op(Op op, const LayerArgs& a) {
+  if (op == Op::Configure) {
+    TrainFwd<I, H, POOL, LAST>::configure();
+    TrainBwd<I, H, POOL, LAST>::configure();
+  } else if (op == Op::Forward) {
+    TrainFwd<I, H, POOL, LAST>::launch(a.in, a.out, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.save, a.amax, a.st);
+  } else {
+    TrainBwd<I, H, POOL, LAST>::launch(a.in, a.save, a.amax, a.w, a.out, a.T, a.n_tiles, a.sm_count, a.dz, a.st);
+  }
+}
+
+void dispatch(Op op, int in, int hid, bool pool, bool last, const LayerArgs& a) {
+#define GNNQC_CASE(I_, H_, POOL_, LAST_) \
+  if (in == I_ && hid == H_ && pool == POOL_ && last == LAST_) return layer_op<I_, H_, POOL_, LAST_>(op, a);
+  GNNQC_CASE(2, 16, false, false)
+  GNNQC_CASE(18, 16, false, false)
+  GNNQC_CASE(16, 16, true, false)
+  GNNQC_CASE(16, 32, false, false)
+  GNNQC_CASE(32, 32, true, false)
+  GNNQC_CASE(32, 64, false, false)
+  GNNQC_CASE(64, 64, true, false)
+  GNNQC_CASE(64, 128, false, true)
+#undef GNNQC_CASE
+  throw std::invalid_argument("training: no kernel for this LSTM layer shape (CML models only)");
+}
+
+constexpr size_t kPartialBytes = size_t(64) << 20;
+
+}  // namespace
+
+struct TrainState {
+  float* mom = nullptr;
+  float* vel = nullptr;
+  GcnFolded* folded = nullptr;
+  BnBatch* stats = nullptr;
+  long long step = 0;
+};
+
+void DeviceModel::configure_train_kernels() {
+  const ModelSpec& s = host.spec;
+  if (s.soilnet) return;
+  LayerArgs none;
+  for (int l = 0; l < s.n_lstm; ++l) {
+    const bool last = (l == s.n_lstm - 1);
+    dispatch(Op::Configure, s.lstm_in[l], s.lstm_hid[l], !last && (l % 2 == 1), last, none);
+  }
+  GNNQC_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWgradSmem)));
+}
+
+TrainState* DeviceModel::train_state() {
+  if (!train) {
+    train = new TrainState();
+    const size_t n = size_t(host.spec.n_params);
+    GNNQC_CUDA(cudaSetDevice(device));
+    GNNQC_CUDA(cudaMalloc(&train->mom, n * sizeof(float)));
+    GNNQC_CUDA(cudaMalloc(&train->vel, n * sizeof(float)));
+    GNNQC_CUDA(cudaMemset(train->mom, 0, n * sizeof(float)));
+    GNNQC_CUDA(cudaMemset(train->vel, 0, n * sizeof(float)));
+    GNNQC_CUDA(cudaMalloc(&train->folded, sizeof(GcnFolded)));
+    GNNQC_CUDA(cudaMalloc(&train->stats, sizeof(BnBatch)));
+  }
+  return train;
+}
+
+void DeviceModel::free_train_state() {
+  if (!train) return;
+  cudaFree(train->mom);
+  cudaFree(train->vel);
+  cudaFree(train->folded);
+  cudaFree(train->stats);
+  delete train;
+  train = nullptr;
+}
+
+void DeviceModel::sync_host_params() {
+  if (!params_dirty || device < 0) return;
+  GNNQC_CUDA(cudaSetDevice(device));
+  GNNQC_CUDA(cudaDeviceSynchronize());
+  GNNQC_CUDA(cudaMemcpy(host.params.data(), d_params, size_t(host.spec.n_params) * sizeof(float), cudaMemcpyDeviceToHost));
+  params_dirty = false;
+}
+
+void DeviceModel::train_moments(const float* feat, long long n_rows, double* moments, cudaStream_t st) {
+  GNNQC_CUDA(cudaSetDevice(device));
+  GNNQC_CUDA(cudaMemsetAsync(moments, 0, 6 * sizeof(double), st));
+  mark_begin("train_moments", st);
+  feat_moments_kernel<<<sm_count * 4, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), n_rows, moments);
+  GNNQC_CUDA(cudaGetLastError());
+  mark_end(st);
+  const double n = static_cast<double>(n_rows);
+  GNNQC_CUDA(cudaMemcpyAsync(moments + 5, &n, sizeof(double), cudaMemcpyHostToDevice, st));
+  GNNQC_CUDA(cudaStreamSynchronize(st));  // `n` lives on this stack frame
+}
+
+// Shared by the GCN and baseline paths.  x_first: the first layer's input tiles (already built).
+void DeviceModel::train_grads(const float* feat, const float* anom, const long long* edges, const int* node_off,
+                              const long long* edge_off, const float* x_seq, const long long* labels, long long B, int T,
+                              long long n_nodes, const double* moments, float cw0, float cw1, long long global_batch, float* rvec,
+                              cudaStream_t st) {
+  const ModelSpec& s = host.spec;
+  const bool gcn = s.has_gcn;
+  GNNQC_CUDA(cudaSetDevice(device));
+  TrainState* ts = train_state();
+  StackPlan plan(s, T);
+  const int L = s.n_lstm;
+  const long long nt = (B + kTile - 1) / kTile;
+  const long long np = s.n_params;
+
+  // ---- scratch layout (whole local batch at once; training batches are small) -------------------
+  size_t off = 0;
+  auto take = [&off](size_t bytes) { size_t at = off; off += align_up(bytes, 256); return at; };
+  const size_t o_deg = take(size_t(std::max<long long>(n_nodes, 1)) * 4), o_coef = take(size_t(std::max<long long>(n_nodes, 1)) * 4);
+  const size_t o_x1 = take(size_t(nt) * plan.t_run[0] * s.lstm_in[0] * kTile * 4);
+  size_t o_y[kMaxLstmLayers], o_save[kMaxLstmLayers], o_amax[kMaxLstmLayers], o_dz[kMaxLstmLayers];
+  size_t g_bytes = 0;
+  for (int l = 0; l < L; ++l) {
+    o_y[l] = take(size_t(nt) * plan.t_out[l] * s.lstm_hid[l] * kTile * 4);
+    o_save[l] = take(size_t(nt) * plan.t_run[l] * 6 * s.lstm_hid[l] * kTile * 4);
+    o_amax[l] = (l % 2 == 1 && l != L - 1) ? take(size_t(nt) * plan.t_out[l] * s.lstm_hid[l] * kTile * 4) : 0;
+    o_dz[l] = take(size_t(nt) * plan.t_run[l] * 4 * s.lstm_hid[l] * kTile * 4);
+    g_bytes = std::max(g_bytes, size_t(nt) * plan.t_run[l] * s.lstm_in[l] * kTile * 4);
+  }
+  const size_t o_g0 = take(g_bytes), o_g1 = take(g_bytes);
+  const size_t o_dy7 = take(size_t(nt) * s.lstm_hid[L - 1] * kTile * 4);
+  const size_t o_head = take(size_t(nt) * kHeadTrainFloats * 4);
+  const size_t o_lossp = take(size_t(nt) * 4);
+  const dim3 grid_fe(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
+  const size_t o_gcnp = take(size_t(grid_fe.x) * grid_fe.y * kGcnSums * 4);
+  const size_t o_part = take(kPartialBytes);
+  char* base = static_cast<char*>(scratch(off));
+  auto F = [base](size_t o) { return reinterpret_cast<float*>(base + o); };
+
+  GNNQC_CUDA(cudaMemsetAsync(rvec, 0, size_t(np + kGcnSums + 1) * sizeof(float), st));
+
+  // ---- forward ----------------------------------------------------------------------------------
+  const float* prm = d_params;
+  if (gcn) {
+    GNNQC_CUDA(cudaMemsetAsync(base + o_deg, 0, size_t(n_nodes) * 4, st));
+    mark_begin("cml_node_coef", st);
+    cml_node_coef_kernel<<<static_cast<unsigned>((B * 32 + 255) / 256), 256, 0, st>>>(edges, node_off, edge_off, reinterpret_cast<int*>(base + o_deg), F(o_coef), B);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
+    bn_prepare_kernel<<<1, 32, 0, st>>>(prm + s.off_gcn_kernel, prm + s.off_gcn_bias, prm + s.off_prelu, prm + s.off_bn_gamma,
+                                        prm + s.off_bn_beta, moments, s.bn_eps, ts->folded, ts->stats);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_begin("train_frontend", st);
+    cml_frontend_devparam_kernel<<<grid_fe, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), reinterpret_cast<const float2*>(anom), F(o_coef),
+                                                          node_off, ts->folded, F(o_x1), B, T, plan.t_run[0]);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
+  } else {
+    mark_begin("seq_to_tiles", st);
+    seq_to_tiles_kernel<2><<<grid_fe, 256, 0, st>>>(x_seq, F(o_x1), B, T, plan.t_run[0]);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
+  }
+  static const char* const kFwd[kMaxLstmLayers] = {"train_fwd_l1", "train_fwd_l2", "train_fwd_l3", "train_fwd_l4", "train_fwd_l5", "train_fwd_l6", "train_fwd_l7"};
+  static const char* const kBwd[kMaxLstmLayers] = {"train_bwd_l1", "train_bwd_l2", "train_bwd_l3", "train_bwd_l4", "train_bwd_l5", "train_bwd_l6", "train_bwd_l7"};
+  const float* in = F(o_x1);
+  int t_in = plan.t_run[0];
+  for (int l = 0; l < L; ++l) {
+    const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
+    LayerArgs a;
+    a.in = in; a.out = F(o_y[l]); a.w = d_packed + packed_off[l]; a.save = F(o_save[l]); a.amax = pool ? F(o_amax[l]) : nullptr;
+    a.T = plan.t_run[l]; a.t_in = t_in; a.t_out = plan.t_out[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
+    mark_begin(kFwd[l], st);
+    dispatch(Op::Forward, s.lstm_in[l], s.lstm_hid[l], pool, last, a);
+    mark_end(st);
+    in = a.out;
+    t_in = plan.t_out[l];
+  }
+  mark_begin("train_head", st);
+  head_train_kernel<128, 64><<<static_cast<unsigned>(nt), 256, 0, st>>>(in, prm + s.off_d1_w, prm + s.off_d1_b, prm + s.off_d2_w, prm + s.off_d2_b,
+                                                                        prm + s.off_out_w, prm + s.off_out_b, s.leaky_alpha, labels, cw0, cw1,
+                                                                        1.f / static_cast<float>(global_batch), F(o_dy7), F(o_head), F(o_lossp),
+                                                                        nullptr, B);
+  GNNQC_CUDA(cudaGetLastError());
+  mark_end(st);
+
+  // ---- backward through the LSTM stack -------------------------------------------------------------
+  const float* dy = F(o_dy7);
+  for (int l = L - 1; l >= 0; --l) {
+    const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
+    LayerArgs a;
+    a.in = dy; a.out = (l % 2 == 0) ? F(o_g0) : F(o_g1); a.w = d_packed_t + packed_t_off[l]; a.save = F(o_save[l]);
+    a.amax = pool ? F(o_amax[l]) : nullptr; a.dz = F(o_dz[l]);
+    a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
+    mark_begin(kBwd[l], st);
+    dispatch(Op::Backward, s.lstm_in[l], s.lstm_hid[l], pool, last, a);
+    mark_end(st);
+    dy = a.out;
+  }
+  const float* dx1 = dy;
+
+  // ---- weight gradients ------------------------------------------------------------------------------
+  auto wgrad = [&](const char* name, const float* A, long long a_tile, long long a_step, int NA, const float* Bm, long long b_tile,
+                   long long b_step, int NC, int n_steps, int bias, float* out_main, float* out_bias) {
+    if (n_steps <= 0) return;
+    WgradArgs g;
+    g.A = A; g.B = Bm; g.a_tile = a_tile; g.a_step = a_step; g.b_tile = b_tile; g.b_step = b_step;
+    g.NA = NA; g.NC = NC; g.n_steps = n_steps; g.n_items = nt * n_steps; g.bias = bias; g.partial = F(o_part);
+    const int rows = NA + bias;
+    const unsigned gx = (rows + kWgA - 1) / kWgA, gy = (NC + kWgC - 1) / kWgC;
+    long long slices = std::max<long long>(1, (static_cast<long long>(sm_count) * 16) / (gx * gy));
+    slices = std::min<long long>(slices, g.n_items);
+    slices = std::min<long long>(slices, static_cast<long long>(kPartialBytes / (size_t(rows) * NC * 4)));
+    mark_begin(name, st);
+    wgrad_kernel<<<dim3(gx, gy, static_cast<unsigned>(slices)), 64, kWgradSmem, st>>>(g);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
+    mark_begin("wgrad_reduce", st);
+    wgrad_reduce_kernel<<<(rows * NC + 255) / 256, 256, 0, st>>>(F(o_part), static_cast<int>(slices), rows, NC, out_main, NA, out_bias);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
+  };
+  for (int l = 0; l < L; ++l) {
+    const int I = s.lstm_in[l], H = s.lstm_hid[l], Tl = plan.t_run[l];
+    const float* xin = (l == 0) ? F(o_x1) : F(o_y[l - 1]);
+    const int t_in_l = (l == 0) ? plan.t_run[0] : plan.t_out[l - 1];
+    const long long dz_tile = static_cast<long long>(Tl) * 4 * H * kTile, dz_step = 4LL * H * kTile;
+    wgrad("wgrad_w", xin, static_cast<long long>(t_in_l) * I * kTile, static_cast<long long>(I) * kTile, I, F(o_dz[l]), dz_tile, dz_step, 4 * H, Tl,
+          1, rvec + s.off_lstm_w[l], rvec + s.off_lstm_b[l]);
+    // recurrent kernel: h_{t-1} (saved quantity 5) against dz_t, t = 1..T-1
+    wgrad("wgrad_u", F(o_save[l]) + 5LL * H * kTile, static_cast<long long>(Tl) * 6 * H * kTile, 6LL * H * kTile, H, F(o_dz[l]) + dz_step, dz_tile,
+          dz_step, 4 * H, Tl - 1, 0, rvec + s.off_lstm_u[l], nullptr);
+  }
+  {
+    const long long ht = kHeadTrainFloats;
+    const int D = s.dense_units, HL = s.lstm_hid[L - 1];
+    wgrad("wgrad_dense", F(o_y[L - 1]), static_cast<long long>(HL) * kTile, 0, HL, F(o_head) + 2LL * D * kTile, ht, 0, D, 1, 1, rvec + s.off_d1_w,
+          rvec + s.off_d1_b);
+    wgrad("wgrad_dense", F(o_head), ht, 0, D, F(o_head) + 3LL * D * kTile, ht, 0, D, 1, 1, rvec + s.off_d2_w, rvec + s.off_d2_b);
+    wgrad("wgrad_dense", F(o_head) + 1LL * D * kTile, ht, 0, D, F(o_head) + 4LL * D * kTile, ht, 0, 1, 1, 1, rvec + s.off_out_w, rvec + s.off_out_b);
+  }
+  if (gcn) {
+    mark_begin("train_frontend_bwd", st);
+    cml_frontend_train_bwd_kernel<<<grid_fe, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), F(o_coef), node_off, prm + s.off_gcn_kernel,
+                                                           prm + s.off_gcn_bias, ts->folded, ts->stats, s.bn_eps, dx1, F(o_gcnp), B, T,
+                                                           plan.t_run[0]);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
+    sum_partials_kernel<<<1, 128, 0, st>>>(F(o_gcnp), static_cast<long long>(grid_fe.x) * grid_fe.y, kGcnSums, rvec + np);
+    GNNQC_CUDA(cudaGetLastError());
+  }
+  sum_partials_kernel<<<1, 128, 0, st>>>(F(o_lossp), nt, 1, rvec + np + kGcnSums);
+  GNNQC_CUDA(cudaGetLastError());
+}
+
+void DeviceModel::train_apply(float* rvec, const double* moments, float lr, cudaStream_t st) {
+  const ModelSpec& s = host.spec;
+  GNNQC_CUDA(cudaSetDevice(device));
+  TrainState* ts = train_state();
+  const long long np = s.n_params;
+  long long skip_lo = 0, skip_hi = 0;
+  if (s.has_gcn) {
+    if (!moments) throw std::invalid_argument("gnnqc_train_apply: a GCN model needs the (global) feature moments");
+    GcnOffsets o{s.off_gcn_kernel, s.off_gcn_bias, s.off_prelu, s.off_bn_gamma, s.off_bn_beta, s.off_bn_mean, s.off_bn_var};
+    gcn_finalize_kernel<<<1, 32, 0, st>>>(rvec, np, d_params, o, moments, ts->stats, s.bn_eps);
+    GNNQC_CUDA(cudaGetLastError());
+    skip_lo = s.off_bn_mean;
+    skip_hi = s.off_bn_var + kGcnChannels;
+  }
+  ts->step += 1;
+  const double b1 = 0.9, b2 = 0.999;
+  const float lr_t = static_cast<float>(lr * std::sqrt(1.0 - std::pow(b2, double(ts->step))) / (1.0 - std::pow(b1, double(ts->step))));
+  mark_begin("adam", st);
+  adam_kernel<<<static_cast<unsigned>((np + 255) / 256), 256, 0, st>>>(d_params, rvec, ts->mom, ts->vel, np, lr_t, 0.9f, 0.999f, 1e-7f, skip_lo,
+                                                                       skip_hi, ts->stats, 0.99f);
+  GNNQC_CUDA(cudaGetLastError());
+  mark_end(st);
+  for (int l = 0; l < s.n_lstm; ++l) {
+    const int in = s.lstm_in[l], h = s.lstm_hid[l], kpad = (in + h + 15) / 16 * 16;
+    const long long n = static_cast<long long>(in + h + 1) * h * 4;
+    repack_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(d_params + s.off_lstm_w[l], d_params + s.off_lstm_u[l],
+                                                                          d_params + s.off_lstm_b[l], in, h, d_packed + packed_off[l],
+                                                                          d_packed_t + packed_t_off[l], kpad);
+    GNNQC_CUDA(cudaGetLastError());
+  }
+  params_dirty = true;
+}
+
+}  // namespace gnnqc

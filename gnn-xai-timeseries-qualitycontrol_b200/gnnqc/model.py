@@ -208,6 +208,57 @@ class NativeModel:
                                scores.data_ptr(), self._stream()))
         return attr_f, attr_a, scores
 
+    # ---- training ------------------------------------------------------------------------
+    def train_vector_len(self):
+        return int(lib.gnnqc_train_vector_len(self._h))
+
+    def train_moments_cml(self, features):
+        """Local feature moments (cuda f64 [6]); all-reduce(sum) them across ranks before use."""
+        torch = _torch()
+        features = self._dev_tensor(features, torch.float32, "features")
+        out = torch.empty(6, dtype=torch.float64, device=features.device)
+        check(lib.gnnqc_train_moments_cml(self._h, features.data_ptr(), features.shape[0], out.data_ptr(), self._stream()))
+        return out
+
+    def train_grads_cml(self, features, anom, edges, node_off, edge_off, labels, moments, class_weights=(1.0, 5.0),
+                        global_batch=None, n_nodes_total=None):
+        """This rank's reduction vector (cuda f32 [train_vector_len]): gradients, raw GCN sums, loss."""
+        torch = _torch()
+        features = self._dev_tensor(features, torch.float32, "features")
+        anom = self._dev_tensor(anom, torch.float32, "anom")
+        edges = self._dev_tensor(edges, torch.int64, "edges")
+        node_off = self._dev_tensor(node_off, torch.int32, "node_off")
+        edge_off = self._dev_tensor(edge_off, torch.int64, "edge_off")
+        labels = self._dev_tensor(labels, torch.int64, "labels")
+        moments = self._dev_tensor(moments, torch.float64, "moments")
+        B, T = anom.shape[0], anom.shape[1]
+        if n_nodes_total is None:
+            n_nodes_total = int(node_off[-1].item())
+        rvec = torch.empty(self.train_vector_len(), dtype=torch.float32, device=anom.device)
+        check(lib.gnnqc_train_grads_cml(self._h, features.data_ptr(), anom.data_ptr(), edges.data_ptr(), node_off.data_ptr(),
+                                        edge_off.data_ptr(), labels.data_ptr(), B, T, n_nodes_total, moments.data_ptr(),
+                                        float(class_weights[0]), float(class_weights[1]), int(global_batch or B), rvec.data_ptr(),
+                                        self._stream()))
+        return rvec
+
+    def train_grads_seq(self, x, labels, class_weights=(1.0, 5.0), global_batch=None):
+        torch = _torch()
+        x = self._dev_tensor(x, torch.float32, "x")
+        labels = self._dev_tensor(labels, torch.int64, "labels")
+        rvec = torch.empty(self.train_vector_len(), dtype=torch.float32, device=x.device)
+        check(lib.gnnqc_train_grads_seq(self._h, x.data_ptr(), labels.data_ptr(), x.shape[0], x.shape[1], float(class_weights[0]),
+                                        float(class_weights[1]), int(global_batch or x.shape[0]), rvec.data_ptr(), self._stream()))
+        return rvec
+
+    def train_apply(self, rvec, moments=None, learning_rate=1e-4):
+        torch = _torch()
+        rvec = self._dev_tensor(rvec, torch.float32, "rvec")
+        mp = None
+        if moments is not None:
+            moments = self._dev_tensor(moments, torch.float64, "moments")
+            mp = moments.data_ptr()
+        check(lib.gnnqc_train_apply(self._h, rvec.data_ptr(), mp, float(learning_rate), self._stream()))
+
     # ---- measurement ---------------------------------------------------------------------
     def launch_count(self):
         return int(lib.gnnqc_launch_count(self._h))

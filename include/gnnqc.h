@@ -143,6 +143,37 @@ int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_de
                  int64_t B, int32_t T, int64_t n_nodes_total, int32_t m_steps,
                  float* attr_features_dev, float* attr_anom_dev, float* scores_dev, void* stream);
 
+/* ---- training ------------------------------------------------------------------------- */
+
+/* Together these replace one train_step of model.fit as train_model sets it up
+ * (libs/fit_model.py:61-112): loss 'binary_crossentropy' on the sigmoid output (Keras evaluates it
+ * from the logits), class_weight {0: w0, 1: w1} as per-sample weights, mean over the batch, Adam
+ * (lr; beta 0.9/0.999, epsilon 1e-7), BatchNormalization of the GeneralConv in training mode
+ * (batch statistics over all node rows, moving statistics with momentum 0.99).  CML models only.
+ *
+ * The step is split where data-parallel ranks must sum across GPUs - the only exchange steps:
+ *   1. gnnqc_train_moments_cml: moments_dev f64[6] = {sum x0, sum x1, sum x0^2, sum x1^2,
+ *      sum x0 x1, row count} of this rank's features          -> all-reduce(sum) over ranks
+ *   2. gnnqc_train_grads_*: rvec_dev f32[gnnqc_train_vector_len()] = this rank's gradients in
+ *      flat-parameter order, 80 raw GeneralConv/BatchNorm sums, and the loss in the last slot;
+ *      everything is already divided by global_batch            -> all-reduce(sum) over ranks
+ *   3. gnnqc_train_apply: closes the BatchNorm backward with the global sums, applies Adam to the
+ *      device copy of the parameters, moves the BN statistics, refreshes the packed weights.
+ * Single GPU: call 1-2-3 without the all-reduces (global_batch = B).  labels_dev: i64 [B]. */
+int64_t gnnqc_train_vector_len(const gnnqc_model* m);
+int gnnqc_train_moments_cml(gnnqc_model* m, const float* features_dev, int64_t n_rows,
+                            double* moments_dev, void* stream);
+int gnnqc_train_grads_cml(gnnqc_model* m, const float* features_dev, const float* anom_dev,
+                          const int64_t* edges_dev, const int32_t* node_off_dev,
+                          const int64_t* edge_off_dev, const int64_t* labels_dev, int64_t B, int32_t T,
+                          int64_t n_nodes_total, const double* moments_dev, float class_weight_0,
+                          float class_weight_1, int64_t global_batch, float* rvec_dev, void* stream);
+int gnnqc_train_grads_seq(gnnqc_model* m, const float* x_dev, const int64_t* labels_dev, int64_t n_seq,
+                          int32_t T, float class_weight_0, float class_weight_1, int64_t global_batch,
+                          float* rvec_dev, void* stream);
+int gnnqc_train_apply(gnnqc_model* m, float* rvec_dev, const double* moments_dev,
+                      float learning_rate, void* stream);
+
 /* gnnqc_score_seq for callers that are not allowed to allocate.  It has no counterpart in the
  * reference.  Some users of this library cannot call cudaMalloc where they score: a
  * fixed-budget real-time loop, a process whose device memory is all owned by another

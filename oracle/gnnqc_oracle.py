@@ -247,3 +247,80 @@ def np_lstm_stack_head(x, named, prefix, first_dense):
     x = lrelu(x @ named[first_dense + "/kernel"].astype(np.float64) + named[first_dense + "/bias"])
     x = lrelu(x @ named["dense2/kernel"].astype(np.float64) + named["dense2/bias"])
     return sig(x @ named["dense_out/kernel"].astype(np.float64) + named["dense_out/bias"]).reshape(-1)
+
+
+# ---- training step ---------------------------------------------------------------------------------
+# libs/fit_model.py:61-112: model.compile(loss='binary_crossentropy', Adam(lr)), model.fit(class_weight=...).
+# Keras semantics restated: the sigmoid output keeps its logits (keras/activations.py sigmoid sets
+# _keras_logits), so binary_crossentropy is sigmoid_cross_entropy_with_logits; class_weight becomes a
+# per-sample weight and the loss is sum(w_b * bce_b) / batch_size; BatchNormalization in training mode
+# normalises with the (biased) batch statistics over ALL node rows of the batch and moves the running
+# statistics with momentum 0.99; Adam is the Keras 2.11 update with epsilon 1e-7.
+BN_MOMENTUM = 0.99
+ADAM_B1, ADAM_B2, ADAM_EPS = 0.9, 0.999, 1e-7
+TRAINABLE_EXCLUDE = ("gcn_layer/batch_norm/moving_mean", "gcn_layer/batch_norm/moving_variance")
+
+
+def _general_conv_train(features, edge_index, w):
+    z = features @ w["gcn_layer/kernel"] + w["gcn_layer/bias"]
+    mu = z.mean(dim=0)
+    var = z.var(dim=0, unbiased=False)
+    zn = (z - mu) / torch.sqrt(var + BN_EPS)
+    z = zn * w["gcn_layer/batch_norm/gamma"] + w["gcn_layer/batch_norm/beta"]
+    alpha = w["gcn_layer/activation/alpha"]
+    z = torch.clamp(z, min=0) + alpha * torch.clamp(z, max=0)
+    tgt, src = edge_index[:, 0], edge_index[:, 1]
+    n = features.shape[0]
+    summed = torch.zeros((n, z.shape[1]), dtype=z.dtype).index_add_(0, tgt, z[src])
+    count = torch.zeros(n, dtype=z.dtype).index_add_(0, tgt, torch.ones(tgt.shape[0], dtype=z.dtype))
+    return summed / torch.clamp(count, min=1).unsqueeze(1), mu.detach(), var.detach()
+
+
+def _logits_head(x, w, first):
+    x = torch.nn.functional.leaky_relu(x @ w[first + "/kernel"] + w[first + "/bias"], LEAKY)
+    x = torch.nn.functional.leaky_relu(x @ w["dense2/kernel"] + w["dense2/bias"], LEAKY)
+    return x @ w["dense_out/kernel"] + w["dense_out/bias"]
+
+
+def loss_and_grads(weights, labels, class_weights, forward_logits, global_batch=None):
+    """weights: dict of leaf tensors (requires_grad on the trainable ones).  Returns (loss, grads)."""
+    logits = forward_logits(weights).reshape(-1)
+    y = labels.to(logits.dtype)
+    sw = torch.where(labels > 0, torch.as_tensor(class_weights[1], dtype=logits.dtype), torch.as_tensor(class_weights[0], dtype=logits.dtype))
+    bce = torch.nn.functional.binary_cross_entropy_with_logits(logits, y, reduction="none")
+    n = global_batch if global_batch is not None else labels.numel()
+    loss = (sw * bce).sum() / n
+    names = [k for k in weights if k not in TRAINABLE_EXCLUDE]
+    grads = torch.autograd.grad(loss, [weights[k] for k in names], allow_unused=True)
+    return loss.detach(), {k: (g if g is not None else torch.zeros_like(weights[k])) for k, g in zip(names, grads)}
+
+
+def train_grads_cml(features, anom, edge_index, sample_indices, labels, named, class_weights=(1.0, 5.0), dtype=torch.float64):
+    """One training-mode forward/backward of the CML GCN model.  Returns (loss, grads dict,
+    batch mean, batch variance of the GeneralConv pre-normalisation activations)."""
+    w = {k: torch.as_tensor(np.asarray(v)).to(dtype).clone().requires_grad_(k not in TRAINABLE_EXCLUDE) for k, v in named.items()}
+    stats = {}
+
+    def fwd(w):
+        B, T = anom.shape[0], anom.shape[1]
+        x, mu, var = _general_conv_train(features.to(dtype), edge_index, w)
+        stats["mean"], stats["var"] = mu, var
+        x = timeseries_pooling(x, sample_indices, B, T)
+        x = torch.cat([anom.to(dtype), x], dim=-1)
+        return _logits_head(time_layer(x, w, "time_layer/"), w, "dense")
+
+    loss, grads = loss_and_grads(w, labels, class_weights, fwd)
+    return loss, grads, stats["mean"], stats["var"]
+
+
+def train_grads_baseline(x, labels, named, class_weights=(1.0, 5.0), dtype=torch.float64):
+    w = {k: torch.as_tensor(np.asarray(v)).to(dtype).clone().requires_grad_(True) for k, v in named.items()}
+    return loss_and_grads(w, labels, class_weights, lambda w: _logits_head(time_layer(x.to(dtype), w, ""), w, "dense1"))
+
+
+def adam_update(param, grad, m, v, step, lr):
+    """Keras 2.11 Adam: step counts from 1."""
+    m = ADAM_B1 * m + (1 - ADAM_B1) * grad
+    v = ADAM_B2 * v + (1 - ADAM_B2) * grad * grad
+    lr_t = lr * np.sqrt(1 - ADAM_B2 ** step) / (1 - ADAM_B1 ** step)
+    return param - lr_t * m / (torch.sqrt(v) + ADAM_EPS), m, v

@@ -1,0 +1,144 @@
+"""GPU parity of the training step (gnnqc_train_*) against the CPU oracle (torch autograd through
+the training-mode restatement of the model, float64).  Gradients are compared per parameter tensor
+with |err| <= 2e-4 * max|grad of that tensor| + 1e-3 * |grad| (fp32 accumulation over up to 162
+steps x 64 windows); the loss with 1e-5 relative."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import gnnqc_oracle as O
+from conftest import MODELS
+from gnnqc import NativeModel, synth
+
+pytestmark = pytest.mark.gpu
+
+
+def cuda(batch):
+    return {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+
+
+def split_rvec(model, rvec):
+    flat = rvec[: model.n_params].cpu().numpy()
+    grads = {p: flat[o: o + int(np.prod(s))].reshape(s) for p, o, s, _ in model.segments()}
+    return grads, float(rvec[-1].item())
+
+
+def check_grads(got, want, skip=()):
+    for name, g in want.items():
+        if name in skip:
+            continue
+        w = g.numpy() if isinstance(g, torch.Tensor) else g
+        err = np.abs(got[name].astype(np.float64) - w)
+        tol = 2e-4 * np.abs(w).max() + 1e-3 * np.abs(w) + 1e-9
+        assert (err <= tol).all(), "%s: max err %.3e vs max |g| %.3e" % (name, err.max(), np.abs(w).max())
+
+
+def make_labels(n, seed):
+    g = torch.Generator().manual_seed(seed)
+    lab = (torch.rand(n, generator=g) < 0.3).long()
+    lab[0], lab[-1] = 1, 0
+    return lab
+
+
+@pytest.mark.parametrize("n,ragged", [(6, False), (70, True)])
+def test_gcn_gradients_match_oracle(n, ragged):
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    try:
+        batch = synth.make_cml_batch(n, seed=40 + n, n_nodes=6, ragged=ragged, min_nodes=3)
+        labels = make_labels(n, n)
+        b = cuda(batch)
+        mom = m.train_moments_cml(b["features"])
+        rvec = m.train_grads_cml(b["features"], b["anom"], b["edges"], b["node_off"], b["edge_off"], labels.cuda(), mom)
+        fin = rvec.clone()
+        m.train_apply(fin, mom, 1e-4)      # closes the BN backward: `fin` now holds the GeneralConv gradients too
+        got, loss = split_rvec(m, fin)
+        feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 2)
+        named = NativeModel.load(os.path.join(MODELS, "model_cml"), device=None).named_params()
+        oloss, ograds, mu, var = O.train_grads_cml(torch.tensor(feat), batch["anom"], torch.tensor(idx), torch.tensor(samp), labels, named)
+        assert abs(loss - oloss.item()) <= 1e-5 * abs(oloss.item()) + 1e-7
+        check_grads(got, ograds, skip=("gcn_layer/bias",))
+        assert np.abs(got["gcn_layer/bias"]).max() == 0.0     # exactly zero in front of batch-stat BN
+        # BN moving statistics moved towards the batch statistics with momentum 0.99
+        new = m.named_params()
+        np.testing.assert_allclose(new["gcn_layer/batch_norm/moving_mean"], 0.99 * named["gcn_layer/batch_norm/moving_mean"] + 0.01 * mu.numpy(), rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(new["gcn_layer/batch_norm/moving_variance"], 0.99 * named["gcn_layer/batch_norm/moving_variance"] + 0.01 * var.numpy(), rtol=1e-4, atol=1e-7)
+    finally:
+        m.close()
+
+
+def test_baseline_gradients_and_adam_step():
+    m = NativeModel.load(os.path.join(MODELS, "model_cml_baseline"), device=0)
+    try:
+        n = 90
+        x = synth.make_seq_batch(n, 2, 181, seed=8)
+        labels = make_labels(n, 1)
+        before = m.get_params()
+        rvec = m.train_grads_seq(x.cuda(), labels.cuda())
+        got, loss = split_rvec(m, rvec)
+        named = NativeModel.load(os.path.join(MODELS, "model_cml_baseline"), device=None).named_params()
+        oloss, ograds = O.train_grads_baseline(x, labels, named)
+        assert abs(loss - oloss.item()) <= 1e-5 * abs(oloss.item()) + 1e-7
+        check_grads(got, ograds)
+        # Adam, first step, from the GPU's own gradients
+        g = rvec[: m.n_params].cpu().numpy().astype(np.float64)
+        m.train_apply(rvec, None, 1e-4)
+        after = m.get_params()
+        mm, vv = 0.1 * g, 0.001 * g * g
+        lr_t = 1e-4 * np.sqrt(1 - 0.999) / (1 - 0.9)
+        want = before - lr_t * mm / (np.sqrt(vv) + 1e-7)
+        np.testing.assert_allclose(after, want, rtol=0, atol=2e-7)
+    finally:
+        m.close()
+
+
+def test_data_parallel_decomposition_is_exact_enough():
+    """Two 'ranks' with half the batch each: summed moments and summed reduction vectors give the
+    full-batch gradients (this is what the NCCL all-reduce does across GPUs)."""
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    try:
+        n = 128
+        full = synth.make_cml_batch(n, seed=3, n_nodes=5)
+        labels = make_labels(n, 2)
+        b = cuda(full)
+        mom = m.train_moments_cml(b["features"])
+        ref = m.train_grads_cml(b["features"], b["anom"], b["edges"], b["node_off"], b["edge_off"], labels.cuda(), mom)
+        T, N = 181, 5
+        parts, moms = [], []
+        for lo, hi in ((0, 64), (64, 128)):
+            eo = full["edge_off"]
+            sub = {"features": b["features"][lo * T * N: hi * T * N], "anom": b["anom"][lo:hi],
+                   "edges": b["edges"][eo[lo]: eo[hi]], "node_off": (b["node_off"][lo: hi + 1] - b["node_off"][lo]).contiguous(),
+                   "edge_off": (b["edge_off"][lo: hi + 1] - b["edge_off"][lo]).contiguous()}
+            parts.append(sub)
+            moms.append(m.train_moments_cml(sub["features"]))
+        gmom = moms[0] + moms[1]
+        torch.testing.assert_close(gmom, mom, rtol=1e-12, atol=1e-9)
+        total = None
+        for (lo, hi), sub in zip(((0, 64), (64, 128)), parts):
+            r = m.train_grads_cml(sub["features"], sub["anom"], sub["edges"], sub["node_off"], sub["edge_off"], labels[lo:hi].cuda(), gmom,
+                                  global_batch=n)
+            total = r if total is None else total + r
+        scale = ref.abs().max().item()
+        assert (total - ref).abs().max().item() <= 2e-5 * scale
+    finally:
+        m.close()
+
+
+def test_loss_goes_down_on_a_fixed_batch():
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    try:
+        batch = cuda(synth.make_cml_batch(64, seed=12, n_nodes=8))
+        labels = make_labels(64, 5).cuda()
+        losses = []
+        for _ in range(12):
+            mom = m.train_moments_cml(batch["features"])
+            rvec = m.train_grads_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"], labels, mom)
+            losses.append(float(rvec[-1].item()))
+            m.train_apply(rvec, mom, 5e-4)
+        assert losses[-1] < losses[0]
+        s = m.score_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"])
+        assert torch.isfinite(s).all()
+    finally:
+        m.close()
