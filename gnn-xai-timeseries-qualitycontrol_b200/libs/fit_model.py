@@ -1,0 +1,135 @@
+"""Drop-in for the reference's libs/fit_model.py (calculate_weights :8-25, MCC_custom :28-58,
+train_model :61-112): same function names and config keys; the train step itself runs in
+libgnnqc.so (gnnqc_train_*), data-parallel over torch.distributed when a process group is up.
+
+Differences that follow from not having Keras: batches are python iterables of
+(inputs, labels) with inputs in the offsets layout of include/gnnqc.h (dict) or the plain
+[B,T,2] tensor of the baseline; metrics are computed on the host with scikit-learn at epoch end;
+PlotLossesKeras is dropped.  The optimiser is Adam only (the shipped configs use 'adam').
+"""
+import copy
+
+import numpy as np
+import torch
+from sklearn.metrics import matthews_corrcoef
+
+from gnnqc import dp
+
+
+def calculate_weights(model_config, train_dataset_batched):
+    wc = model_config.weight_classes
+    if not wc.use:
+        return None
+    if wc.calculate:
+        flags = np.concatenate([np.asarray(torch.as_tensor(b[1]).cpu()).reshape(-1) for b in train_dataset_batched])
+        total, positives = len(flags), flags.sum()
+        return {0: total / (total - positives), 1: 2 * total / positives}
+    if wc.class_0 is not None and wc.class_1 is not None:
+        return {0: wc.class_0, 1: wc.class_1}
+    return {0: 1, 1: 5}
+
+
+def mcc_metric(y_true, y_pred, threshold=0.5):
+    return matthews_corrcoef(np.asarray(y_true).reshape(-1), (np.asarray(y_pred).reshape(-1) > threshold).astype(np.int64))
+
+
+class MCC_custom:
+    """Epoch-end MCC on the training (and validation) batches, like the reference's callback."""
+
+    def __init__(self, train, validation=None):
+        self.train, self.validation = train, validation
+
+    def on_epoch_end(self, model, logs):
+        def score(batches):
+            y = np.concatenate([np.asarray(torch.as_tensor(b[1]).cpu()).reshape(-1) for b in batches])
+            return mcc_metric(y, model.predict(batches))
+        logs["MCC_score_train"] = np.round(score(self.train), 5)
+        if self.validation:
+            logs["MCC_score_val"] = np.round(score(self.validation), 5)
+
+
+def learning_rate_for_epoch(model_config, epoch, lr):
+    """LearningRateScheduler(scheduler) of the reference (:96-102): from epoch `after_epochs` on the
+    current rate is multiplied by `rate` at every epoch start."""
+    sch = model_config.learning_learn_scheduler
+    if sch.use and epoch >= sch.after_epochs:
+        return lr * sch.rate
+    return lr
+
+
+def _bce_from_scores(p, y, class_weights):
+    p = np.clip(np.asarray(p, dtype=np.float64).reshape(-1), 1e-7, 1 - 1e-7)
+    y = np.asarray(y, dtype=np.float64).reshape(-1)
+    w = np.where(y > 0, class_weights[1], class_weights[0]) if class_weights else 1.0
+    return float(np.mean(w * -(y * np.log(p) + (1 - y) * np.log(1 - p))))
+
+
+def train_step(native, inputs, labels, class_weights, lr):
+    """One optimisation step on one global batch; returns the (global) loss.  Works for one process
+    or for every rank of a torch.distributed group (each rank passes the same global batch and
+    works on its own shard)."""
+    rank, world_size = dp.world()
+    dev = torch.device("cuda", native.device)
+    cw = (class_weights[0], class_weights[1]) if class_weights else (1.0, 1.0)
+    labels = torch.as_tensor(labels).to(torch.int64)
+    if native.has_gcn:
+        B = inputs["anom"].shape[0]
+        sub, lab = dp.shard_cml_batch(inputs, labels, rank, world_size)
+        sub = {k: (v.to(dev, non_blocking=True) if isinstance(v, torch.Tensor) else v) for k, v in sub.items()}
+        moments = native.train_moments_cml(sub["features"])
+        dp.all_reduce_sum(moments)
+        rvec = native.train_grads_cml(sub["features"], sub["anom"], sub["edges"], sub["node_off"].to(torch.int32), sub["edge_off"],
+                                      lab.to(dev), moments, cw, global_batch=B, n_nodes_total=sub["n_nodes_total"])
+        dp.all_reduce_sum(rvec)
+        native.train_apply(rvec, moments, lr)
+    else:
+        x = torch.as_tensor(inputs)
+        B = x.shape[0]
+        xs, lab = dp.shard_seq_batch(x, labels, rank, world_size)
+        rvec = native.train_grads_seq(xs.to(dev, dtype=torch.float32), lab.to(dev), cw, global_batch=B)
+        dp.all_reduce_sum(rvec)
+        native.train_apply(rvec, None, lr)
+    return float(rvec[-1].item())
+
+
+def train_model(model, model_config, preproc_config, train_dataset_batched, val_dataset_batched=None, baseline=False,
+                classes_weights=None, labels=None, checkpoint_path=None):
+    """Returns (history, model).  history: dict of per-epoch lists (loss, val_loss, lr, MCC_score_*)."""
+    if model_config.optimizer != "adam":
+        raise NotImplementedError("only optimizer='adam' is built")
+    classes_weights = calculate_weights(model_config, train_dataset_batched)
+    train_batches = list(train_dataset_batched)
+    val_batches = list(val_dataset_batched) if val_dataset_batched is not None else None
+    history = {"loss": [], "val_loss": [], "lr": []}
+    lr = float(model_config.learning_rate)
+    best, best_params, since_best = np.inf, None, 0
+    mcc = MCC_custom(train_batches, val_batches) if model_config.get("mcc_callback", False) else None
+    for epoch in range(int(model_config.epochs)):
+        lr = learning_rate_for_epoch(model_config, epoch, lr)
+        losses = [train_step(model.native, inputs, lab, classes_weights, lr) for inputs, lab in train_batches]
+        logs = {"loss": float(np.mean(losses)), "lr": lr}
+        if val_batches:
+            p = model.predict(val_batches)
+            y = np.concatenate([np.asarray(torch.as_tensor(b[1]).cpu()).reshape(-1) for b in val_batches])
+            logs["val_loss"] = _bce_from_scores(p, y, None)
+        if mcc:
+            mcc.on_epoch_end(model, logs)
+        for k, v in logs.items():
+            history.setdefault(k, []).append(v)
+        print("Epoch %d/%d - %s" % (epoch + 1, int(model_config.epochs), " - ".join("%s: %.5g" % kv for kv in logs.items())))
+        # EarlyStopping(monitor='val_loss', patience, restore_best_weights=True) + ModelCheckpoint(save_best_only)
+        monitored = logs.get("val_loss")
+        if monitored is not None:
+            if monitored < best:
+                best, since_best = monitored, 0
+                best_params = copy.deepcopy(model.native.get_params())
+                if checkpoint_path and dp.world()[0] == 0:
+                    model.save(checkpoint_path)
+            else:
+                since_best += 1
+                if since_best >= int(model_config.es_patience):
+                    print("Early stopping at epoch %d" % (epoch + 1))
+                    break
+    if best_params is not None and since_best > 0:
+        model.native.set_params(best_params)
+    return history, model

@@ -1,0 +1,104 @@
+"""Host-side data-parallel logic over a world_size-2 gloo group on CPU: shards partition the batch,
+the two all-reduces of the training step reproduce the single-process sums, and the epoch logic
+(learning-rate schedule, class weights) matches the reference's rules."""
+import os
+import socket
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from gnnqc import dp, synth
+from gnnqc.config import default_model_config
+from libs import fit_model
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+def _worker(rank, world_size, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world_size)
+    try:
+        batch = synth.make_cml_batch(11, seed=1, ragged=True)
+        labels = torch.arange(11) % 2
+        sub, lab = dp.shard_cml_batch(batch, labels, rank, world_size)
+        # stand-in for the device step: "moments" and a "reduction vector" that are plain sums over
+        # the shard, so the all-reduced result must equal the full-batch sums
+        f = sub["features"].double()
+        moments = torch.stack([f[:, 0].sum(), f[:, 1].sum(), (f[:, 0] ** 2).sum(), (f[:, 1] ** 2).sum(), (f[:, 0] * f[:, 1]).sum(),
+                               torch.tensor(float(f.shape[0]), dtype=torch.float64)])
+        dp.all_reduce_sum(moments)
+        rvec = torch.stack([sub["anom"].sum(), lab.float().sum(), torch.tensor(float(sub["anom"].shape[0]))])
+        dp.all_reduce_sum(rvec)
+        n = dp.global_count(sub["anom"].shape[0])
+        out[rank] = (moments.numpy(), rvec.numpy(), n, int(sub["node_off"][-1]), sub["edges"].shape[0], dp.world())
+    finally:
+        dist.destroy_process_group()
+
+
+def test_two_rank_gloo_all_reduce_matches_single_process():
+    port = _free_port()
+    mgr = mp.Manager()
+    out = mgr.dict()
+    mp.spawn(_worker, args=(2, port, out), nprocs=2, join=True)
+    batch = synth.make_cml_batch(11, seed=1, ragged=True)
+    labels = torch.arange(11) % 2
+    f = batch["features"].double()
+    want_m = np.array([f[:, 0].sum(), f[:, 1].sum(), (f[:, 0] ** 2).sum(), (f[:, 1] ** 2).sum(), (f[:, 0] * f[:, 1]).sum(), f.shape[0]])
+    for rank in (0, 1):
+        m, r, n, nodes, edges, w = out[rank]
+        np.testing.assert_allclose(m, want_m, rtol=1e-12)
+        np.testing.assert_allclose(r, [batch["anom"].sum().item(), labels.sum().item(), 11], rtol=1e-5)
+        assert n == 11 and w == (rank, 2)
+    assert out[0][3] + out[1][3] == int(batch["node_off"][-1])
+    assert out[0][4] + out[1][4] == batch["edges"].shape[0]
+
+
+def test_shards_partition_every_batch_size():
+    for n in (1, 2, 7, 64, 129):
+        for ws in (1, 2, 4, 8):
+            r = [dp.shard_range(n, k, ws) for k in range(ws)]
+            assert r[0][0] == 0 and r[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(r, r[1:]))
+            assert max(h - l for l, h in r) - min(h - l for l, h in r) <= 1
+
+
+def test_shard_contents_are_the_original_windows():
+    batch = synth.make_cml_batch(9, seed=4, ragged=True)
+    labels = torch.arange(9)
+    T = 181
+    seen = []
+    for rank in range(4):
+        sub, lab = dp.shard_cml_batch(batch, labels, rank, 4)
+        lo, hi = dp.shard_range(9, rank, 4)
+        assert torch.equal(lab, labels[lo:hi]) and torch.equal(sub["anom"], batch["anom"][lo:hi])
+        n0 = int(batch["node_off"][lo])
+        assert torch.equal(sub["features"], batch["features"][n0 * T: int(batch["node_off"][hi]) * T])
+        assert int(sub["node_off"][0]) == 0 and int(sub["edge_off"][0]) == 0
+        seen.append(sub["anom"].shape[0])
+    assert sum(seen) == 9
+
+
+def test_schedule_and_class_weights_follow_the_reference_rules():
+    mc = default_model_config()
+    lr = mc.learning_rate
+    lrs = []
+    for epoch in range(8):
+        lr = fit_model.learning_rate_for_epoch(mc, epoch, lr)
+        lrs.append(lr)
+    np.testing.assert_allclose(lrs[:5], [1e-4] * 5)
+    np.testing.assert_allclose(lrs[5:], [1e-4 * 0.95, 1e-4 * 0.95 ** 2, 1e-4 * 0.95 ** 3])
+    assert fit_model.calculate_weights(mc, []) == {0: 1, 1: 5}
+    mc.weight_classes.calculate = True
+    w = fit_model.calculate_weights(mc, [(None, torch.tensor([0, 0, 0, 1])), (None, torch.tensor([0, 1, 0, 0]))])
+    assert w == {0: 8 / 6, 1: 2 * 8 / 2}
+    mc.weight_classes.use = False
+    assert fit_model.calculate_weights(mc, []) is None
