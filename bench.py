@@ -1,7 +1,8 @@
 #!/usr/bin/env python
 """bench.py - windows scored per second by the CML GCN model (BASELINE.json configs[0]) on N B200s.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference] [--workload cml_gcn|cml_baseline]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+                    [--workload cml_gcn|cml_baseline|soilnet_gcn|ig|train]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
 One "step" = one pass of the scoring hot path over one batch of synthetic CML-shaped windows
@@ -13,6 +14,10 @@ One "step" = one pass of the scoring hot path over one batch of synthetic CML-sh
   cpu_baseline  the CPU oracle (torch fp32, all host cores) on a bounded sample - "port", since
             the reference's TensorFlow path is not installable here
 --impl reference times that CPU oracle alone (the reference's own CPU implementation is unavailable).
+
+Other workloads (not the driver's default line): cml_baseline (configs[1]), soilnet_gcn (configs[2],
+210-sensor windows, unit = sensor-sequences/s), ig (configs[3], 50 interpolation steps, unit =
+attributions/s), train (configs[4], data-parallel training step, unit = windows/s).
 """
 import argparse
 import json
@@ -28,6 +33,9 @@ sys.path.insert(0, os.path.join(ROOT, "gnn-xai-timeseries-qualitycontrol_b200"))
 MODELS = os.path.join(ROOT, "tests", "golden", "models")
 T_CML, N_NODES = 181, 23
 METRIC = "cml_windows_scored_per_sec"
+METRICS = {"cml_gcn": ("cml_windows_scored_per_sec", "windows/s"), "cml_baseline": ("cml_baseline_windows_scored_per_sec", "windows/s"),
+           "soilnet_gcn": ("soilnet_sensor_sequences_scored_per_sec", "sequences/s"), "ig": ("cml_ig_attributions_per_sec", "attributions/s"),
+           "train": ("cml_gcn_training_windows_per_sec", "windows/s")}
 
 # Algorithmic FLOPs (2*MACs of every matmul) per window and per kernel.
 LSTM_SHAPES = {"cml_gcn": [(181, 18, 16), (181, 16, 16), (60, 16, 32), (60, 32, 32), (20, 32, 64), (20, 64, 64), (6, 64, 128)],
@@ -177,8 +185,9 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gnnqc", choices=["gnnqc", "reference"])
-    ap.add_argument("--workload", default="cml_gcn", choices=["cml_gcn", "cml_baseline"])
-    ap.add_argument("--windows", type=int, default=65536, help="windows per GPU per step")
+    ap.add_argument("--workload", default="cml_gcn", choices=sorted(METRICS))
+    ap.add_argument("--windows", type=int, default=0, help="units per GPU per step (0 = workload default)")
+    ap.add_argument("--m-steps", type=int, default=50, help="IG interpolation steps")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "gnnqc" else args.warmup
@@ -187,13 +196,15 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     if args.impl == "reference":
+        if args.workload not in ("cml_gcn", "cml_baseline"):
+            args.workload = "cml_gcn"
         run_reference(args, rank, world)
         return
 
     import torch
     import torch.distributed as dist
 
-    from gnnqc import NativeModel, synth
+    from gnnqc import NativeModel, dp, synth
     from gnnqc._lib import lib
     from gnnqc.host_pipeline import CmlHostScorer, SeqHostScorer
 
@@ -201,20 +212,54 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    gcn = args.workload == "cml_gcn"
-    model = NativeModel.load(os.path.join(MODELS, "model_cml" if gcn else "model_cml_baseline"), device=local_rank)
-    B = args.windows
+    wl = args.workload
+    metric, unit = METRICS[wl]
+    model_name = {"cml_gcn": "model_cml", "ig": "model_cml", "train": "model_cml", "cml_baseline": "model_cml_baseline",
+                  "soilnet_gcn": "model_soilnet"}[wl]
+    model = NativeModel.load(os.path.join(MODELS, model_name), device=local_rank)
+    B = args.windows or {"cml_gcn": 65536, "cml_baseline": 65536, "soilnet_gcn": 256, "ig": 16384, "train": 4096}[wl]
+    T = T_CML
+    cfg_extra = {}
+    e2e_path = None
 
-    # Synthetic inputs, generated on the device (weak scaling: every rank has its own B windows).
-    if gcn:
+    # Synthetic inputs, generated on the device (weak scaling: every rank has its own B units per step).
+    if wl in ("cml_gcn", "ig", "train"):
         batch = synth.make_cml_batch(B, seed=44 + rank, n_nodes=N_NODES, device=str(dev))
         n_nodes_total = B * N_NODES
-        step = lambda: model.score_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"], n_nodes_total)  # noqa: E731
-        in_bytes = sum(batch[k].numel() * batch[k].element_size() for k in ("features", "anom", "edges", "node_off", "edge_off"))
-    else:
+        keys = ("features", "anom", "edges", "node_off", "edge_off")
+        in_bytes = sum(batch[k].numel() * batch[k].element_size() for k in keys)
+        units = B
+        if wl == "cml_gcn":
+            step = lambda: model.score_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"], n_nodes_total)  # noqa: E731
+        elif wl == "ig":
+            cfg_extra["m_steps"] = args.m_steps
+            step = lambda: model.ig_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"], args.m_steps, n_nodes_total)[2]  # noqa: E731
+        else:
+            labels = (torch.rand(B, device=dev) < 1.0 / 6.0).long()      # 16.7 % positives
+            cfg_extra.update({"class_weights": [1, 5], "optimizer": "adam", "learning_rate": 1e-4, "global_batch": B * world,
+                              "collectives_per_step": "all-reduce of 6 f64 moments + all-reduce of the %d-float reduction vector" % model.train_vector_len()})
+
+            def step():
+                mom = model.train_moments_cml(batch["features"])
+                dp.all_reduce_sum(mom)
+                rvec = model.train_grads_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"], labels, mom,
+                                             (1.0, 5.0), global_batch=B * world, n_nodes_total=n_nodes_total)
+                dp.all_reduce_sum(rvec)
+                model.train_apply(rvec, mom, 1e-4)
+                return rvec[-1:]
+    elif wl == "cml_baseline":
         x = synth.make_seq_batch(B, 2, T_CML, seed=44 + rank, device=str(dev))
         step = lambda: model.score_seq(x)  # noqa: E731
-        in_bytes = x.numel() * 4
+        in_bytes, units = x.numel() * 4, B
+    else:  # soilnet_gcn: B windows of 210 sensors, T = 337
+        T = 337
+        batch = synth.make_soilnet_batch(B, seed=44 + rank, n_nodes=210, device=str(dev))
+        n_nodes_total = B * 210
+        keys = ("features", "edges", "node_off", "edge_off")
+        in_bytes = sum(batch[k].numel() * batch[k].element_size() for k in keys)
+        units = n_nodes_total
+        cfg_extra.update({"windows_per_gpu_per_step": B, "sensors_per_window": 210})
+        step = lambda: model.score_soilnet(batch["features"], batch["edges"], batch["node_off"], batch["edge_off"], T, n_nodes_total)  # noqa: E731
 
     def barrier():
         if world > 1:
@@ -223,7 +268,7 @@ def main():
 
     # ---- device-resident timing -------------------------------------------------------------
     for _ in range(args.warmup):
-        scores = step()
+        result = step()
     barrier()
     launches0 = model.launch_count()
     sampler = ClockSampler(local_rank)
@@ -232,7 +277,7 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
-        scores = step()
+        result = step()
     e1.record()
     barrier()
     ms_total = e0.elapsed_time(e1)
@@ -242,24 +287,53 @@ def main():
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     ms_step = float(t.item()) / args.steps
-    value = world * B / (ms_step * 1e-3)
+    value = world * units / (ms_step * 1e-3)
 
-    # ---- per-kernel timing (same steps, events around every launch) ----------------------------
+    # ---- per-kernel timing (events around every launch; not for the training loop, whose state moves) ----
+    prof = {}
+    prof_steps = args.steps if wl != "ig" else 1
     model.profile(True)
-    for _ in range(args.steps):
+    for _ in range(prof_steps):
         step()
     prof = model.profile_read()
     model.profile(False)
 
     # ---- end to end from pinned host buffers ----------------------------------------------------
-    if gcn:
-        host = {k: batch[k].cpu().pin_memory() for k in ("features", "anom", "edges", "node_off", "edge_off")}
+    h2d = d2h = 0
+    if wl == "cml_gcn":
+        host = {k: batch[k].cpu().pin_memory() for k in keys}
         scorer = CmlHostScorer(model, chunk_windows=8192)
         e2e_step = lambda: scorer.score(host["features"], host["anom"], host["edges"], host["node_off"], host["edge_off"])  # noqa: E731
-    else:
+        e2e_path = "CmlHostScorer (pinned host -> chunked H2D on a copy stream -> gnnqc_score_cml -> D2H)"
+    elif wl == "cml_baseline":
         host_x = x.cpu().pin_memory()
         scorer = SeqHostScorer(model, chunk_seqs=16384)
         e2e_step = lambda: scorer.score(host_x)  # noqa: E731
+        e2e_path = "SeqHostScorer"
+    else:
+        host = {k: batch[k].cpu().pin_memory() for k in keys}
+        scorer = None
+        if wl == "train":
+            host_labels = labels.cpu().pin_memory()
+
+        def e2e_step():
+            d = {k: host[k].to(dev, non_blocking=True) for k in keys}
+            if wl == "soilnet_gcn":
+                return model.score_soilnet(d["features"], d["edges"], d["node_off"], d["edge_off"], T, n_nodes_total).cpu()
+            if wl == "ig":
+                af, aa, p = model.ig_cml(d["features"], d["anom"], d["edges"], d["node_off"], d["edge_off"], args.m_steps, n_nodes_total)
+                return af.cpu(), aa.cpu(), p.cpu()
+            lab = host_labels.to(dev, non_blocking=True)
+            mom = model.train_moments_cml(d["features"])
+            dp.all_reduce_sum(mom)
+            rvec = model.train_grads_cml(d["features"], d["anom"], d["edges"], d["node_off"], d["edge_off"], lab, mom, (1.0, 5.0),
+                                         global_batch=B * world, n_nodes_total=n_nodes_total)
+            dp.all_reduce_sum(rvec)
+            model.train_apply(rvec, mom, 1e-4)
+            return rvec[-1:].cpu()
+        h2d = in_bytes + (B * 8 if wl == "train" else 0)
+        d2h = {"soilnet_gcn": n_nodes_total * 4, "ig": batch["features"].numel() * 4 + (batch["anom"].numel() * 4 if wl == "ig" else 0) + B * 4, "train": 4}[wl]
+        e2e_path = "pinned host -> H2D -> %s -> D2H of the result" % {"soilnet_gcn": "gnnqc_score_soilnet", "ig": "gnnqc_ig_cml", "train": "gnnqc_train_*"}[wl]
     for _ in range(2):
         out = e2e_step()
     barrier()
@@ -272,16 +346,18 @@ def main():
     t = torch.tensor([dt], device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    e2e_value = world * B * e2e_steps / float(t.item())
-    if not torch.equal(out.cuda(dev), scores):
-        raise SystemExit("e2e scores differ from the device-resident scores")
+    e2e_value = world * units * e2e_steps / float(t.item())
+    if scorer is not None:
+        h2d, d2h = scorer.last_h2d_bytes, scorer.last_d2h_bytes
+        if not torch.equal(out.cuda(dev), result):
+            raise SystemExit("e2e scores differ from the device-resident scores")
 
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    # ---- roofline of the dominant kernel ----------------------------------------------------------
+    # ---- roofline ------------------------------------------------------------------------------------
     peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     hbm_peak, hbm_src = 6650.0, "fallback"
     if os.path.exists(peaks_path):
@@ -289,44 +365,60 @@ def main():
     import ctypes as C
     fp32 = C.c_double()
     lib.gnnqc_probe_fp32_peak(local_rank, 1, C.byref(fp32))
-    fl_alg, fl_live = layer_flops(args.workload), layer_flops(args.workload, live=True)
+    shapes = "cml_baseline" if wl == "cml_baseline" else "cml_gcn"
+    if wl == "soilnet_gcn":
+        fl_alg = [2 * t_ * (i_ + h_) * 4 * h_ for t_, i_, h_ in [(337, 19, 16), (337, 16, 16), (112, 16, 32), (112, 32, 32), (37, 32, 64), (37, 64, 64), (12, 64, 128)]]
+        fl_live = [2 * t_ * (i_ + h_) * 4 * h_ for t_, i_, h_ in [(324, 19, 16), (324, 16, 16), (108, 16, 32), (108, 32, 32), (36, 32, 64), (36, 64, 64), (12, 64, 128)]]
+    else:
+        fl_alg, fl_live = layer_flops(shapes), layer_flops(shapes, live=True)
+    passes = {"ig": args.m_steps + 1}.get(wl, 1)
     kernels = []
     for name, (ms, cnt) in sorted(prof.items(), key=lambda kv: -kv[1][0]):
-        k = {"name": name, "ms_per_step": ms / args.steps, "launches_per_step": cnt / args.steps}
-        if name.startswith("lstm_l"):
+        k = {"name": name, "ms_per_step": ms / prof_steps, "launches_per_step": cnt / prof_steps}
+        if "_l" in name and name[-1].isdigit() and ("lstm" in name or "fwd" in name or "bwd" in name):
             i = int(name[-1]) - 1
-            k["tflops_executed"] = fl_live[i] * B / (ms / args.steps * 1e-3) / 1e12
-            k["tflops_algorithmic"] = fl_alg[i] * B / (ms / args.steps * 1e-3) / 1e12
+            k["tflops_executed"] = fl_live[i] * units * passes / (ms / prof_steps * 1e-3) / 1e12
+            k["tflops_algorithmic"] = fl_alg[i] * units * passes / (ms / prof_steps * 1e-3) / 1e12
         kernels.append(k)
-    top = next(k for k in kernels if k["name"].startswith("lstm_l"))
+    timed = [k for k in kernels if "tflops_executed" in k]
+    top = timed[0]
     total_kernel_ms = sum(k["ms_per_step"] for k in kernels)
+    # whole-step executed FLOPs per unit: forward stack (+ the same again for the input-gradient
+    # backward in ig; + backward + weight gradients in train)
+    step_mult = {"ig": 2 * passes, "train": 3}.get(wl, 1)
+    step_tflops = sum(fl_live) * step_mult * units / (ms_step * 1e-3) / 1e12
+    bpu = {"cml_gcn": bytes_per_window("cml_gcn"), "cml_baseline": bytes_per_window("cml_baseline"), "soilnet_gcn": 4 * 3 * 337 + 4,
+           "ig": 2 * bytes_per_window("cml_gcn"), "train": bytes_per_window("cml_gcn") + 4}[wl]
     roofline = {
         "bound": "fp32", "kernel": top["name"], "achieved": top["tflops_executed"], "peak": fp32.value, "unit": "TFLOP/s",
         "frac": top["tflops_executed"] / fp32.value if fp32.value else None, "traffic": None,
         "peak_source": "gnnqc_probe_fp32_peak (FFMA2 chains) measured in this run",
         "note": "fp32 CUDA-core kernel: compute bound (~190 FLOP/B), so neither HBM nor the tensor pipe is the binding roof; "
                 "achieved counts executed FLOPs (dead steps past 27*6 are skipped); algorithmic = %.2f TFLOP/s" % top["tflops_algorithmic"],
-        "stack": {"tflops_executed": sum(fl_live) * B / (sum(k["ms_per_step"] for k in kernels if k["name"].startswith("lstm_l")) * 1e-3) / 1e12,
-                  "share_of_step": sum(k["ms_per_step"] for k in kernels if k["name"].startswith("lstm_l")) / total_kernel_ms},
-        "hbm": {"achieved": bytes_per_window(args.workload) * B / (ms_step * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
-                "frac": bytes_per_window(args.workload) * B / (ms_step * 1e-3) / 1e9 / hbm_peak, "peak_source": hbm_src},
+        "whole_step": {"tflops_executed": step_tflops, "frac": step_tflops / fp32.value if fp32.value else None,
+                       "lstm_share_of_kernel_time": sum(k["ms_per_step"] for k in timed) / total_kernel_ms},
+        "hbm": {"achieved": bpu * units / (ms_step * 1e-3) / 1e9, "peak": hbm_peak, "unit": "GB/s",
+                "frac": bpu * units / (ms_step * 1e-3) / 1e9 / hbm_peak, "peak_source": hbm_src,
+                "note": "algorithmic bytes (inputs + outputs) per unit: %d" % bpu},
     }
 
     cpu = None
-    if not args.no_cpu_baseline:
-        sample = 128 if gcn else 4096
-        wps, cores, secs = cpu_oracle_throughput(args.workload, sample, repeats=2)
+    if not args.no_cpu_baseline and wl in ("cml_gcn", "cml_baseline"):
+        sample = 128 if wl == "cml_gcn" else 4096
+        wps, cores, secs = cpu_oracle_throughput(wl, sample, repeats=2)
         cpu = {"value": wps, "unit": "windows/s", "cores": cores, "kind": "port",
                "sample": "%d windows, best of 2 after warm-up (%.1f s each); reference TF CPU path unavailable on this box" % (sample, secs)}
 
+    config = {"workload": wl, "model": model_name, "units_per_gpu_per_step": units, "seq_len": T,
+              "nodes_per_window": {"cml_baseline": 1, "soilnet_gcn": 210}.get(wl, N_NODES), "input_bytes_per_step": in_bytes,
+              "l2_policy": "inputs plus inter-layer tiles per step (%.0f MB in, GBs of tiles) exceed the 126 MB L2" % (in_bytes / 1e6),
+              "parallelism": "windows sharded, no collective" if wl != "train" else "data parallel, NCCL all-reduce of moments + gradients"}
+    config.update(cfg_extra)
     line = {
-        "metric": METRIC, "value": value, "unit": "windows/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "metric": metric, "value": value, "unit": unit, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "model": "model_cml" if gcn else "model_cml_baseline", "windows_per_gpu_per_step": B,
-                   "seq_len": T_CML, "nodes_per_window": N_NODES if gcn else 1, "input_bytes_per_step": in_bytes,
-                   "l2_policy": "inputs larger than L2 (%.0f MB per step)" % (in_bytes / 1e6), "parallelism": "windows sharded, no collective"},
-        "e2e": {"value": e2e_value, "unit": "windows/s", "h2d_bytes_per_step": scorer.last_h2d_bytes, "d2h_bytes_per_step": scorer.last_d2h_bytes,
-                "steps": e2e_steps, "path": "CmlHostScorer (pinned host -> chunked H2D on a copy stream -> gnnqc_score_cml -> D2H)" if gcn else "SeqHostScorer"},
+        "config": config,
+        "e2e": {"value": e2e_value, "unit": unit, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h), "steps": e2e_steps, "path": e2e_path},
         "gpu_launches": launches, "clocks": clocks, "roofline": roofline, "kernels": kernels, "cpu_baseline": cpu,
     }
     print(json.dumps(line), flush=True)

@@ -71,3 +71,31 @@ def test_ig_completeness_and_dead_steps(model):
     b = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
     p = model.score_cml(b["features"], b["anom"], b["edges"], b["node_off"], b["edge_off"]).cpu().numpy()
     np.testing.assert_allclose(gp, p, rtol=1e-5, atol=1e-6)
+
+
+def test_explainer_writes_the_six_files_per_sample(model, tmp_path):
+    from gnnqc.config import to_config
+    from libs.create_model import load_model
+    from xai.libs.integrated_gradients import IntegratedGradientsExplainer, split_work
+
+    clf = load_model(os.path.join(MODELS, "model_cml"), device=0)
+    xai = to_config({"output_dir": str(tmp_path), "project": "unit-ig",
+                     "integrated_gradients": {"m_steps": 4, "baseline": "zero", "scale_gradients": True, "negative_values": "keep",
+                                              "threshold": 0.956, "dataset": "test", "which_samples": ["TN", "TP", "FP", "FN"]}})
+    pre = to_config({"ds_type": "cml", "timestep_before": 120, "timestep_after": 60})
+    ex = IntegratedGradientsExplainer(clf, xai, pre)
+    batch = synth.make_cml_batch(5, seed=2, ragged=True, n_nodes=7)
+    meta = ([("cml%d" % i) for i in range(5)], ["20190101_000%d00" % i for i in range(5)], [0, 1, 0, 0, 1])
+    res = ex.get_gradients([batch], meta=[meta])[0]
+    assert len(res["files"]) == 30
+    no = batch["node_off"].numpy()
+    gf, ga, gp = run_gpu(model, batch, 4)
+    for i in range(5):
+        d = [p for p in res["files"] if p.name.startswith("gradients_features_unwrapped_") and ("cml%d_" % i) in p.name]
+        arr = np.load(d[0])
+        n = no[i + 1] - no[i]
+        assert arr.shape == (n, 181, 2)
+        rows = gf[no[i] * 181: no[i + 1] * 181]
+        for k in range(n):                       # the reference's a[i::n_neighbors]
+            np.testing.assert_array_equal(arr[k], rows[k::n])
+    assert split_work(list(range(7)), 1, 3) == [1, 4]
