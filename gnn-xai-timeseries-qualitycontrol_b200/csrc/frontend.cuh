@@ -223,50 +223,51 @@ static __global__ void __launch_bounds__(256) cml_frontend_bwd_kernel(const floa
                                                                       float2* __restrict__ attr_feat, float2* __restrict__ attr_anom,
                                                                       long long n_windows, int T, int t_run, float alpha, float wk,
                                                                       int first) {
-  const int b = threadIdx.x & 63, tq = threadIdx.x >> 6;
-  const long long tile = blockIdx.x;
-  const long long win = tile * kTile + b;
-  const int t0 = blockIdx.y * 32 + tq * 8;
+  // One CTA per window.  Lanes walk the window's feature rows in memory order ((t, n) pairs are
+  // contiguous), so the feature reads and the attribution read-modify-writes are fully coalesced;
+  // the 16 upstream gradients of a row depend on t only and come out of L1 as broadcasts.
+  const long long win = blockIdx.x;
   if (win >= n_windows) return;
+  const long long tile = win / kTile;
+  const int b = static_cast<int>(win % kTile);
   const int n0 = node_off[win];
   const int nn = node_off[win + 1] - n0;
   constexpr int CH = 2 + kGcnChannelsDev;
-#pragma unroll 1
-  for (int dt = 0; dt < 8; ++dt) {
-    const int t = t0 + dt;
-    if (t >= T) break;
-    const long long row0 = static_cast<long long>(n0) * T + static_cast<long long>(t) * nn;
-    if (t >= t_run) {
-      if (first) {
-        for (int n = 0; n < nn; ++n) attr_feat[row0 + n] = make_float2(0.f, 0.f);
-        attr_anom[win * T + t] = make_float2(0.f, 0.f);
-      }
+  const long long row0 = static_cast<long long>(n0) * T;
+  const int live_rows = t_run * nn, all_rows = first ? T * nn : live_rows;
+  const float* gbase = dx1 + (tile * t_run) * CH * kTile + b;
+  for (int r = threadIdx.x; r < all_rows; r += 256) {
+    if (r >= live_rows) {                 // steps that cannot reach the score: attribution 0
+      attr_feat[row0 + r] = make_float2(0.f, 0.f);
       continue;
     }
-    const float* g = dx1 + ((tile * t_run + t) * CH) * kTile + b;
-    float dp[kGcnChannelsDev];
+    const int t = r / nn, n = r - t * nn;
+    const float2 v = __ldg(feat + row0 + r);
+    const float cf = __ldg(coef + n0 + n);
+    const float* g = gbase + static_cast<long long>(t) * CH * kTile;
+    float gx = 0.f, gy = 0.f;
 #pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) dp[c] = g[(2 + c) * kTile];
-    for (int n = 0; n < nn; ++n) {
-      const float2 v = __ldg(feat + row0 + n);
-      const float cf = __ldg(coef + n0 + n);
-      float gx = 0.f, gy = 0.f;
-#pragma unroll
-      for (int c = 0; c < kGcnChannelsDev; ++c) {
-        const float z = fmaf(alpha * v.x, p.a[0][c], fmaf(alpha * v.y, p.a[1][c], p.c[c]));
-        const float s = dp[c] * (z > 0.f ? 1.f : p.alpha[c]);
-        gx = fmaf(s, p.a[0][c], gx);
-        gy = fmaf(s, p.a[1][c], gy);
-      }
-      float2 a = first ? make_float2(0.f, 0.f) : attr_feat[row0 + n];
-      a.x = fmaf(wk * v.x * cf, gx, a.x);
-      a.y = fmaf(wk * v.y * cf, gy, a.y);
-      attr_feat[row0 + n] = a;
+    for (int c = 0; c < kGcnChannelsDev; ++c) {
+      const float z = fmaf(alpha * v.x, p.a[0][c], fmaf(alpha * v.y, p.a[1][c], p.c[c]));
+      const float s = __ldg(g + (2 + c) * kTile) * (z > 0.f ? 1.f : p.alpha[c]);
+      gx = fmaf(s, p.a[0][c], gx);
+      gy = fmaf(s, p.a[1][c], gy);
     }
+    float2 a = first ? make_float2(0.f, 0.f) : attr_feat[row0 + r];
+    a.x = fmaf(wk * v.x * cf, gx, a.x);
+    a.y = fmaf(wk * v.y * cf, gy, a.y);
+    attr_feat[row0 + r] = a;
+  }
+  for (int t = threadIdx.x; t < (first ? T : t_run); t += 256) {
+    if (t >= t_run) {
+      attr_anom[win * T + t] = make_float2(0.f, 0.f);
+      continue;
+    }
+    const float* g = gbase + static_cast<long long>(t) * CH * kTile;
     const float2 av = __ldg(anom + win * T + t);
     float2 a = first ? make_float2(0.f, 0.f) : attr_anom[win * T + t];
-    a.x = fmaf(wk * av.x, g[0], a.x);
-    a.y = fmaf(wk * av.y, g[kTile], a.y);
+    a.x = fmaf(wk * av.x, __ldg(g), a.x);
+    a.y = fmaf(wk * av.y, __ldg(g + kTile), a.y);
     attr_anom[win * T + t] = a;
   }
 }

@@ -191,7 +191,6 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
     const long long nt = std::min(chunk, n_tiles - t0);
     const long long win0 = t0 * kTile, nw = std::min<long long>(B - win0, nt * kTile);
     const dim3 grid_fe(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
-    const dim3 grid_fb(static_cast<unsigned>(nt), static_cast<unsigned>((T + 31) / 32));
     const float2* feat2 = reinterpret_cast<const float2*>(feat);
     const float2* anom2 = reinterpret_cast<const float2*>(anom) + win0 * T;
     for (int k = 0; k <= m_steps; ++k) {
@@ -238,7 +237,7 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
         dy = a.out;
       }
       mark_begin("ig_frontend_bwd", st);
-      cml_frontend_bwd_kernel<<<grid_fb, 256, 0, st>>>(feat2, anom2, coef, node_off + win0, folded, dy,
+      cml_frontend_bwd_kernel<<<static_cast<unsigned>(nw), 256, 0, st>>>(feat2, anom2, coef, node_off + win0, folded, dy,
                                                        reinterpret_cast<float2*>(attr_feat), reinterpret_cast<float2*>(attr_anom) + win0 * T,
                                                        nw, T, plan.t_run[0], alpha, wk, k == 0 ? 1 : 0);
       GNNQC_CUDA(cudaGetLastError());

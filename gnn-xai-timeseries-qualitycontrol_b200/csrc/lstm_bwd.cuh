@@ -30,7 +30,8 @@ struct BwdCfg {
   static constexpr int COLS = 4 * H;
   static constexpr int GROUPS = H * (kTile / 4);          // float4 cell groups per step
   static constexpr int CPG = (GROUPS + NT - 1) / NT;      // groups owned by a thread
-  static constexpr size_t W_FLOATS = WGLOBAL ? 0 : size_t(COLS) * KPAD;
+  static constexpr int CC = 32;                           // WGLOBAL: weight columns per streamed chunk
+  static constexpr size_t W_FLOATS = WGLOBAL ? size_t(2) * CC * KPAD : size_t(COLS) * KPAD;
   static constexpr size_t SMEM_BYTES = (W_FLOATS + size_t(COLS) * kTile + size_t(H) * kTile) * 4;
 };
 
@@ -57,7 +58,7 @@ lstm_layer_bwd_kernel(const float* __restrict__ dy,    // grad wrt this layer's 
     float4* dst = reinterpret_cast<float4*>(wsm);
     for (int i = tid; i < C::COLS * C::KPAD / 4; i += C::NT) dst[i] = __ldg(src + i);
   }
-  const float4* w4 = WGLOBAL ? reinterpret_cast<const float4*>(wT) : reinterpret_cast<const float4*>(wsm);
+  const float4* w4 = reinterpret_cast<const float4*>(wsm);
   // phase-B coordinates
   const int rl = lane & 3, bl = lane >> 2;
   const int row0 = warp * 16 + rl * 4;
@@ -134,15 +135,37 @@ lstm_layer_bwd_kernel(const float* __restrict__ dy,    // grad wrt this layer's 
 #pragma unroll
         for (int i = 0; i < 4; ++i) acc[r][i] = 0ull;
       const ulonglong2* dz2 = reinterpret_cast<const ulonglong2*>(dzs);
+      auto mul_cols = [&](const float4* __restrict__ wbase, int col0, int ncol) {
 #pragma unroll 4
-      for (int col = 0; col < C::COLS; ++col) {
-        const float4 w = WGLOBAL ? __ldg(w4 + (col * C::KPAD + row0) / 4) : w4[(col * C::KPAD + row0) / 4];
-        const ulonglong2 a = dz2[col * (kTile / 4) + bl], b = dz2[col * (kTile / 4) + 8 + bl];
-        const unsigned long long w0 = dup2(w.x), w1 = dup2(w.y), w2 = dup2(w.z), w3 = dup2(w.w);
-        ffma2(acc[0][0], a.x, w0); ffma2(acc[0][1], a.y, w0); ffma2(acc[0][2], b.x, w0); ffma2(acc[0][3], b.y, w0);
-        ffma2(acc[1][0], a.x, w1); ffma2(acc[1][1], a.y, w1); ffma2(acc[1][2], b.x, w1); ffma2(acc[1][3], b.y, w1);
-        ffma2(acc[2][0], a.x, w2); ffma2(acc[2][1], a.y, w2); ffma2(acc[2][2], b.x, w2); ffma2(acc[2][3], b.y, w2);
-        ffma2(acc[3][0], a.x, w3); ffma2(acc[3][1], a.y, w3); ffma2(acc[3][2], b.x, w3); ffma2(acc[3][3], b.y, w3);
+        for (int cc = 0; cc < ncol; ++cc) {
+          const int col = col0 + cc;
+          const float4 w = wbase[(cc * C::KPAD + row0) / 4];
+          const ulonglong2 a = dz2[col * (kTile / 4) + bl], b = dz2[col * (kTile / 4) + 8 + bl];
+          const unsigned long long w0 = dup2(w.x), w1 = dup2(w.y), w2 = dup2(w.z), w3 = dup2(w.w);
+          ffma2(acc[0][0], a.x, w0); ffma2(acc[0][1], a.y, w0); ffma2(acc[0][2], b.x, w0); ffma2(acc[0][3], b.y, w0);
+          ffma2(acc[1][0], a.x, w1); ffma2(acc[1][1], a.y, w1); ffma2(acc[1][2], b.x, w1); ffma2(acc[1][3], b.y, w1);
+          ffma2(acc[2][0], a.x, w2); ffma2(acc[2][1], a.y, w2); ffma2(acc[2][2], b.x, w2); ffma2(acc[2][3], b.y, w2);
+          ffma2(acc[3][0], a.x, w3); ffma2(acc[3][1], a.y, w3); ffma2(acc[3][2], b.x, w3); ffma2(acc[3][3], b.y, w3);
+        }
+      };
+      if (WGLOBAL) {
+        // Transposed weights streamed from L2 in 32-column chunks (double-buffered cp.async).
+        constexpr int CHUNK_F4 = C::CC * C::KPAD / 4, N_CHUNKS = C::COLS / C::CC;
+        auto issue_w = [&](int c) {
+          float4* dst = reinterpret_cast<float4*>(wsm) + (c & 1) * CHUNK_F4;
+          const float4* src = reinterpret_cast<const float4*>(wT) + static_cast<long long>(c) * CHUNK_F4;
+          for (int i = tid; i < CHUNK_F4; i += C::NT) ptx::cp_async16(dst + i, src + i);
+          ptx::cp_async_commit();
+        };
+        issue_w(0);
+        for (int c = 0; c < N_CHUNKS; ++c) {
+          ptx::cp_async_wait<0>();
+          __syncthreads();
+          if (c + 1 < N_CHUNKS) issue_w(c + 1);
+          mul_cols(w4 + (c & 1) * CHUNK_F4, c * C::CC, C::CC);
+        }
+      } else {
+        mul_cols(w4, 0, C::COLS);
       }
       // dhs was last read in phase A (before the barrier above), so it can be overwritten now.
 #pragma unroll

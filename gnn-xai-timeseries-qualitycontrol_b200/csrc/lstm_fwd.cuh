@@ -15,8 +15,8 @@
 // gate pre-activations of those cells are accumulated in registers, the cell state c stays in
 // registers for the whole sequence, h_t goes to a double-buffered shared tile for step t+1.
 // Packed weights wpk[k][unit][gate] (k < I: kernel rows, k >= I: recurrent rows) followed by
-// bias[unit][gate] are resident in shared memory (or read through L1/L2 when WGLOBAL, for the
-// one layer whose 393 KB do not fit).
+// bias[unit][gate] are resident in shared memory; for the one layer whose 393 KB do not fit
+// (WGLOBAL) they are streamed from L2 through a double-buffered 16-row chunk ring with cp.async.
 #pragma once
 #include <cstdint>
 
@@ -86,7 +86,9 @@ struct LstmCfg {
                                                       // 8-way bank conflict of the per-unit float4 stores
   static constexpr int XBYTES = I * kTile * 4;        // one step of input for one tile
   static constexpr int NST = NST_ > 0 ? NST_ : ((XBYTES >= 16384) ? 2 : 4);  // ring depth
-  static constexpr size_t W_FLOATS = WGLOBAL ? 0 : size_t(K) * H * 4;
+  static constexpr int KC = 16;                       // WGLOBAL: weight rows per streamed chunk
+  static constexpr size_t W_FLOATS = WGLOBAL ? size_t(2) * KC * H * 4 : size_t(K) * H * 4;
+  static_assert(!WGLOBAL || (I % KC == 0 && H % KC == 0), "streamed layers need chunk-aligned widths");
   static constexpr size_t SMEM_BYTES =
       (W_FLOATS + size_t(H) * 4 + size_t(NST) * I * kTile + 2 * size_t(H) * HSTR) * 4 + NST * 8;
   static_assert(H % (LJ * RJ) == 0 && kTile % (LB * RB) == 0 && RB % 4 == 0, "bad tiling");
@@ -153,7 +155,7 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
     for (long long q = 0; q < C::NST && q < total; ++q) issue_load(q);
   }
 
-  const float4* w4 = WGLOBAL ? reinterpret_cast<const float4*>(wpk) : reinterpret_cast<const float4*>(wsm);
+  const float4* w4 = reinterpret_cast<const float4*>(wsm);
   const float4* b4p = reinterpret_cast<const float4*>(bsm);
 
   float cst[RJ][RB];
@@ -190,7 +192,7 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
         const ulonglong2* act2 = reinterpret_cast<const ulonglong2*>(act4);
         auto load = [&](int k, float4 (&w)[RJ], unsigned long long (&xp)[RB / 2]) {
 #pragma unroll
-          for (int r = 0; r < RJ; ++r) w[r] = WGLOBAL ? __ldg(wrow4 + k * H + unit0 + r * LJ) : wrow4[k * H + unit0 + r * LJ];
+          for (int r = 0; r < RJ; ++r) w[r] = wrow4[k * H + unit0 + r * LJ];
 #pragma unroll
           for (int qq = 0; qq < C::NQ; ++qq) {
             const ulonglong2 v = act2[k * astr + b4 + qq * C::LB];
@@ -228,7 +230,7 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
       for (int k = 0; k < kn; ++k) {
         float4 w[RJ];
 #pragma unroll
-        for (int r = 0; r < RJ; ++r) w[r] = WGLOBAL ? __ldg(wrow4 + k * H + unit0 + r * LJ) : wrow4[k * H + unit0 + r * LJ];
+        for (int r = 0; r < RJ; ++r) w[r] = wrow4[k * H + unit0 + r * LJ];
         if (PACKED) {
           unsigned long long xp[RB / 2];
           const ulonglong2* act2 = reinterpret_cast<const ulonglong2*>(act4);
@@ -267,14 +269,38 @@ lstm_layer_kernel(const float* __restrict__ xin,   // [n_tiles][t_in_stride][I][
         }
       }
     };
-    // Input projection: needs only this step's x tile (TMA ring), not h.
-    {
+    if (WGLOBAL) {
+      // Weights streamed chunk by chunk; chunk c+1 is in flight while chunk c is multiplied.
+      const int n_chunks = (t > 0 ? C::K : I) / C::KC;
+      constexpr int CHUNK_F4 = C::KC * H;   // float4 per chunk
+      auto issue_w = [&](int c) {
+        float4* dst = reinterpret_cast<float4*>(wsm) + (c & 1) * CHUNK_F4;
+        const float4* src = reinterpret_cast<const float4*>(wpk) + static_cast<long long>(c) * CHUNK_F4;
+        for (int i = tid; i < CHUNK_F4; i += C::NT) ptx::cp_async16(dst + i, src + i);
+        ptx::cp_async_commit();
+      };
+      issue_w(0);
       const int s = static_cast<int>(q % C::NST);
       ptx::mbar_wait(&bars[s], static_cast<uint32_t>((q / C::NST) & 1));
-      contract(reinterpret_cast<const float4*>(xs + s * I * kTile), kTile / 4, w4, I);
+      for (int c = 0; c < n_chunks; ++c) {
+        ptx::cp_async_wait<0>();
+        __syncthreads();                       // chunk c landed for everyone; chunk c-1 fully consumed
+        if (c + 1 < n_chunks) issue_w(c + 1);
+        const int k0 = c * C::KC;
+        const float4* wc = w4 + (c & 1) * CHUNK_F4;
+        if (k0 < I) contract(reinterpret_cast<const float4*>(xs + s * I * kTile) + k0 * (kTile / 4), kTile / 4, wc, C::KC);
+        else contract(reinterpret_cast<const float4*>(hs + (t & 1) * H * C::HSTR) + (k0 - I) * (C::HSTR / 4), C::HSTR / 4, wc, C::KC);
+      }
+    } else {
+      // Input projection: needs only this step's x tile (TMA ring), not h.
+      {
+        const int s = static_cast<int>(q % C::NST);
+        ptx::mbar_wait(&bars[s], static_cast<uint32_t>((q / C::NST) & 1));
+        contract(reinterpret_cast<const float4*>(xs + s * I * kTile), kTile / 4, w4, I);
+      }
+      // Recurrent part: h_{t-1} from the shared double buffer (zero state at t == 0).
+      if (t > 0) contract(reinterpret_cast<const float4*>(hs + (t & 1) * H * C::HSTR), C::HSTR / 4, w4 + I * H, H);
     }
-    // Recurrent part: h_{t-1} from the shared double buffer (zero state at t == 0).
-    if (t > 0) contract(reinterpret_cast<const float4*>(hs + (t & 1) * H * C::HSTR), C::HSTR / 4, w4 + I * H, H);
 
     float4* hnext = reinterpret_cast<float4*>(hs + ((t + 1) & 1) * H * C::HSTR);
 #pragma unroll

@@ -52,5 +52,16 @@ __device__ __forceinline__ void bulk_load(void* smem_dst, const void* gmem_src, 
                : "memory");
 }
 
+// Ampere-style 16-byte asynchronous global -> shared copies (LDGSTS), used where many threads
+// cooperatively stage a block whose rows are not one contiguous run.
+__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(smem_addr(smem)), "l"(gmem) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() {
+  asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory");
+}
+
 }  // namespace ptx
 }  // namespace gnnqc

@@ -31,12 +31,9 @@ struct WgradArgs {
   float* partial;    // [slices][NA + bias][NC]
 };
 
-__device__ __forceinline__ void cp_async16(void* smem, const void* gmem) {
-  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(ptx::smem_addr(smem)), "l"(gmem) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+using ptx::cp_async16;
+using ptx::cp_async_commit;
+using ptx::cp_async_wait;
 
 static __global__ void __launch_bounds__(64) wgrad_kernel(const WgradArgs g) {
   extern __shared__ __align__(16) float wg_smem[];
