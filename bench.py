@@ -35,7 +35,8 @@ T_CML, N_NODES = 181, 23
 METRIC = "cml_windows_scored_per_sec"
 METRICS = {"cml_gcn": ("cml_windows_scored_per_sec", "windows/s"), "cml_baseline": ("cml_baseline_windows_scored_per_sec", "windows/s"),
            "soilnet_gcn": ("soilnet_sensor_sequences_scored_per_sec", "sequences/s"), "ig": ("cml_ig_attributions_per_sec", "attributions/s"),
-           "train": ("cml_gcn_training_windows_per_sec", "windows/s")}
+           "train": ("cml_gcn_training_windows_per_sec", "windows/s"),
+           "cml_series": ("cml_windows_scored_per_sec_from_resident_series", "windows/s")}
 
 # Algorithmic FLOPs (2*MACs of every matmul) per window and per kernel.
 LSTM_SHAPES = {"cml_gcn": [(181, 18, 16), (181, 16, 16), (60, 16, 32), (60, 32, 32), (20, 32, 64), (20, 64, 64), (6, 64, 128)],
@@ -201,6 +202,7 @@ def main():
         run_reference(args, rank, world)
         return
 
+    import numpy as np
     import torch
     import torch.distributed as dist
 
@@ -214,10 +216,10 @@ def main():
     dev = torch.device("cuda", local_rank)
     wl = args.workload
     metric, unit = METRICS[wl]
-    model_name = {"cml_gcn": "model_cml", "ig": "model_cml", "train": "model_cml", "cml_baseline": "model_cml_baseline",
+    model_name = {"cml_gcn": "model_cml", "ig": "model_cml", "train": "model_cml", "cml_series": "model_cml", "cml_baseline": "model_cml_baseline",
                   "soilnet_gcn": "model_soilnet"}[wl]
     model = NativeModel.load(os.path.join(MODELS, model_name), device=local_rank)
-    B = args.windows or {"cml_gcn": 65536, "cml_baseline": 65536, "soilnet_gcn": 256, "ig": 16384, "train": 4096}[wl]
+    B = args.windows or {"cml_gcn": 65536, "cml_baseline": 65536, "soilnet_gcn": 256, "ig": 65536, "train": 4096, "cml_series": 65536}[wl]
     T = T_CML
     cfg_extra = {}
     e2e_path = None
@@ -247,6 +249,20 @@ def main():
                 dp.all_reduce_sum(rvec)
                 model.train_apply(rvec, mom, 1e-4)
                 return rvec[-1:]
+    elif wl == "cml_series":
+        # On-device window builder: a resident raw network, windows named by (sensor, time index).
+        from gnnqc.series import CmlSeries
+        S, per = 2048, max(1, B // 2048)
+        net = synth.make_cml_network(S, 4096, seed=42 + rank)
+        series = CmlSeries(net["raw"], net["rmed"], net["nbr_off"], net["nbr_idx"], net["edge_off"], net["edges"], device=local_rank)
+        B = S * per
+        tgt_h = torch.arange(S, dtype=torch.int32).repeat_interleave(per).pin_memory()
+        tau_h = (2000 + torch.arange(per, dtype=torch.int32)).repeat(S).pin_memory()
+        tgt_d, tau_d = tgt_h.to(dev), tau_h.to(dev)
+        step = lambda: model.score_cml_series(series, tgt_d, tau_d, 120, 60)  # noqa: E731
+        in_bytes, units = B * 8, B
+        cfg_extra.update({"sensors": S, "consecutive_windows_per_sensor": per, "resident_series_bytes": int(net["raw"].nbytes * 2),
+                          "mean_neighbourhood": float(np.diff(net["nbr_off"]).mean())})
     elif wl == "cml_baseline":
         x = synth.make_seq_batch(B, 2, T_CML, seed=44 + rank, device=str(dev))
         step = lambda: model.score_seq(x)  # noqa: E731
@@ -305,6 +321,17 @@ def main():
         scorer = CmlHostScorer(model, chunk_windows=8192)
         e2e_step = lambda: scorer.score(host["features"], host["anom"], host["edges"], host["node_off"], host["edge_off"])  # noqa: E731
         e2e_path = "CmlHostScorer (pinned host -> chunked H2D on a copy stream -> gnnqc_score_cml -> D2H)"
+    elif wl == "cml_series":
+        scorer = None
+        slab_raw = np.ascontiguousarray(net["raw"][:, 2000 + 60: 2000 + 60 + per])
+        slab_med = np.ascontiguousarray(net["rmed"][:, 2000 + 60: 2000 + 60 + per])
+
+        def e2e_step():
+            # the samples that are new for this step's windows arrive from the host, then the window list
+            series.update(2000 + 60, slab_raw, slab_med)
+            return model.score_cml_series(series, tgt_h.to(dev, non_blocking=True), tau_h.to(dev, non_blocking=True), 120, 60).cpu()
+        h2d, d2h = int(slab_raw.nbytes * 2 + B * 8), B * 4
+        e2e_path = "gnnqc_series_update (new samples) + window list H2D -> gnnqc_score_cml_series -> D2H"
     elif wl == "cml_baseline":
         host_x = x.cpu().pin_memory()
         scorer = SeqHostScorer(model, chunk_seqs=16384)
@@ -387,7 +414,7 @@ def main():
     # backward in ig; + backward + weight gradients in train)
     step_mult = {"ig": 2 * passes, "train": 3}.get(wl, 1)
     step_tflops = sum(fl_live) * step_mult * units / (ms_step * 1e-3) / 1e12
-    bpu = {"cml_gcn": bytes_per_window("cml_gcn"), "cml_baseline": bytes_per_window("cml_baseline"), "soilnet_gcn": 4 * 3 * 337 + 4,
+    bpu = {"cml_gcn": bytes_per_window("cml_gcn"), "cml_series": 16 + 8 + 4, "cml_baseline": bytes_per_window("cml_baseline"), "soilnet_gcn": 4 * 3 * 337 + 4,
            "ig": 2 * bytes_per_window("cml_gcn"), "train": bytes_per_window("cml_gcn") + 4}[wl]
     roofline = {
         "bound": "fp32", "kernel": top["name"], "achieved": top["tflops_executed"], "peak": fp32.value, "unit": "TFLOP/s",

@@ -63,6 +63,10 @@ def _load():
         "gnnqc_score_seq_noalloc": (C.c_int, [vp, vp, i64, i32, vp, vp]),
         "gnnqc_score_cml": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, vp, vp]),
         "gnnqc_score_soilnet": (C.c_int, [vp, vp, vp, vp, vp, i64, i32, i64, i64, vp, vp]),
+        "gnnqc_series_create": (C.c_int, [C.c_int, vp, vp, i64, i64, vp, vp, vp, vp, C.POINTER(vp)]),
+        "gnnqc_series_update": (C.c_int, [vp, i64, i64, vp, vp]),
+        "gnnqc_series_free": (None, [vp]),
+        "gnnqc_score_cml_series": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, vp, vp, vp]),
         "gnnqc_ig_cml": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, i32, vp, vp, vp, vp]),
         "gnnqc_train_vector_len": (i64, [vp]),
         "gnnqc_train_moments_cml": (C.c_int, [vp, vp, i64, vp, vp]),

@@ -186,6 +186,19 @@ class NativeModel:
                                       B, int(T), n_nodes_total, edges.shape[0], out.data_ptr(), self._stream()))
         return out
 
+    def score_cml_series(self, series, target, t_anom, timestep_before=120, timestep_after=60, return_counts=False):
+        """Scores windows named by (target sensor, time index) straight from a resident CmlSeries.
+        target, t_anom: cuda int32 [B].  Windows the reference would skip come back as NaN."""
+        torch = _torch()
+        target = self._dev_tensor(target, torch.int32, "target")
+        t_anom = self._dev_tensor(t_anom, torch.int32, "t_anom")
+        B = target.numel()
+        out = torch.empty(B, dtype=torch.float32, device=target.device)
+        counts = torch.empty(B, dtype=torch.int32, device=target.device) if return_counts else None
+        check(lib.gnnqc_score_cml_series(self._h, series._h, target.data_ptr(), t_anom.data_ptr(), B, int(timestep_before), int(timestep_after),
+                                         out.data_ptr(), counts.data_ptr() if return_counts else None, self._stream()))
+        return (out, counts) if return_counts else out
+
     def ig_cml(self, features, anom, edges, node_off, edge_off, m_steps=50, n_nodes_total=None):
         """Integrated gradients (zero baseline, trapezoid, scaled by the input) for the CML GCN
         model.  Returns (attr_features [Ntot,2], attr_anom [B,T,2], scores [B]) as CUDA tensors."""

@@ -150,6 +150,38 @@ def make_soilnet_batch(n_windows, seed=44, n_nodes=210, ragged=False, T=337, dev
     return {"features": features, "edges": edges, "node_off": node_off, "edge_off": edge_off, "labels": labels.long(), "T": T}
 
 
+def make_cml_network(n_sensors, n_times, seed=42, mean_neighbours=20, max_neighbours=32, nan_frac=0.0005):
+    """Synthetic raw CML network for the window-builder path (SURVEY.md 8(d) config 4 shape, scaled):
+    returns numpy raw [S,Tt,2] (dB levels with NaN gaps), rolling medians [S,Tt,2] (here: a slow
+    moving baseline, exact rolling medians are an offline product in the reference), and the
+    per-target neighbourhoods / adjacency for a 20 km radius (nearest `max_neighbours` kept)."""
+    import numpy as np
+    rng = np.random.default_rng(seed)
+    side = math.sqrt(n_sensors * math.pi * 400.0 / mean_neighbours)
+    xy = rng.uniform(0, side, size=(n_sensors, 2)).astype(np.float32)
+    base = rng.uniform(40, 80, size=(n_sensors, 1, 2)).astype(np.float32)
+    drift = np.cumsum(rng.normal(0, 0.01, size=(n_sensors, n_times, 2)).astype(np.float32), axis=1)
+    rmed = base + drift
+    raw = rmed + rng.normal(0, 0.3, size=(n_sensors, n_times, 2)).astype(np.float32)
+    raw[rng.random((n_sensors, n_times)) < nan_frac] = np.nan
+    nbr_off, nbr_idx, edge_off, edges = [0], [], [0], []
+    for s0 in range(0, n_sensors, 256):          # blocked distance computation
+        d = np.linalg.norm(xy[s0:s0 + 256, None, :] - xy[None, :, :], axis=-1)
+        for k in range(d.shape[0]):
+            nb = np.nonzero(d[k] < 20.0)[0]
+            if len(nb) > max_neighbours:
+                nb = np.sort(nb[np.argsort(d[k][nb], kind="stable")[:max_neighbours]])
+            sub = np.linalg.norm(xy[nb, None, :] - xy[None, nb, :], axis=-1) < 20.0
+            r, c = np.nonzero(sub)
+            nbr_idx.append(nb)
+            nbr_off.append(nbr_off[-1] + len(nb))
+            edges.append(np.stack([r, c], axis=1))
+            edge_off.append(edge_off[-1] + len(r))
+    return {"raw": raw, "rmed": rmed.astype(np.float32), "nbr_off": np.asarray(nbr_off, np.int32),
+            "nbr_idx": np.concatenate(nbr_idx).astype(np.int32), "edge_off": np.asarray(edge_off, np.int64),
+            "edges": np.concatenate(edges).astype(np.int64).reshape(-1, 2)}
+
+
 def make_seq_batch(n_seq, n_features, T, seed=44, device="cpu"):
     """Plain [n_seq, T, F] sequences for the baseline models (CML: the target series)."""
     g = torch.Generator(device=device)

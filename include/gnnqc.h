@@ -124,6 +124,39 @@ int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom
                     const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
                     float* scores_dev, void* stream);
 
+/* ---- scoring from resident raw series (on-device window builder) ------------------------ */
+
+/* Replaces, for sweeps over a whole network, the reference's materialise-then-score pipeline:
+ * create_tfrecords_dataset (libs/preprocessing_functions.py:388-412: window slicing, windows
+ * whose target has a NaN are skipped, neighbours with a NaN in the window are dropped),
+ * parse_cml_tfrecord_fn (:620-622: subtract each sensor's rolling median taken at the window's
+ * target time), prepare_batch_cml (:638-666) and GCNClassifier.call.  The raw network stays in HBM;
+ * a window is named by (target sensor, time index), so ~8 bytes per window cross PCIe.
+ *
+ * gnnqc_series_create copies to `device`:
+ *   raw_host, rmed_host  f32 [n_sensors, n_times, 2]  TL_1/TL_2 and their rolling medians
+ *                        (NaN = missing sample; the medians are precomputed per dataset as in
+ *                        calculate_statistics, :123-140)
+ *   nbr_off_host i32 [n_sensors+1], nbr_idx_host i32: for every sensor the sensors of its
+ *                        neighbourhood in the reference's order, ITSELF INCLUDED, at most 32
+ *   edge_off_host i64 [n_sensors+1], edges_host i64 [E,2]: adjacency of that neighbourhood
+ *                        (distance < max_sample_distance, self-loops included) as
+ *                        (receiving, sending) positions in the neighbour list
+ * gnnqc_series_update overwrites the time range [t0, t0+n_t) from host slabs [n_sensors, n_t, 2].
+ * gnnqc_score_cml_series: target_dev i32 [B], t_anom_dev i32 [B] -> scores_dev f32 [B]; a window
+ * that the reference would skip (incomplete, or NaN in the target series) gets NaN.  n_nodes_dev
+ * (optional, i32 [B]) receives the number of sensors used per window (0 = skipped). */
+typedef struct gnnqc_series gnnqc_series;
+int gnnqc_series_create(int device, const float* raw_host, const float* rmed_host, int64_t n_sensors,
+                        int64_t n_times, const int32_t* nbr_off_host, const int32_t* nbr_idx_host,
+                        const int64_t* edge_off_host, const int64_t* edges_host, gnnqc_series** out);
+int gnnqc_series_update(gnnqc_series* s, int64_t t0, int64_t n_t, const float* raw_host,
+                        const float* rmed_host);
+void gnnqc_series_free(gnnqc_series* s);
+int gnnqc_score_cml_series(gnnqc_model* m, const gnnqc_series* series, const int32_t* target_dev,
+                           const int32_t* t_anom_dev, int64_t B, int32_t timestep_before,
+                           int32_t timestep_after, float* scores_dev, int32_t* n_nodes_dev, void* stream);
+
 /* ---- attribution ---------------------------------------------------------------------- */
 
 /* Replaces IntegratedGradientsExplainer._get_gradients_single_batch for the CML GCN model

@@ -1,0 +1,67 @@
+"""On-device window builder (gnnqc_score_cml_series) == materialise the windows on the host the way
+the reference does, then score them (bit-identical to gnnqc_score_cml, within 1e-4 of the oracle)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import gnnqc_oracle as O
+import window_builder as WB
+from conftest import MODELS
+from gnnqc import NativeModel, synth
+from gnnqc.series import CmlSeries, neighbourhoods_from_distances
+
+pytestmark = pytest.mark.gpu
+
+
+def make_network(S=14, Tt=900, seed=0, nan_frac=0.002):
+    rng = np.random.default_rng(seed)
+    xy = rng.uniform(0, 45, size=(S, 2))
+    dist = np.linalg.norm(xy[:, None] - xy[None], axis=-1)
+    raw = 60.0 + np.cumsum(rng.normal(0, 0.05, size=(S, Tt, 2)), axis=1) + rng.normal(0, 0.3, size=(S, Tt, 2))
+    raw[3, 400:] += 6.0                                   # a jump on one link
+    holes = rng.random((S, Tt)) < nan_frac
+    raw[holes] = np.nan
+    raw[5, 200:260] = np.nan                              # a long gap on one neighbour
+    raw = raw.astype(np.float32)
+    rmed = WB.rolling_median(raw, 240).astype(np.float32)
+    return raw, rmed, dist
+
+
+def test_series_scoring_matches_materialised_windows():
+    raw, rmed, dist = make_network()
+    nbr_off, nbr_idx, edge_off, edges = neighbourhoods_from_distances(dist, 20.0)
+    assert (np.diff(nbr_off) <= 32).all()
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    series = CmlSeries(raw, rmed, nbr_off, nbr_idx, edge_off, edges, device=0)
+    try:
+        rng = np.random.default_rng(1)
+        targets = rng.integers(0, raw.shape[0], size=300).astype(np.int32)
+        t_anom = rng.integers(100, raw.shape[1] - 30, size=300).astype(np.int32)   # some windows run off either end
+        got, counts = m.score_cml_series(series, torch.tensor(targets).cuda(), torch.tensor(t_anom).cuda(), 120, 60, return_counts=True)
+        got, counts = got.cpu().numpy(), counts.cpu().numpy()
+        batch, kept, want_counts = WB.materialise_windows(raw, rmed, nbr_off, nbr_idx, edge_off, edges, targets, t_anom, 120, 60)
+        assert kept.sum() > 100 and (~kept).sum() > 5
+        assert np.array_equal(np.isnan(got), ~kept)
+        assert np.array_equal(counts, want_counts)
+        assert (want_counts[kept] < np.diff(nbr_off)[targets[kept]]).any()        # some neighbours were dropped for NaNs
+        b = {k: torch.as_tensor(v).cuda() for k, v in batch.items() if k != "T"}
+        ref = m.score_cml(b["features"], b["anom"], b["edges"], b["node_off"], b["edge_off"]).cpu().numpy()
+        assert np.array_equal(got[kept], ref)                                      # same arithmetic, same order
+        tb = {k: (torch.as_tensor(v) if k != "T" else v) for k, v in batch.items()}
+        feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(tb), 2)
+        w = O.to_torch_weights(m.named_params(), torch.float32)
+        oracle = O.gcn_forward_cml(torch.tensor(feat), tb["anom"], torch.tensor(idx), torch.tensor(samp), w).reshape(-1).numpy()
+        assert np.all(np.abs(got[kept] - oracle) <= 1e-4 + 1e-4 * np.abs(oracle))
+        # streaming update: overwrite a range, scores of windows that do not touch it are unchanged
+        new = raw[:, 700:760].copy()
+        new[:, :, 0] += 1.0
+        series.update(700, new, rmed[:, 700:760])
+        again = m.score_cml_series(series, torch.tensor(targets).cuda(), torch.tensor(t_anom).cuda(), 120, 60).cpu().numpy()
+        untouched = kept & (t_anom + 60 < 700)
+        assert np.array_equal(again[untouched], got[untouched])
+        assert not np.array_equal(again[kept & (t_anom + 60 >= 700) & (t_anom - 120 < 760)], got[kept & (t_anom + 60 >= 700) & (t_anom - 120 < 760)])
+    finally:
+        series.close()
+        m.close()
