@@ -112,7 +112,10 @@ class ClockSampler:
 
 
 class CpuOracle:
-    """The CPU oracle (torch fp32, all host threads) on a fixed sample of the workload."""
+    """The CPU oracle (torch fp32, all host threads) on a fixed sample of the workload, fed in batches
+    of 128 windows - the reference's batch_size (preprocessing_config.yml:5)."""
+
+    BATCH = 128
 
     def __init__(self, workload, sample_windows):
         sys.path.insert(0, os.path.join(ROOT, "oracle"))
@@ -128,19 +131,22 @@ class CpuOracle:
         name = "model_cml" if workload == "cml_gcn" else "model_cml_baseline"
         named = NativeModel.load(os.path.join(MODELS, name), device=None).named_params()
         w = O.to_torch_weights(named, torch.float32)
-        if workload == "cml_gcn":
-            batch = synth.make_cml_batch(sample_windows, seed=44, n_nodes=N_NODES)
-            feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 2)
-            feat, idx, samp = torch.tensor(feat), torch.tensor(idx), torch.tensor(samp)
-            self.fn = lambda: O.gcn_forward_cml(feat, batch["anom"], idx, samp, w)
-        else:
-            x = synth.make_seq_batch(sample_windows, 2, T_CML, seed=44)
-            self.fn = lambda: O.baseline_forward(x, w)
+        self.calls = []
+        for i, lo in enumerate(range(0, sample_windows, self.BATCH)):
+            n = min(self.BATCH, sample_windows - lo)
+            if workload == "cml_gcn":
+                batch = synth.make_cml_batch(n, seed=44 + i, n_nodes=N_NODES)
+                feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 2)
+                args = (torch.tensor(feat), batch["anom"], torch.tensor(idx), torch.tensor(samp), w)
+                self.calls.append((O.gcn_forward_cml, args))
+            else:
+                self.calls.append((O.baseline_forward, (synth.make_seq_batch(n, 2, T_CML, seed=44 + i), w)))
 
     def step(self):
         with self.torch.no_grad():
             t0 = time.perf_counter()
-            self.fn()
+            for fn, args in self.calls:
+                fn(*args)
             return time.perf_counter() - t0
 
 
@@ -157,7 +163,7 @@ def run_reference(args, rank, world):
     say - this arm times the CPU oracle port on the host cores."""
     if rank != 0:
         return
-    sample = 128 if args.workload == "cml_gcn" else 2048
+    sample = 2048 if args.workload == "cml_gcn" else 16384
     o = CpuOracle(args.workload, sample)
     cores = o.cores
     times = []
@@ -171,10 +177,10 @@ def run_reference(args, rank, world):
         "impl": "reference", "metric": METRIC, "value": value, "unit": "windows/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": args.workload, "windows_per_step": sample, "seq_len": T_CML, "nodes_per_window": N_NODES,
+        "config": {"workload": args.workload, "windows_per_step": sample, "batch_size": 128, "seq_len": T_CML, "nodes_per_window": N_NODES,
                    "note": "CPU oracle port (torch fp32); reference TF/Keras CPU path unavailable on this box"},
         "cpu_baseline": {"value": value, "unit": "windows/s", "cores": cores, "kind": "port",
-                         "sample": "%d windows per step" % sample},
+                         "sample": "%d windows per step in batches of 128" % sample},
         "e2e": {"value": value, "unit": "windows/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
     print(json.dumps(line), flush=True)
@@ -431,10 +437,10 @@ def main():
 
     cpu = None
     if not args.no_cpu_baseline and wl in ("cml_gcn", "cml_baseline"):
-        sample = 128 if wl == "cml_gcn" else 4096
+        sample = 1024 if wl == "cml_gcn" else 16384
         wps, cores, secs = cpu_oracle_throughput(wl, sample, repeats=2)
         cpu = {"value": wps, "unit": "windows/s", "cores": cores, "kind": "port",
-               "sample": "%d windows, best of 2 after warm-up (%.1f s each); reference TF CPU path unavailable on this box" % (sample, secs)}
+               "sample": "%d windows in batches of 128, best of 2 after warm-up (%.1f s each); reference TF CPU path unavailable on this box" % (sample, secs)}
 
     config = {"workload": wl, "model": model_name, "units_per_gpu_per_step": units, "seq_len": T,
               "nodes_per_window": {"cml_baseline": 1, "soilnet_gcn": 210}.get(wl, N_NODES), "input_bytes_per_step": in_bytes,
