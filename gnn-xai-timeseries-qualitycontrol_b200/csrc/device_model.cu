@@ -234,6 +234,7 @@ void DeviceModel::configure_kernels() {
     const bool pool = !last && (l % 2 == 1);
     layer_dispatch<true>(s.lstm_in[l], s.lstm_hid[l], pool, last, nullptr, nullptr, nullptr, 0, 0, 0, 0, 0, nullptr);
   }
+  GNNQC_CUDA(cudaFuncSetAttribute(cml_frontend_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFeSmem)));
   if (s.lstm_hid[s.n_lstm - 1] != 128 || s.dense_units != 64)
     throw std::invalid_argument("head kernel supports a 128 -> 64 -> 64 -> 1 head only");
 }
@@ -346,8 +347,16 @@ void DeviceModel::score_cml(const float* feat, const float* anom, const long lon
     const long long win0 = t0 * kTile, nw = std::min<long long>(B - win0, nt * kTile);
     dim3 grid(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
     mark_begin("cml_frontend", st);
-    cml_frontend_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), reinterpret_cast<const float2*>(anom) + win0 * T,
-                                              coef, node_off + win0, folded, buf_a, nw, T, plan.t_run[0]);
+    static const bool plain_frontend = [] { const char* e = std::getenv("GNNQC_FRONTEND"); return e && std::strcmp(e, "plain") == 0; }();
+    if (plain_frontend) {
+      cml_frontend_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), reinterpret_cast<const float2*>(anom) + win0 * T,
+                                                coef, node_off + win0, folded, buf_a, nw, T, plan.t_run[0]);
+    } else {
+      dim3 grid_tma(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + kFeTch - 1) / kFeTch));
+      cml_frontend_tma_kernel<<<grid_tma, 256, kFeSmem, st>>>(reinterpret_cast<const float2*>(feat), n_nodes * T,
+                                                              reinterpret_cast<const float2*>(anom) + win0 * T, coef, node_off + win0, folded,
+                                                              buf_a, nw, T, plan.t_run[0], 1.f);
+    }
     GNNQC_CUDA(cudaGetLastError());
     mark_end(st);
     run_stack(plan, buf_a, buf_b, nt, nw, scores + win0, st);

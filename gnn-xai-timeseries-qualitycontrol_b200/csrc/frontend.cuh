@@ -104,6 +104,34 @@ struct GcnFolded {
   float alpha[kGcnChannelsDev];
 };
 
+// PReLU pooled over nodes without a branch per element: prelu(z) = k1*z + k2*|z| with
+// k1 = (1+alpha)/2, k2 = (1-alpha)/2, and z is affine in the two input channels, so
+//   sum_n cf_n prelu(z_n) = k1 * (a0*S0 + a1*S1 + c*Sc) + k2 * sum_n cf_n |z_n|
+// with S0 = sum cf_n x0_n, S1 = sum cf_n x1_n, Sc = sum cf_n.  Per (node, channel) that is two
+// FFMA for z and one FFMA (|z| is an operand modifier) instead of six instructions.
+struct PoolAcc {
+  float s0 = 0.f, s1 = 0.f, sc = 0.f;
+  float sabs[kGcnChannelsDev];
+  __device__ __forceinline__ PoolAcc() {
+#pragma unroll
+    for (int c = 0; c < kGcnChannelsDev; ++c) sabs[c] = 0.f;
+  }
+  __device__ __forceinline__ void add(const GcnFolded& p, float2 v, float cf) {
+    s0 = fmaf(cf, v.x, s0);
+    s1 = fmaf(cf, v.y, s1);
+    sc += cf;
+#pragma unroll
+    for (int c = 0; c < kGcnChannelsDev; ++c) {
+      const float z = fmaf(v.x, p.a[0][c], fmaf(v.y, p.a[1][c], p.c[c]));
+      sabs[c] = fmaf(cf, fabsf(z), sabs[c]);
+    }
+  }
+  __device__ __forceinline__ float pooled(const GcnFolded& p, int c) const {
+    const float lin = fmaf(p.a[0][c], s0, fmaf(p.a[1][c], s1, p.c[c] * sc));
+    return fmaf(0.5f * (1.f + p.alpha[c]), lin, 0.5f * (1.f - p.alpha[c]) * sabs[c]);
+  }
+};
+
 // ---- CML front-end: features (b,t,n) + coef + target series -> x1 tiles [tile][t][18][64] --
 // Restates GCNClassifier.call for 'cml' up to the Concatenate (libs/create_model.py:217-223):
 // channels 0..1 = anomalous_sensor_features, 2..17 = pooled GeneralConv output.
@@ -123,27 +151,19 @@ __device__ __forceinline__ void cml_frontend_body(const float2* __restrict__ fea
   for (int dt = 0; dt < 8; ++dt) {
     const int t = t0 + dt;
     if (t >= t_run) break;
-    float acc[kGcnChannelsDev];
-#pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) acc[c] = 0.f;
+    PoolAcc acc;
     const float2* row = feat + (static_cast<long long>(n0) * T + static_cast<long long>(t) * nn);
     for (int n = 0; n < nn; ++n) {
       float2 v = __ldg(row + n);
       v.x *= alpha; v.y *= alpha;   // integrated-gradients path scaling; exact no-op for alpha == 1
-      const float cf = __ldg(coef + n0 + n);
-#pragma unroll
-      for (int c = 0; c < kGcnChannelsDev; ++c) {
-        float z = fmaf(v.x, p.a[0][c], fmaf(v.y, p.a[1][c], p.c[c]));
-        z = fmaxf(z, 0.f) + p.alpha[c] * fminf(z, 0.f);
-        acc[c] = fmaf(cf, z, acc[c]);
-      }
+      acc.add(p, v, __ldg(coef + n0 + n));
     }
     const float2 av = live ? __ldg(anom + win * T + t) : make_float2(0.f, 0.f);
     float* o = out + ((tile * t_run + t) * CH) * kTile + b;
     o[0] = av.x * alpha;
     o[kTile] = av.y * alpha;
 #pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc[c];
+    for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc.pooled(p, c);
   }
 }
 
@@ -164,6 +184,81 @@ static __global__ void __launch_bounds__(256) cml_frontend_devparam_kernel(const
   if (threadIdx.x < sizeof(GcnFolded) / 4) reinterpret_cast<float*>(&p)[threadIdx.x] = reinterpret_cast<const float*>(pp)[threadIdx.x];
   __syncthreads();
   cml_frontend_body(feat, anom, coef, node_off, p, out, n_windows, T, t_run, 1.f);
+}
+
+// ---- CML front-end, TMA-staged --------------------------------------------------------------
+// Same arithmetic as cml_frontend_kernel, but each window's slab of kFeTch timesteps (a contiguous
+// kFeTch*N_b*8-byte run of the features array) is fetched with ONE cp.async.bulk (TMA) into its
+// own shared-memory slot, all 64 windows of the tile signalling one mbarrier; the threads then
+// read the slab from shared memory instead of streaming 8-byte pieces of 64 different rows.
+// The features array only guarantees 8-byte alignment per window (N_b*T can be odd), so the copy
+// starts at the enclosing 16-byte boundary and the reader skips the 0 or 8 lead bytes.  Windows
+// with more than kFeCap nodes, or whose rounded-up copy would run past the end of the array,
+// take the direct-load path (slot flag -1).
+constexpr int kFeTch = 4;                                   // timesteps per CTA
+constexpr int kFeCap = 32;                                  // nodes per window staged through smem
+constexpr int kFeSlot = kFeTch * kFeCap * 8 + 16;           // bytes per window slot (16 * odd)
+constexpr size_t kFeSmem = size_t(kTile) * kFeSlot + kTile * sizeof(int) + 16;
+
+static __global__ void __launch_bounds__(256) cml_frontend_tma_kernel(const float2* __restrict__ feat, long long feat_rows,
+                                                                      const float2* __restrict__ anom, const float* __restrict__ coef,
+                                                                      const int* __restrict__ node_off, const GcnFolded p,
+                                                                      float* __restrict__ out, long long n_windows, int T, int t_run,
+                                                                      float alpha) {
+  extern __shared__ __align__(128) unsigned char fe_smem[];
+  unsigned char* slots = fe_smem;
+  int* lead_s = reinterpret_cast<int*>(fe_smem + size_t(kTile) * kFeSlot);
+  uint64_t* bar = reinterpret_cast<uint64_t*>(fe_smem + size_t(kTile) * kFeSlot + kTile * sizeof(int));
+  const int tid = threadIdx.x, b = tid & 63, tq = tid >> 6;
+  const long long tile = blockIdx.x;
+  const long long win = tile * kTile + b;
+  const int t0 = blockIdx.y * kFeTch;
+  const int tch = min(kFeTch, t_run - t0);
+  const bool live = win < n_windows;
+  const int n0 = live ? node_off[win] : 0;
+  const int nn = live ? node_off[win + 1] - n0 : 0;
+  if (tid == 0) {
+    ptx::mbar_init(bar, kTile);
+    ptx::mbar_init_fence();
+  }
+  __syncthreads();
+  if (tid < kTile) {   // thread b issues the copy of window b
+    int lead = -1;
+    if (live && nn > 0 && nn <= kFeCap) {
+      const long long first_row = static_cast<long long>(n0) * T + static_cast<long long>(t0) * nn;   // float2 index
+      const unsigned long long addr = reinterpret_cast<unsigned long long>(feat + first_row);
+      const int ld = static_cast<int>(addr & 15ull);
+      const unsigned bytes = (static_cast<unsigned>(ld) + static_cast<unsigned>(tch * nn) * 8u + 15u) & ~15u;
+      const unsigned long long end = reinterpret_cast<unsigned long long>(feat + feat_rows);
+      if (addr - ld + bytes <= end) {
+        lead = ld;
+        ptx::mbar_arrive_expect_tx(bar, bytes);
+        ptx::bulk_load(slots + size_t(b) * kFeSlot, reinterpret_cast<const void*>(addr - ld), bytes, bar);
+      }
+    }
+    lead_s[b] = lead;
+    if (lead < 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(ptx::smem_addr(bar)) : "memory");
+  }
+  __syncthreads();        // lead_s visible
+  ptx::mbar_wait(bar, 0);
+  const int t = t0 + tq;
+  if (tq >= tch) return;
+  constexpr int CH = 2 + kGcnChannelsDev;
+  PoolAcc acc;
+  const int lead = lead_s[b];
+  const float2* srow = reinterpret_cast<const float2*>(slots + size_t(b) * kFeSlot + (lead < 0 ? 0 : lead)) + tq * nn;
+  const float2* grow = feat + (static_cast<long long>(n0) * T + static_cast<long long>(t) * nn);
+  for (int n = 0; n < nn; ++n) {
+    float2 v = (lead >= 0) ? srow[n] : __ldg(grow + n);
+    v.x *= alpha; v.y *= alpha;   // integrated-gradients path scaling; exact no-op for alpha == 1
+    acc.add(p, v, __ldg(coef + n0 + n));
+  }
+  const float2 av = live ? __ldg(anom + win * T + t) : make_float2(0.f, 0.f);
+  float* o = out + ((tile * t_run + t) * CH) * kTile + b;
+  o[0] = av.x * alpha;
+  o[kTile] = av.y * alpha;
+#pragma unroll
+  for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc.pooled(p, c);
 }
 
 // ---- dense head: [tile][128][64] -> sigmoid(Dense(LeakyReLU(Dense(LeakyReLU(Dense))))) ------

@@ -160,28 +160,20 @@ __global__ void __launch_bounds__(256) series_frontend_kernel(const gnnqc_series
   for (int dt = 0; dt < 8; ++dt) {
     const int t = tt0 + dt;
     if (t >= t_run) break;
-    float acc[kGcnChannelsDev];
-#pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) acc[c] = 0.f;
+    PoolAcc acc;
     float2 tv = make_float2(0.f, 0.f);
     for (int n = 0; n < nn; ++n) {
       const float2 raw = __ldg(sr.raw + static_cast<long long>(__ldg(sensors + n)) * sr.Tt + base_t + t);
       const float2 m = __ldg(med + n);
       const float2 v = make_float2(raw.x - m.x, raw.y - m.y);
       if (n == tslot) tv = v;
-      const float cf = __ldg(coef + n);
-#pragma unroll
-      for (int c = 0; c < kGcnChannelsDev; ++c) {
-        float z = fmaf(v.x, p.a[0][c], fmaf(v.y, p.a[1][c], p.c[c]));
-        z = fmaxf(z, 0.f) + p.alpha[c] * fminf(z, 0.f);
-        acc[c] = fmaf(cf, z, acc[c]);
-      }
+      acc.add(p, v, __ldg(coef + n));
     }
     float* o = out + ((tile * t_run + t) * CH) * kTile + b;
     o[0] = tv.x;
     o[kTile] = tv.y;
 #pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc[c];
+    for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc.pooled(p, c);
   }
 }
 
