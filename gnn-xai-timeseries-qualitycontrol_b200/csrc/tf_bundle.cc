@@ -8,6 +8,7 @@
 //    crc32c of those bytes.  A string tensor is: varint length per element, masked crc32c
 //    of the lengths (as uint32 each), then the bytes.
 #include "tf_bundle.h"
+#include "wire.h"
 
 #include <algorithm>
 #include <cstdio>
@@ -22,6 +23,7 @@ constexpr uint64_t kTableMagic = 0xdb4775248b80fb57ull;
 const char* const kObjectGraphKey = "_CHECKPOINTABLE_OBJECT_GRAPH";
 
 [[noreturn]] void fail(const std::string& what) { throw std::runtime_error("tf_bundle: " + what); }
+using wire::Cursor;
 
 std::vector<uint8_t> slurp(const std::string& path) {
   std::ifstream f(path, std::ios::binary);
@@ -33,45 +35,6 @@ std::vector<uint8_t> slurp(const std::string& path) {
   if (n > 0 && !f.read(reinterpret_cast<char*>(buf.data()), n)) fail("short read on " + path);
   return buf;
 }
-
-// Bounded cursor over a byte range; all protobuf / table decoding goes through it.
-struct Cursor {
-  const uint8_t* p;
-  const uint8_t* end;
-  bool done() const { return p >= end; }
-  uint64_t varint() {
-    uint64_t v = 0;
-    for (int shift = 0; shift < 64; shift += 7) {
-      if (p >= end) fail("truncated varint");
-      uint8_t c = *p++;
-      v |= static_cast<uint64_t>(c & 0x7f) << shift;
-      if (!(c & 0x80)) return v;
-    }
-    fail("varint too long");
-  }
-  Cursor sub(size_t n) {
-    if (static_cast<size_t>(end - p) < n) fail("truncated length-delimited field");
-    Cursor c{p, p + n};
-    p += n;
-    return c;
-  }
-  uint32_t fixed32() {
-    if (end - p < 4) fail("truncated fixed32");
-    uint32_t v;
-    std::memcpy(&v, p, 4);
-    p += 4;
-    return v;
-  }
-  void skip(int wire) {
-    switch (wire) {
-      case 0: varint(); break;
-      case 1: sub(8); break;
-      case 2: sub(varint()); break;
-      case 5: sub(4); break;
-      default: fail("unsupported protobuf wire type");
-    }
-  }
-};
 
 struct BlockHandle {
   uint64_t offset, size;

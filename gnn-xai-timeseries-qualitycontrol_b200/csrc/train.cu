@@ -274,13 +274,14 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     const unsigned gx = (rows + kWgA - 1) / kWgA, gy = (NC + kWgC - 1) / kWgC;
     long long slices = std::max<long long>(1, (static_cast<long long>(sm_count) * 16) / (gx * gy));
     slices = std::min<long long>(slices, g.n_items);
+    slices = std::min<long long>(slices, 512);
     slices = std::min<long long>(slices, static_cast<long long>(kPartialBytes / (size_t(rows) * NC * 4)));
     mark_begin(name, st);
     wgrad_kernel<<<dim3(gx, gy, static_cast<unsigned>(slices)), 64, kWgradSmem, st>>>(g);
     GNNQC_CUDA(cudaGetLastError());
     mark_end(st);
     mark_begin("wgrad_reduce", st);
-    wgrad_reduce_kernel<<<(rows * NC + 255) / 256, 256, 0, st>>>(F(o_part), static_cast<int>(slices), rows, NC, out_main, NA, out_bias);
+    wgrad_reduce_kernel<<<(rows * NC * 32 + 255) / 256, 256, 0, st>>>(F(o_part), static_cast<int>(slices), rows, NC, out_main, NA, out_bias);
     GNNQC_CUDA(cudaGetLastError());
     mark_end(st);
   };

@@ -114,13 +114,17 @@ static __global__ void __launch_bounds__(64) wgrad_kernel(const WgradArgs g) {
   }
 }
 
-// out[a*ld + c] = sum_s partial[s][a][c]   (rows a < rows, fixed order -> deterministic)
+// out[a][c] = sum_s partial[s][a][c].  One warp per output element: lane l adds slices l, l+32, ...
+// and the 32 partial sums are combined with a fixed shuffle tree, so the result does not depend on
+// scheduling (deterministic) and no thread walks hundreds of slices serially.
 static __global__ void __launch_bounds__(256) wgrad_reduce_kernel(const float* __restrict__ partial, int slices, int rows, int cols,
                                                                   float* __restrict__ out_main, int main_rows, float* __restrict__ out_bias) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  const int i = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (i >= rows * cols) return;
   float s = 0.f;
-  for (int k = 0; k < slices; ++k) s += partial[static_cast<long long>(k) * rows * cols + i];
+  for (int k = lane; k < slices; k += 32) s += partial[static_cast<long long>(k) * rows * cols + i];
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_down_sync(0xffffffffu, s, o);
+  if (lane != 0) return;
   const int a = i / cols, c = i % cols;
   if (a < main_rows) out_main[i] = s;
   else if (out_bias != nullptr) out_bias[c] = s;

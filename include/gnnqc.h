@@ -157,6 +157,27 @@ int gnnqc_score_cml_series(gnnqc_model* m, const gnnqc_series* series, const int
                            const int32_t* t_anom_dev, int64_t B, int32_t timestep_before,
                            int32_t timestep_after, float* scores_dev, int32_t* n_nodes_dev, void* stream);
 
+/* ---- reading the reference's TFRecord window files (host only) -------------------------------- */
+
+/* Replaces tf.data.TFRecordDataset + parse_cml_tfrecord_fn + batch + prepare_batch_cml for one file
+ * written by create_tfrecords_dataset (libs/preprocessing_functions.py:388-412, schema create_example
+ * :220-283, parse :567-634, batch :638-666): every tf.train.SequenceExample becomes one window of a
+ * batch in the layout of gnnqc_score_cml.  normalization = the mode of parse_cml_tfrecord_fn
+ * ("rolling_median" default; "standarization", "scale", "median", "rolling_median_fractional",
+ * "rolling_mean", "none").  Record checksums are verified.  gnnqc_cml_records_copy fills caller
+ * arrays sized from gnnqc_cml_records_info (any pointer may be NULL); _id / _dates return the target
+ * sensor id and the comma-joined date strings of window i. */
+typedef struct gnnqc_cml_records gnnqc_cml_records;
+int gnnqc_tfrecord_read_cml(const char* path, const char* normalization, gnnqc_cml_records** out);
+int gnnqc_cml_records_info(const gnnqc_cml_records* r, int64_t* n_windows, int64_t* T,
+                           int64_t* n_nodes_total, int64_t* n_edges_total);
+int gnnqc_cml_records_copy(const gnnqc_cml_records* r, float* features_host, float* anom_host,
+                           int64_t* edges_host, int32_t* node_off_host, int64_t* edge_off_host,
+                           int64_t* labels_host);
+const char* gnnqc_cml_records_id(const gnnqc_cml_records* r, int64_t i);
+const char* gnnqc_cml_records_dates(const gnnqc_cml_records* r, int64_t i);
+void gnnqc_cml_records_free(gnnqc_cml_records* r);
+
 /* ---- attribution ---------------------------------------------------------------------- */
 
 /* Replaces IntegratedGradientsExplainer._get_gradients_single_batch for the CML GCN model
