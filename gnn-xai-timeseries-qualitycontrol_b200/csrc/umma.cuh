@@ -1,0 +1,82 @@
+// tcgen05 (5th-generation tensor core) building blocks for sm_100a: TMEM allocation, UMMA
+// shared-memory / instruction descriptors, MMA issue, commit, TMEM loads.  Inline PTX only.
+//
+// Operand layout used throughout (K-major, no swizzle - the "interleave" canonical layout):
+// an operand tile of R rows x K elements of bf16 is stored as [K/8][R][8]: 8x8 "core matrices" of
+// 8 rows x 16 bytes, rows of a core matrix 16 bytes apart, the next 8 rows 128 bytes further
+// (stride byte offset, SBO), the next 8 K-elements R*16 bytes further (leading byte offset, LBO).
+//   byte(r, k) = (k / 8) * R * 16 + r * 16 + (k % 8) * 2
+// One tcgen05.mma of kind::f16 consumes K = 16, i.e. two core-matrix columns; advancing to the next
+// K-chunk adds 2 * LBO to the descriptor's start address.
+#pragma once
+#include <cstdint>
+
+#include "ptx.cuh"
+
+namespace gnnqc {
+namespace umma {
+
+// 64-bit shared-memory matrix descriptor (sm_100 format, version 1, no swizzle).
+__device__ __forceinline__ uint64_t smem_desc(const void* smem_ptr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  const uint32_t addr = ptx::smem_addr(smem_ptr);
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((addr & 0x3FFFF) >> 4);          // start address, bits [0,14)
+  d |= static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16;  // leading byte offset, bits [16,30)
+  d |= static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32;  // stride byte offset, bits [32,46)
+  d |= static_cast<uint64_t>(1) << 46;                          // descriptor version (Blackwell)
+  return d;                                                      // base offset 0, layout type 0 (none)
+}
+
+// 32-bit instruction descriptor: bf16 x bf16 -> fp32, both operands K-major, dense.
+__host__ __device__ constexpr uint32_t instr_desc_bf16(int m, int n) {
+  return (1u << 4)                       // D format: F32
+         | (1u << 7)                     // A format: BF16
+         | (1u << 10)                    // B format: BF16
+         | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, uint32_t ncols) {   // one full warp
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(ptx::smem_addr(smem_slot)), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {      // the same warp
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void fence_before_sync() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void fence_after_sync() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+// generic-proxy shared-memory writes -> visible to the async proxy (tensor core operand fetch)
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] * B[smem]^T, issued by ONE thread.
+__device__ __forceinline__ void mma_bf16(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, bool accumulate) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "setp.ne.b32 p, %4, 0;\n"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+      "}\n" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(static_cast<uint32_t>(accumulate))
+      : "memory");
+}
+// Arrives on `bar` once all MMAs issued so far by this thread have completed.
+__device__ __forceinline__ void commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(ptx::smem_addr(bar)) : "memory");
+}
+
+// 32 lanes x 16 consecutive 32-bit columns: thread i of the warp gets row (lane base + i).  The
+// wait is part of the same asm statement so the compiler cannot consume the registers early.
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+      "tcgen05.wait::ld.sync.aligned;\n"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+}  // namespace umma
+}  // namespace gnnqc

@@ -83,6 +83,7 @@ def _load():
         "gnnqc_launch_count": (i64, [vp]),
         "gnnqc_profile_enable": (C.c_int, [vp, C.c_int]),
         "gnnqc_profile_read": (C.c_int, [vp, C.c_int, vp, C.POINTER(C.c_double), C.POINTER(i64), C.POINTER(C.c_int)]),
+        "gnnqc_selftest_umma": (C.c_int, [C.c_int, C.POINTER(C.c_float)]),
         "gnnqc_probe_fp32_peak": (C.c_int, [C.c_int, C.c_int, C.POINTER(C.c_double)]),
     }
     for name, (res, args) in sigs.items():

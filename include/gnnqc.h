@@ -269,6 +269,10 @@ int64_t gnnqc_score_scratch_bytes(const gnnqc_model* m, int64_t n_seq, int32_t T
  * roofline denominator of the fp32 LSTM kernels. */
 int gnnqc_probe_fp32_peak(int device, int mode, double* tflops_out);
 
+/* No reference counterpart (self-test): runs one 128x64x48 bf16 GEMM through the tcgen05 / TMEM
+ * path of csrc/umma.cuh on `device` and returns its largest deviation from a host float loop. */
+int gnnqc_selftest_umma(int device, float* max_abs_err);
+
 /* No reference counterpart (measurement only).  gnnqc_launch_count: kernels this handle has
  * enqueued since it was created.  gnnqc_profile_enable(1) makes every later launch record a
  * pair of CUDA events on its stream; gnnqc_profile_read synchronises the device, sums the
