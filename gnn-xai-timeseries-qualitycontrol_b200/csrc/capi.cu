@@ -197,7 +197,10 @@ int gnnqc_score_seq(gnnqc_model* m, const float* x_dev, int64_t n_seq, int32_t T
   if (int rc = need_device(m, "gnnqc_score_seq")) return rc;
   if (n_seq < 0 || T <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_score_seq: bad n_seq / T");
   if (n_seq > 0 && (!x_dev || !scores_dev)) return fail(GNNQC_ERR_ARG, "gnnqc_score_seq: null buffer");
-  return guarded([&] { m->dm.score_seq(x_dev, n_seq, T, scores_dev, static_cast<cudaStream_t>(stream)); });
+  return guarded([&] {
+    m->dm.refresh_tc();
+    m->dm.score_seq(x_dev, n_seq, T, scores_dev, static_cast<cudaStream_t>(stream));
+  });
 }
 
 int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom_dev, const int64_t* edges_dev,
@@ -210,6 +213,7 @@ int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom
   if (B > 0 && (!features_dev || !anom_dev || !edges_dev || !node_off_dev || !edge_off_dev || !scores_dev))
     return fail(GNNQC_ERR_ARG, "gnnqc_score_cml: null buffer");
   return guarded([&] {
+    m->dm.refresh_tc();
     m->dm.sync_host_params();
     m->dm.score_cml(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
                     reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, scores_dev,
@@ -228,6 +232,7 @@ int gnnqc_score_soilnet(gnnqc_model* m, const float* features_dev, const int64_t
   if (B > 0 && (!features_dev || !edges_dev || !node_off_dev || !edge_off_dev || !scores_dev))
     return fail(GNNQC_ERR_ARG, "gnnqc_score_soilnet: null buffer");
   return guarded([&] {
+    m->dm.refresh_tc();
     m->dm.sync_host_params();
     m->dm.score_soilnet(features_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
                         reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, n_edges_total, scores_dev,

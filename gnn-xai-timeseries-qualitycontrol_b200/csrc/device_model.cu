@@ -71,6 +71,7 @@ DeviceModel::~DeviceModel() {
     cudaFree(d_params);
     cudaFree(d_packed);
     cudaFree(d_packed_t);
+    cudaFree(d_packed_tc);
     cudaFree(d_scratch);
   }
 }
@@ -126,6 +127,26 @@ void DeviceModel::upload() {
   }
   if (!d_packed_t) GNNQC_CUDA(cudaMalloc(&d_packed_t, total_t * sizeof(float)));
   GNNQC_CUDA(cudaMemcpy(d_packed_t, packed_t.data(), total_t * sizeof(float), cudaMemcpyHostToDevice));
+
+  // bf16 hi/lo operand tiles for the layers that run on the tensor cores.
+  size_t total_tc = 0;
+  for (int l = 0; l < s.n_lstm; ++l) {
+    packed_tc_off[l] = total_tc;
+    total_tc += (tc_packed_bytes(s.lstm_in[l], s.lstm_hid[l]) + 255) / 256 * 256;
+  }
+  std::vector<unsigned char> packed_tc(total_tc, 0);
+  for (int l = 0; l < s.n_lstm; ++l)
+    tc_pack_host(host.params.data() + s.off_lstm_w[l], host.params.data() + s.off_lstm_u[l], host.params.data() + s.off_lstm_b[l],
+                 s.lstm_in[l], s.lstm_hid[l], packed_tc.data() + packed_tc_off[l]);
+  if (!d_packed_tc) GNNQC_CUDA(cudaMalloc(&d_packed_tc, total_tc));
+  GNNQC_CUDA(cudaMemcpy(d_packed_tc, packed_tc.data(), total_tc, cudaMemcpyHostToDevice));
+  tc_stale = false;
+}
+
+void DeviceModel::refresh_tc() {
+  if (!tc_stale) return;
+  sync_host_params();
+  upload();
 }
 
 void* DeviceModel::scratch(size_t bytes) {
@@ -233,6 +254,7 @@ void DeviceModel::configure_kernels() {
     const bool last = (l == s.n_lstm - 1);
     const bool pool = !last && (l % 2 == 1);
     layer_dispatch<true>(s.lstm_in[l], s.lstm_hid[l], pool, last, nullptr, nullptr, nullptr, 0, 0, 0, 0, 0, nullptr);
+    if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last)) tc_configure(s.lstm_in[l], s.lstm_hid[l], pool);
   }
   GNNQC_CUDA(cudaFuncSetAttribute(cml_frontend_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFeSmem)));
   if (s.lstm_hid[s.n_lstm - 1] != 128 || s.dense_units != 64)
@@ -250,8 +272,12 @@ void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, l
     float* out = (l % 2 == 0) ? buf_b : buf_a;
     static const char* const kNames[kMaxLstmLayers] = {"lstm_l1", "lstm_l2", "lstm_l3", "lstm_l4", "lstm_l5", "lstm_l6", "lstm_l7"};
     mark_begin(kNames[l], st);
-    layer_dispatch<false>(s.lstm_in[l], s.lstm_hid[l], pool, last, in, out, d_packed + packed_off[l], plan.t_run[l], t_in,
-                          plan.t_out[l], n_tiles, sm_count, st);
+    if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last))
+      tc_launch(s.lstm_in[l], s.lstm_hid[l], pool, in, out, d_packed_tc + packed_tc_off[l], plan.t_run[l], t_in, plan.t_out[l], n_tiles,
+                sm_count, st);
+    else
+      layer_dispatch<false>(s.lstm_in[l], s.lstm_hid[l], pool, last, in, out, d_packed + packed_off[l], plan.t_run[l], t_in,
+                            plan.t_out[l], n_tiles, sm_count, st);
     mark_end(st);
     in = out;
     t_in = plan.t_out[l];

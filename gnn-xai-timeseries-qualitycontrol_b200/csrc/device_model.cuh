@@ -41,7 +41,15 @@ struct LaunchRecord {
   cudaEvent_t start, stop;
 };
 
-struct TrainState;   // optimizer slots and per-step BN state (csrc/train.cu)
+struct TrainState;
+
+// Tensor-core LSTM layers (csrc/lstm_tc.cu).
+bool tc_layer_supported(int in, int hid, bool pool, bool last);
+size_t tc_packed_bytes(int in, int hid);
+void tc_pack_host(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out);
+void tc_configure(int in, int hid, bool pool);
+void tc_launch(int in, int hid, bool pool, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
+               int sm_count, cudaStream_t st);   // optimizer slots and per-step BN state (csrc/train.cu)
 
 struct DeviceModel {
   HostModel host;
@@ -52,6 +60,10 @@ struct DeviceModel {
   size_t packed_off[kMaxLstmLayers] = {0};
   float* d_packed_t = nullptr;  // per-layer transposed copy wT[col][Kpad] for the backward kernels
   size_t packed_t_off[kMaxLstmLayers] = {0};
+  unsigned char* d_packed_tc = nullptr;   // bf16 hi/lo operand tiles for the tensor-core layers
+  size_t packed_tc_off[kMaxLstmLayers] = {0};
+  bool tc_stale = false;                   // set by train_apply; refreshed lazily before scoring
+  void refresh_tc();
   void* d_scratch = nullptr;
   size_t scratch_bytes = 0;
 

@@ -304,6 +304,7 @@ int gnnqc_score_cml_series(gnnqc_model* m, const gnnqc_series* series, const int
   if (!target_dev || !t_anom_dev || !scores_dev) return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_score_cml_series: null buffer");
   try {
     using namespace gnnqc;
+    dm.refresh_tc();
     dm.sync_host_params();
     GNNQC_CUDA(cudaSetDevice(dm.device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);

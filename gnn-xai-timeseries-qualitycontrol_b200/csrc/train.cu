@@ -349,6 +349,7 @@ void DeviceModel::train_apply(float* rvec, const double* moments, float lr, cuda
     GNNQC_CUDA(cudaGetLastError());
   }
   params_dirty = true;
+  tc_stale = true;
 }
 
 }  // namespace gnnqc
