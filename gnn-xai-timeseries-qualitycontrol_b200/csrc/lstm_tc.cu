@@ -3,6 +3,7 @@
 #include <cuda_bf16.h>
 
 #include <algorithm>
+#include <cstdio>
 #include <cstdlib>
 #include <cstring>
 #include <vector>
@@ -19,9 +20,16 @@ struct TcLaunch {
   static auto kernel() { return lstm_tc_kernel<I, H, POOL>; }
   static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
   static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st) {
-    int per_sm = 1;
-    GNNQC_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel(), Cfg::NT, Cfg::SMEM_BYTES));
-    per_sm = std::max(1, std::min(per_sm, 512 / Cfg::TMEM_COLS));   // every resident CTA holds TMEM_COLS of the 512 TMEM columns
+    // The occupancy API answers 1 for kernels that allocate tensor memory, although CTAs do share an
+    // SM as long as their TMEM columns, shared memory and registers fit; size the persistent grid
+    // from those three limits directly.
+    cudaFuncAttributes fa;
+    GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
+    const int regs_per_cta = ((fa.numRegs + 7) / 8 * 8) * ((Cfg::NT + 31) / 32 * 32);
+    int per_sm = std::min({512 / Cfg::TMEM_COLS, static_cast<int>((227 * 1024) / (Cfg::SMEM_BYTES + fa.sharedSizeBytes + 1024)), 65536 / regs_per_cta});
+    if (const char* e = std::getenv("GNNQC_TC_CTAS")) per_sm = std::atoi(e);
+    per_sm = std::max(1, per_sm);
+    if (std::getenv("GNNQC_DEBUG")) std::fprintf(stderr, "[gnnqc] tc I=%d H=%d ctas/sm=%d regs=%d smem=%zu tmem_cols=%d\n", I, H, per_sm, fa.numRegs, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
     const long long n_pairs = (n_tiles + 1) / 2;
     const long long grid = std::min<long long>(n_pairs, static_cast<long long>(sm_count) * per_sm);
     kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles));
