@@ -254,7 +254,7 @@ void DeviceModel::configure_kernels() {
     const bool last = (l == s.n_lstm - 1);
     const bool pool = !last && (l % 2 == 1);
     layer_dispatch<true>(s.lstm_in[l], s.lstm_hid[l], pool, last, nullptr, nullptr, nullptr, 0, 0, 0, 0, 0, nullptr);
-    if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last)) tc_configure(s.lstm_in[l], s.lstm_hid[l], pool);
+    if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last)) tc_configure(s.lstm_in[l], s.lstm_hid[l], pool, last);
   }
   GNNQC_CUDA(cudaFuncSetAttribute(cml_frontend_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFeSmem)));
   if (s.lstm_hid[s.n_lstm - 1] != 128 || s.dense_units != 64)
@@ -273,7 +273,7 @@ void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, l
     static const char* const kNames[kMaxLstmLayers] = {"lstm_l1", "lstm_l2", "lstm_l3", "lstm_l4", "lstm_l5", "lstm_l6", "lstm_l7"};
     mark_begin(kNames[l], st);
     if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last))
-      tc_launch(s.lstm_in[l], s.lstm_hid[l], pool, in, out, d_packed_tc + packed_tc_off[l], plan.t_run[l], t_in, plan.t_out[l], n_tiles,
+      tc_launch(s.lstm_in[l], s.lstm_hid[l], pool, last, in, out, d_packed_tc + packed_tc_off[l], plan.t_run[l], t_in, plan.t_out[l], n_tiles,
                 sm_count, st);
     else
       layer_dispatch<false>(s.lstm_in[l], s.lstm_hid[l], pool, last, in, out, d_packed + packed_off[l], plan.t_run[l], t_in,

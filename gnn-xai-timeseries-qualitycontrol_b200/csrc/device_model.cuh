@@ -47,8 +47,8 @@ struct TrainState;
 bool tc_layer_supported(int in, int hid, bool pool, bool last);
 size_t tc_packed_bytes(int in, int hid);
 void tc_pack_host(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out);
-void tc_configure(int in, int hid, bool pool);
-void tc_launch(int in, int hid, bool pool, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
+void tc_configure(int in, int hid, bool pool, bool last);
+void tc_launch(int in, int hid, bool pool, bool last, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
                int sm_count, cudaStream_t st);   // optimizer slots and per-step BN state (csrc/train.cu)
 
 struct DeviceModel {

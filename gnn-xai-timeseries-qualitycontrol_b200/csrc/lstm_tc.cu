@@ -10,6 +10,7 @@
 
 #include "device_model.cuh"
 #include "lstm_tc.cuh"
+#include "lstm_tc_big.cuh"
 
 namespace gnnqc {
 namespace {
@@ -20,18 +21,33 @@ struct TcLaunch {
   static auto kernel() { return lstm_tc_kernel<I, H, POOL>; }
   static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
   static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st) {
-    // The occupancy API answers 1 for kernels that allocate tensor memory, although CTAs do share an
-    // SM as long as their TMEM columns, shared memory and registers fit; size the persistent grid
-    // from those three limits directly.
-    cudaFuncAttributes fa;
-    GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
-    const int regs_per_cta = ((fa.numRegs + 7) / 8 * 8) * ((Cfg::NT + 31) / 32 * 32);
-    int per_sm = std::min({512 / Cfg::TMEM_COLS, static_cast<int>((227 * 1024) / (Cfg::SMEM_BYTES + fa.sharedSizeBytes + 1024)), 65536 / regs_per_cta});
-    if (const char* e = std::getenv("GNNQC_TC_CTAS")) per_sm = std::atoi(e);
-    per_sm = std::max(1, per_sm);
-    if (std::getenv("GNNQC_DEBUG")) std::fprintf(stderr, "[gnnqc] tc I=%d H=%d ctas/sm=%d regs=%d smem=%zu tmem_cols=%d\n", I, H, per_sm, fa.numRegs, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
+    // One persistent CTA per SM (four window groups inside, lstm_tc.cuh); tiles are dealt evenly.
+    if (std::getenv("GNNQC_DEBUG")) {
+      cudaFuncAttributes fa;
+      GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
+      std::fprintf(stderr, "[gnnqc] tc I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
+    }
+    const long long grid = std::min<long long>(n_tiles, sm_count);
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles));
+    GNNQC_CUDA(cudaGetLastError());
+  }
+};
+
+// Wide layers (lstm_tc_big.cuh): one CTA per SM, weights resident (H = 64) or streamed (H = 128).
+template <int I, int H, bool POOL, bool LAST>
+struct TcBigLaunch {
+  static constexpr bool STREAM = (H > 64);
+  using Cfg = TcBigCfg<I, H, STREAM>;
+  static auto kernel() { return lstm_tc_big_kernel<I, H, POOL, LAST, STREAM>; }
+  static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
+  static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st) {
     const long long n_pairs = (n_tiles + 1) / 2;
-    const long long grid = std::min<long long>(n_pairs, static_cast<long long>(sm_count) * per_sm);
+    const long long grid = std::min<long long>(n_pairs, sm_count);
+    if (std::getenv("GNNQC_DEBUG")) {
+      cudaFuncAttributes fa;
+      GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
+      std::fprintf(stderr, "[gnnqc] tc-big I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
+    }
     kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles));
     GNNQC_CUDA(cudaGetLastError());
   }
@@ -55,7 +71,20 @@ bool tc_case(TcOp op, const TcArgs& a) {
   return true;
 }
 
-bool tc_dispatch(TcOp op, int in, int hid, bool pool, const TcArgs& a) {
+template <int I, int H, bool POOL, bool LAST>
+bool tc_big_case(TcOp op, const TcArgs& a) {
+  if (op == TcOp::Configure) TcBigLaunch<I, H, POOL, LAST>::configure();
+  else if (op == TcOp::Launch) TcBigLaunch<I, H, POOL, LAST>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st);
+  return true;
+}
+
+bool tc_is_big(int hid) { return hid >= 64; }
+
+bool tc_dispatch(TcOp op, int in, int hid, bool pool, bool last, const TcArgs& a) {
+  if (in == 32 && hid == 64 && !pool && !last) return tc_big_case<32, 64, false, false>(op, a);
+  if (in == 64 && hid == 64 && pool && !last) return tc_big_case<64, 64, true, false>(op, a);
+  if (in == 64 && hid == 128 && !pool && last) return tc_big_case<64, 128, false, true>(op, a);
+  if (last) return false;
 #define GNNQC_TC_CASE(I_, H_, POOL_) \
   if (in == I_ && hid == H_ && pool == POOL_) return tc_case<I_, H_, POOL_>(op, a);
   GNNQC_TC_CASE(2, 16, false)
@@ -74,7 +103,7 @@ int tc_max_hidden() {
     const char* e = std::getenv("GNNQC_TC");
     if (e && std::strcmp(e, "0") == 0) return 0;
     const char* m = std::getenv("GNNQC_TC_MAXH");
-    return m ? std::atoi(m) : 32;
+    return m ? std::atoi(m) : 128;
   }();
   return v;
 }
@@ -82,17 +111,44 @@ int tc_max_hidden() {
 }  // namespace
 
 bool tc_layer_supported(int in, int hid, bool pool, bool last) {
-  if (last || hid > tc_max_hidden()) return false;
-  return tc_dispatch(TcOp::Query, in, hid, pool, TcArgs());
+  if (hid > tc_max_hidden()) return false;
+  return tc_dispatch(TcOp::Query, in, hid, pool, last, TcArgs());
 }
 
 size_t tc_packed_bytes(int in, int hid) {
+  if (tc_is_big(hid)) {
+    const int kp = ((in + 7) / 8 * 8 + hid + 15) / 16 * 16;
+    return size_t(hid / 32) * (kp / 16) * 8192 + size_t(4 * hid) * 4;
+  }
   const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, n = 4 * hid;
   return size_t(2) * kp * n * 2 + size_t(n) * 4;
 }
 
 // B_hi | B_lo in [KP/8][N][8] bf16 (row n = Keras gate column, k = [inputs | pad | hidden | pad]), then bias.
 void tc_pack_host(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out) {
+  if (tc_is_big(hid)) {
+    // pieces [chunk of 32 units][K slice of 16]{hi, lo}, each half [2][128][8] bf16 with operand row
+    // n = gate * 32 + unit-in-chunk (lstm_tc_big.cuh), then the bias in Keras column order.
+    const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, kc_n = kp / 16, n4 = 4 * hid;
+    for (int c = 0; c < hid / 32; ++c)
+      for (int kc = 0; kc < kc_n; ++kc) {
+        __nv_bfloat16* hi = reinterpret_cast<__nv_bfloat16*>(out + (size_t(c) * kc_n + kc) * 8192);
+        __nv_bfloat16* lo = hi + 2048;
+        for (int kk = 0; kk < 16; ++kk)
+          for (int nrow = 0; nrow < 128; ++nrow) {
+            const int k = kc * 16 + kk, col = (nrow / 32) * hid + c * 32 + (nrow % 32);
+            float v = 0.f;
+            if (k < in) v = W[size_t(k) * n4 + col];
+            else if (k >= ip && k < ip + hid) v = U[size_t(k - ip) * n4 + col];
+            const __nv_bfloat16 h = __float2bfloat16_rn(v);
+            const size_t at = (size_t(kk / 8) * 128 + nrow) * 8 + (kk % 8);
+            hi[at] = h;
+            lo[at] = __float2bfloat16_rn(v - __bfloat162float(h));
+          }
+      }
+    std::memcpy(out + size_t(hid / 32) * kc_n * 8192, bias, size_t(n4) * 4);
+    return;
+  }
   const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, n = 4 * hid;
   __nv_bfloat16* bhi = reinterpret_cast<__nv_bfloat16*>(out);
   __nv_bfloat16* blo = bhi + size_t(kp) * n;
@@ -110,13 +166,13 @@ void tc_pack_host(const float* W, const float* U, const float* bias, int in, int
   std::memcpy(out + size_t(2) * kp * n * 2, bias, size_t(n) * 4);
 }
 
-void tc_configure(int in, int hid, bool pool) { tc_dispatch(TcOp::Configure, in, hid, pool, TcArgs()); }
+void tc_configure(int in, int hid, bool pool, bool last) { tc_dispatch(TcOp::Configure, in, hid, pool, last, TcArgs()); }
 
-void tc_launch(int in, int hid, bool pool, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
+void tc_launch(int in, int hid, bool pool, bool last, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
                int sm_count, cudaStream_t st) {
   TcArgs a;
   a.x = x; a.y = y; a.w = w; a.T = T; a.t_in = t_in; a.t_out = t_out; a.n_tiles = n_tiles; a.sm_count = sm_count; a.st = st;
-  if (!tc_dispatch(TcOp::Launch, in, hid, pool, a)) throw std::invalid_argument("no tensor-core kernel for this layer shape");
+  if (!tc_dispatch(TcOp::Launch, in, hid, pool, last, a)) throw std::invalid_argument("no tensor-core kernel for this layer shape");
 }
 
 }  // namespace gnnqc
