@@ -124,6 +124,7 @@ size_t tc_packed_bytes(int in, int hid) {
   return size_t(2) * kp * n * 2 + size_t(n) * 4;
 }
 
+// Gate columns are pre-multiplied by the factor of their exponential (lstm_cell_tc).
 // B_hi | B_lo in [KP/8][N][8] bf16 (row n = Keras gate column, k = [inputs | pad | hidden | pad]), then bias.
 void tc_pack_host(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out) {
   if (tc_is_big(hid)) {
@@ -140,13 +141,15 @@ void tc_pack_host(const float* W, const float* U, const float* bias, int in, int
             float v = 0.f;
             if (k < in) v = W[size_t(k) * n4 + col];
             else if (k >= ip && k < ip + hid) v = U[size_t(k - ip) * n4 + col];
+            v *= tc_gate_scale(nrow / 32);
             const __nv_bfloat16 h = __float2bfloat16_rn(v);
             const size_t at = (size_t(kk / 8) * 128 + nrow) * 8 + (kk % 8);
             hi[at] = h;
             lo[at] = __float2bfloat16_rn(v - __bfloat162float(h));
           }
       }
-    std::memcpy(out + size_t(hid / 32) * kc_n * 8192, bias, size_t(n4) * 4);
+    float* bout = reinterpret_cast<float*>(out + size_t(hid / 32) * kc_n * 8192);
+    for (int col = 0; col < n4; ++col) bout[col] = bias[col] * tc_gate_scale(col / hid);
     return;
   }
   const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, n = 4 * hid;
@@ -157,13 +160,15 @@ void tc_pack_host(const float* W, const float* U, const float* bias, int in, int
       float v = 0.f;
       if (k < in) v = W[size_t(k) * n + col];
       else if (k >= ip && k < ip + hid) v = U[size_t(k - ip) * n + col];
+      v *= tc_gate_scale(col / hid);
       const __nv_bfloat16 h = __float2bfloat16_rn(v);
       const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
       const size_t at = (size_t(k / 8) * n + col) * 8 + (k % 8);
       bhi[at] = h;
       blo[at] = l;
     }
-  std::memcpy(out + size_t(2) * kp * n * 2, bias, size_t(n) * 4);
+  float* bout = reinterpret_cast<float*>(out + size_t(2) * kp * n * 2);
+  for (int col = 0; col < n; ++col) bout[col] = bias[col] * tc_gate_scale(col / hid);
 }
 
 void tc_configure(int in, int hid, bool pool, bool last) { tc_dispatch(TcOp::Configure, in, hid, pool, last, TcArgs()); }

@@ -80,6 +80,38 @@ __device__ __forceinline__ void split8(const float (&v)[8], uint4& hi, uint4& lo
   lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
+// Cell update on pre-scaled pre-activations.  The packed weights and biases of the tensor-core
+// layers carry the factors of the exponentials (-log2 e for the i, f, o columns, -2 log2 e for the
+// candidate column, kTcGateScale), so the accumulator plus bias IS the ex2 argument:
+//   a = e^-zi, f = e^-zf, g = e^-2zg, o = e^-zo,
+//   c' = [c (1+a)(1+g) + (1-g)(1+f)] / [(1+f)(1+a)(1+g)],  h = (1-e^-2c') / [(1+o)(1+e^-2c')].
+// Only large POSITIVE arguments can overflow the products, so one min per exponential is enough
+// (2^36 ~ e^25: sigmoid error < 2e-11); 5 ex2 + 2 rcp on the MUFU pipe, 20 other instructions.
+__host__ __device__ constexpr float tc_gate_scale(int gate) { return gate == 2 ? -2.8853900817779268f : -1.4426950408889634f; }
+
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float lstm_cell_tc(float ei, float ef, float eg, float eo, float& c) {
+  constexpr float kCap = 36.f;
+  const float a = ex2_approx(fminf(ei, kCap));
+  const float f = ex2_approx(fminf(ef, kCap));
+  const float g = ex2_approx(fminf(eg, kCap));
+  const float o = ex2_approx(fminf(eo, kCap));
+  const float g1 = 1.f + g;
+  const float pa = fmaf(a, g1, g1);          // (1+a)(1+g)
+  const float pf = 1.f + f;
+  const float tg = fmaf(-g, pf, pf);         // (1-g)(1+f)
+  const float cn = fmaf(c, pa, tg) * rcp_approx(pf * pa);
+  c = cn;
+  const float e = ex2_approx(fminf(cn * tc_gate_scale(2), kCap));
+  const float e1 = 1.f + e;
+  const float r = rcp_approx(fmaf(o, e1, e1));   // 1 / [(1+o)(1+e)]
+  return fmaf(-e, r, r);
+}
+
 template <int I, int H, bool POOL>
 __global__ void __launch_bounds__((TcCfg<I, H>::NT), 1)
 lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_stride][I][64]
@@ -217,7 +249,7 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
         const int j0 = b8 * 8;
 #pragma unroll
         for (int i = 0; i < 8; ++i)
-          hv[i] = lstm_cell_fused(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
+          hv[i] = lstm_cell_tc(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
                                   zo[i] + bias[3 * H + j0 + i], cst[j0 + i]);
         if (POOL) {
           const int ph = t % 3;

@@ -227,7 +227,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
           const int l0 = ci * C::UB + b8 * 8;      // its slot in cst / pmax
 #pragma unroll
           for (int i = 0; i < 8; ++i)
-            hv[i] = lstm_cell_fused(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
+            hv[i] = lstm_cell_tc(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
                                     zo[i] + bias[3 * H + j0 + i], cst[l0 + i]);
           if (POOL) {
             const int ph = t % 3;
