@@ -256,7 +256,8 @@ void DeviceModel::configure_kernels() {
     layer_dispatch<true>(s.lstm_in[l], s.lstm_hid[l], pool, last, nullptr, nullptr, nullptr, 0, 0, 0, 0, 0, nullptr);
     if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last)) tc_configure(s.lstm_in[l], s.lstm_hid[l], pool, last);
   }
-  GNNQC_CUDA(cudaFuncSetAttribute(cml_frontend_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFeSmem)));
+  configure_cml_frontend();
+  GNNQC_CUDA(cudaGetLastError());
   if (s.lstm_hid[s.n_lstm - 1] != 128 || s.dense_units != 64)
     throw std::invalid_argument("head kernel supports a 128 -> 64 -> 64 -> 1 head only");
 }
@@ -374,15 +375,12 @@ void DeviceModel::score_cml(const float* feat, const float* anom, const long lon
     dim3 grid(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
     mark_begin("cml_frontend", st);
     static const bool plain_frontend = [] { const char* e = std::getenv("GNNQC_FRONTEND"); return e && std::strcmp(e, "plain") == 0; }();
-    if (plain_frontend) {
+    if (plain_frontend)   // A/B: direct loads, one CTA per (tile, 32 steps)
       cml_frontend_kernel<<<grid, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), reinterpret_cast<const float2*>(anom) + win0 * T,
                                                 coef, node_off + win0, folded, buf_a, nw, T, plan.t_run[0]);
-    } else {
-      dim3 grid_tma(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + kFeTch - 1) / kFeTch));
-      cml_frontend_tma_kernel<<<grid_tma, 256, kFeSmem, st>>>(reinterpret_cast<const float2*>(feat), n_nodes * T,
-                                                              reinterpret_cast<const float2*>(anom) + win0 * T, coef, node_off + win0, folded,
-                                                              buf_a, nw, T, plan.t_run[0], 1.f);
-    }
+    else
+      launch_cml_frontend(reinterpret_cast<const float2*>(feat), n_nodes * T, reinterpret_cast<const float2*>(anom) + win0 * T, coef,
+                          node_off + win0, folded, buf_a, nw, T, plan.t_run[0], nt, 1.f, sm_count, st);
     GNNQC_CUDA(cudaGetLastError());
     mark_end(st);
     run_stack(plan, buf_a, buf_b, nt, nw, scores + win0, st);

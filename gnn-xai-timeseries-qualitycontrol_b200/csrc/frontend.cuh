@@ -126,6 +126,29 @@ struct PoolAcc {
       sabs[c] = fmaf(cf, fabsf(z), sabs[c]);
     }
   }
+  // Same update with z formed two channels at a time (fma.rn.f32x2: the scalar input is a broadcast
+  // operand and the channel-pair constants stay in uniform registers when `p` is a kernel parameter).
+  __device__ __forceinline__ void add_packed(const GcnFolded& p, float2 v, float cf) {
+    s0 = fmaf(cf, v.x, s0);
+    s1 = fmaf(cf, v.y, s1);
+    sc += cf;
+    unsigned long long vx, vy;
+    asm("mov.b64 %0, {%1, %1};" : "=l"(vx) : "f"(v.x));
+    asm("mov.b64 %0, {%1, %1};" : "=l"(vy) : "f"(v.y));
+#pragma unroll
+    for (int c = 0; c < kGcnChannelsDev; c += 2) {
+      unsigned long long z, a0, a1;
+      asm("mov.b64 %0, {%1, %2};" : "=l"(z) : "f"(p.c[c]), "f"(p.c[c + 1]));
+      asm("mov.b64 %0, {%1, %2};" : "=l"(a0) : "f"(p.a[0][c]), "f"(p.a[0][c + 1]));
+      asm("mov.b64 %0, {%1, %2};" : "=l"(a1) : "f"(p.a[1][c]), "f"(p.a[1][c + 1]));
+      asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(z) : "l"(vy), "l"(a1));
+      asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(z) : "l"(vx), "l"(a0));
+      float z0, z1;
+      asm("mov.b64 {%0, %1}, %2;" : "=f"(z0), "=f"(z1) : "l"(z));
+      sabs[c] = fmaf(cf, fabsf(z0), sabs[c]);
+      sabs[c + 1] = fmaf(cf, fabsf(z1), sabs[c + 1]);
+    }
+  }
   __device__ __forceinline__ float pooled(const GcnFolded& p, int c) const {
     const float lin = fmaf(p.a[0][c], s0, fmaf(p.a[1][c], s1, p.c[c] * sc));
     return fmaf(0.5f * (1.f + p.alpha[c]), lin, 0.5f * (1.f - p.alpha[c]) * sabs[c]);
@@ -186,79 +209,144 @@ static __global__ void __launch_bounds__(256) cml_frontend_devparam_kernel(const
   cml_frontend_body(feat, anom, coef, node_off, p, out, n_windows, T, t_run, 1.f);
 }
 
-// ---- CML front-end, TMA-staged --------------------------------------------------------------
-// Same arithmetic as cml_frontend_kernel, but each window's slab of kFeTch timesteps (a contiguous
-// kFeTch*N_b*8-byte run of the features array) is fetched with ONE cp.async.bulk (TMA) into its
-// own shared-memory slot, all 64 windows of the tile signalling one mbarrier; the threads then
-// read the slab from shared memory instead of streaming 8-byte pieces of 64 different rows.
-// The features array only guarantees 8-byte alignment per window (N_b*T can be odd), so the copy
-// starts at the enclosing 16-byte boundary and the reader skips the 0 or 8 lead bytes.  Windows
-// with more than kFeCap nodes, or whose rounded-up copy would run past the end of the array,
-// take the direct-load path (slot flag -1).
-constexpr int kFeTch = 4;                                   // timesteps per CTA
-constexpr int kFeCap = 32;                                  // nodes per window staged through smem
-constexpr int kFeSlot = kFeTch * kFeCap * 8 + 16;           // bytes per window slot (16 * odd)
-constexpr size_t kFeSmem = size_t(kTile) * kFeSlot + kTile * sizeof(int) + 16;
+// ---- CML front-end, persistent, TMA-staged and double-buffered --------------------------------
+// Same arithmetic as cml_frontend_kernel.  A window's slab of 8 timesteps (a contiguous
+// 8*N_b*8-byte run of the features array) is fetched with ONE cp.async.bulk (TMA) into its own
+// shared-memory slot, the 16 windows of an item signalling one mbarrier; the threads then read the
+// slab from shared memory instead of streaming 8-byte pieces of many different rows.  The features
+// array only guarantees 8-byte alignment per window (N_b*T can be odd), so the copy starts at the
+// enclosing 16-byte boundary and the reader skips the 0 or 8 lead bytes.  Windows with more than
+// kFsCap nodes, or whose rounded-up copy would run past the end of the array, take direct loads.
+// A CTA of 128 threads (lane = 16 windows x 8 steps) walks a contiguous range of (16-window block,
+// step octet) items with two slab buffers, so the copy of the next item is always in flight under
+// the arithmetic of the current one, and a buffer is refilled with item i+2 as soon as every
+// thread is done with item i.  The block's node coefficients sit in shared memory for its ~20 items.
+constexpr int kFsWin = 16;                                  // windows per item
+constexpr int kFsSteps = 8;                                 // timesteps per item
+constexpr int kFsThreads = kFsWin * kFsSteps;
+constexpr int kFsCap = 32;                                  // nodes per window staged through smem
+constexpr int kFsSlot = kFsSteps * kFsCap * 8 + 16;         // bytes per window slot (16 * odd)
+constexpr int kFsSlab = kFsWin * kFsSlot;
+constexpr int kFsCoefStride = kFsCap + 1;                   // per-window coefficient row in smem (odd: no bank conflicts)
+constexpr size_t kFsSmem = 2 * size_t(kFsSlab) + 2 * kFsWin * sizeof(int) + 2 * 8 + 16 + kFsWin * kFsCoefStride * sizeof(float);
+constexpr int kFsCtasPerSm = 3;
 
-static __global__ void __launch_bounds__(256) cml_frontend_tma_kernel(const float2* __restrict__ feat, long long feat_rows,
-                                                                      const float2* __restrict__ anom, const float* __restrict__ coef,
-                                                                      const int* __restrict__ node_off, const GcnFolded p,
-                                                                      float* __restrict__ out, long long n_windows, int T, int t_run,
-                                                                      float alpha) {
-  extern __shared__ __align__(128) unsigned char fe_smem[];
-  unsigned char* slots = fe_smem;
-  int* lead_s = reinterpret_cast<int*>(fe_smem + size_t(kTile) * kFeSlot);
-  uint64_t* bar = reinterpret_cast<uint64_t*>(fe_smem + size_t(kTile) * kFeSlot + kTile * sizeof(int));
-  const int tid = threadIdx.x, b = tid & 63, tq = tid >> 6;
-  const long long tile = blockIdx.x;
-  const long long win = tile * kTile + b;
-  const int t0 = blockIdx.y * kFeTch;
-  const int tch = min(kFeTch, t_run - t0);
-  const bool live = win < n_windows;
-  const int n0 = live ? node_off[win] : 0;
-  const int nn = live ? node_off[win + 1] - n0 : 0;
-  if (tid == 0) {
-    ptx::mbar_init(bar, kTile);
+static __global__ void __launch_bounds__(kFsThreads) cml_frontend_stream_kernel(const float2* __restrict__ feat, long long feat_rows,
+                                                                                const float2* __restrict__ anom, const float* __restrict__ coef,
+                                                                                const int* __restrict__ node_off, const GcnFolded p,
+                                                                                float* __restrict__ out, long long n_windows, int T, int t_run,
+                                                                                int n_tiles, float alpha) {
+  extern __shared__ __align__(128) unsigned char fs_smem[];
+  int* lead_s = reinterpret_cast<int*>(fs_smem + 2 * kFsSlab);                         // [2][kFsWin]
+  uint64_t* full = reinterpret_cast<uint64_t*>(fs_smem + 2 * kFsSlab + 2 * kFsWin * sizeof(int));   // [2]
+  float* coef_s = reinterpret_cast<float*>(fs_smem + 2 * kFsSlab + 2 * kFsWin * sizeof(int) + 32);  // [kFsWin][kFsCoefStride]
+  const int r = threadIdx.x, tq = r / kFsWin, bl = r % kFsWin;
+  const int NTO = (t_run + kFsSteps - 1) / kFsSteps;
+  const long long items = static_cast<long long>(n_tiles) * (kTile / kFsWin) * NTO;
+  const long long i0 = items * blockIdx.x / gridDim.x, i1 = items * (blockIdx.x + 1) / gridDim.x;
+  if (r == 0) {
+    ptx::mbar_init(&full[0], kFsWin);
+    ptx::mbar_init(&full[1], kFsWin);
     ptx::mbar_init_fence();
   }
   __syncthreads();
-  if (tid < kTile) {   // thread b issues the copy of window b
-    int lead = -1;
-    if (live && nn > 0 && nn <= kFeCap) {
-      const long long first_row = static_cast<long long>(n0) * T + static_cast<long long>(t0) * nn;   // float2 index
-      const unsigned long long addr = reinterpret_cast<unsigned long long>(feat + first_row);
-      const int ld = static_cast<int>(addr & 15ull);
-      const unsigned bytes = (static_cast<unsigned>(ld) + static_cast<unsigned>(tch * nn) * 8u + 15u) & ~15u;
-      const unsigned long long end = reinterpret_cast<unsigned long long>(feat + feat_rows);
-      if (addr - ld + bytes <= end) {
-        lead = ld;
-        ptx::mbar_arrive_expect_tx(bar, bytes);
-        ptx::bulk_load(slots + size_t(b) * kFeSlot, reinterpret_cast<const void*>(addr - ld), bytes, bar);
+
+  // thread r < 16 requests window r's slab of an item into buffer s.
+  // lead_s: >= 0 byte offset of the first row inside the slot (0 for a window without nodes), -1 direct loads.
+  auto issue_slab = [&](long long item, int s) {
+    const long long blk_n = item / NTO;
+    const int t0n = static_cast<int>(item % NTO) * kFsSteps;
+    const int tchn = min(kFsSteps, t_run - t0n);
+    const long long winn = blk_n * kFsWin + r;
+    int lead = 0;
+    bool copied = false;
+    if (winn < n_windows) {
+      const int n0n = node_off[winn], nnn = node_off[winn + 1] - n0n;
+      if (nnn > 0) {
+        lead = -1;
+        const long long first_row = static_cast<long long>(n0n) * T + static_cast<long long>(t0n) * nnn;   // float2 index
+        const unsigned long long addr = reinterpret_cast<unsigned long long>(feat + first_row);
+        const int ld = static_cast<int>(addr & 15ull);
+        const unsigned bytes = (static_cast<unsigned>(ld) + static_cast<unsigned>(tchn * nnn) * 8u + 15u) & ~15u;
+        const unsigned long long end = reinterpret_cast<unsigned long long>(feat + feat_rows);
+        if (nnn <= kFsCap && addr - ld + bytes <= end) {
+          lead = ld;
+          copied = true;
+          ptx::mbar_arrive_expect_tx(&full[s], bytes);
+          ptx::bulk_load(fs_smem + size_t(s) * kFsSlab + size_t(r) * kFsSlot, reinterpret_cast<const void*>(addr - ld), bytes, &full[s]);
+        }
       }
     }
-    lead_s[b] = lead;
-    if (lead < 0) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(ptx::smem_addr(bar)) : "memory");
+    lead_s[s * kFsWin + r] = lead;
+    if (!copied) asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(ptx::smem_addr(&full[s])) : "memory");
+  };
+  if (r < kFsWin) {
+    if (i0 < i1) issue_slab(i0, 0);
+    if (i0 + 1 < i1) issue_slab(i0 + 1, 1);
   }
-  __syncthreads();        // lead_s visible
-  ptx::mbar_wait(bar, 0);
-  const int t = t0 + tq;
-  if (tq >= tch) return;
+
   constexpr int CH = 2 + kGcnChannelsDev;
-  PoolAcc acc;
-  const int lead = lead_s[b];
-  const float2* srow = reinterpret_cast<const float2*>(slots + size_t(b) * kFeSlot + (lead < 0 ? 0 : lead)) + tq * nn;
-  const float2* grow = feat + (static_cast<long long>(n0) * T + static_cast<long long>(t) * nn);
-  for (int n = 0; n < nn; ++n) {
-    float2 v = (lead >= 0) ? srow[n] : __ldg(grow + n);
-    v.x *= alpha; v.y *= alpha;   // integrated-gradients path scaling; exact no-op for alpha == 1
-    acc.add(p, v, __ldg(coef + n0 + n));
-  }
-  const float2 av = live ? __ldg(anom + win * T + t) : make_float2(0.f, 0.f);
-  float* o = out + ((tile * t_run + t) * CH) * kTile + b;
-  o[0] = av.x * alpha;
-  o[kTile] = av.y * alpha;
+  long long cur_blk = -1;
+  int n0 = 0, nn = 0;
+  for (long long it = i0; it < i1; ++it) {
+    const int s = static_cast<int>((it - i0) & 1);
+    const long long blk = it / NTO;
+    const int t = static_cast<int>(it % NTO) * kFsSteps + tq;
+    const long long win = blk * kFsWin + bl;
+    const bool live = win < n_windows;
+    if (blk != cur_blk) {
+      cur_blk = blk;
+      n0 = live ? node_off[win] : 0;
+      nn = live ? node_off[win + 1] - n0 : 0;
+      // the block's node coefficients stay in shared memory for its ~20 items
+      for (int n = tq; n < min(nn, kFsCap); n += kFsSteps) coef_s[bl * kFsCoefStride + n] = __ldg(coef + n0 + n);
+      __syncthreads();
+    }
+    ptx::mbar_wait(&full[s], static_cast<uint32_t>(((it - i0) >> 1) & 1));
+    if (t < t_run) {
+      const int lead = lead_s[s * kFsWin + bl];
+      const float2* srow = reinterpret_cast<const float2*>(fs_smem + size_t(s) * kFsSlab + size_t(bl) * kFsSlot + (lead < 0 ? 0 : lead)) + tq * nn;
+      const float2* grow = feat + (static_cast<long long>(n0) * T + static_cast<long long>(t) * nn);
+      const float* crow = coef + n0;
+      const float* cs = coef_s + bl * kFsCoefStride;
+      PoolAcc acc;
+      if (lead >= 0) {   // implies nn <= kFsCap
+#pragma unroll 4
+        for (int n = 0; n < nn; ++n) {
+          float2 v = srow[n];
+          v.x *= alpha; v.y *= alpha;   // integrated-gradients path scaling; exact no-op for alpha == 1
+          acc.add_packed(p, v, cs[n]);
+        }
+      } else {
+        for (int n = 0; n < nn; ++n) {
+          float2 v = __ldg(grow + n);
+          v.x *= alpha; v.y *= alpha;
+          acc.add_packed(p, v, __ldg(crow + n));
+        }
+      }
+      const float2 av = live ? __ldg(anom + win * T + t) : make_float2(0.f, 0.f);
+      float* o = out + (((win / kTile) * t_run + t) * CH) * kTile + (win % kTile);
+      o[0] = av.x * alpha;
+      o[kTile] = av.y * alpha;
 #pragma unroll
-  for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc.pooled(p, c);
+      for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc.pooled(p, c);
+    }
+    __syncthreads();   // everyone is done with buffer s
+    if (r < kFsWin && it + 2 < i1) issue_slab(it + 2, s);
+  }
+}
+
+// Launch helper: grid sized to the SM count, dynamic shared memory opted in by configure_cml_frontend().
+inline void configure_cml_frontend() {
+  cudaFuncSetAttribute(cml_frontend_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFsSmem));
+}
+inline void launch_cml_frontend(const float2* feat, long long feat_rows, const float2* anom, const float* coef, const int* node_off,
+                                const GcnFolded& p, float* out, long long n_windows, int T, int t_run, long long n_tiles, float alpha,
+                                int sm_count, cudaStream_t st) {
+  const long long items = n_tiles * (kTile / kFsWin) * ((t_run + kFsSteps - 1) / kFsSteps);
+  const long long grid = items < static_cast<long long>(sm_count) * kFsCtasPerSm ? items : static_cast<long long>(sm_count) * kFsCtasPerSm;
+  cml_frontend_stream_kernel<<<static_cast<unsigned>(grid > 0 ? grid : 1), kFsThreads, kFsSmem, st>>>(feat, feat_rows, anom, coef, node_off, p, out,
+                                                                                                     n_windows, T, t_run, static_cast<int>(n_tiles), alpha);
 }
 
 // ---- dense head: [tile][128][64] -> sigmoid(Dense(LeakyReLU(Dense(LeakyReLU(Dense))))) ------

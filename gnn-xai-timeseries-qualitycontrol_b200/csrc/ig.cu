@@ -132,7 +132,8 @@ GcnFolded fold_gcn_params(const HostModel& m) {
 void DeviceModel::configure_ig_kernels() {
   const ModelSpec& s = host.spec;
   if (!s.has_gcn || s.soilnet) return;
-  GNNQC_CUDA(cudaFuncSetAttribute(cml_frontend_tma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFeSmem)));
+  configure_cml_frontend();
+  GNNQC_CUDA(cudaGetLastError());
   LayerArgs none;
   for (int l = 0; l < s.n_lstm; ++l) {
     const bool last = (l == s.n_lstm - 1);
@@ -191,14 +192,13 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
   for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
     const long long nt = std::min(chunk, n_tiles - t0);
     const long long win0 = t0 * kTile, nw = std::min<long long>(B - win0, nt * kTile);
-    const dim3 grid_tma(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + kFeTch - 1) / kFeTch));
     const float2* feat2 = reinterpret_cast<const float2*>(feat);
     const float2* anom2 = reinterpret_cast<const float2*>(anom) + win0 * T;
     for (int k = 0; k <= m_steps; ++k) {
       const float alpha = static_cast<float>(k) / static_cast<float>(m_steps);
       const float wk = ((k == 0 || k == m_steps) ? 0.5f : 1.0f) / static_cast<float>(m_steps);
       mark_begin("ig_frontend", st);
-      cml_frontend_tma_kernel<<<grid_tma, 256, kFeSmem, st>>>(feat2, n_nodes * T, anom2, coef, node_off + win0, folded, buf_a, nw, T, plan.t_run[0], alpha);
+      launch_cml_frontend(feat2, n_nodes * T, anom2, coef, node_off + win0, folded, buf_a, nw, T, plan.t_run[0], nt, alpha, sm_count, st);
       GNNQC_CUDA(cudaGetLastError());
       mark_end(st);
       // forward, saving gates
