@@ -49,7 +49,8 @@ size_t tc_packed_bytes(int in, int hid);
 void tc_pack_host(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out);
 void tc_configure(int in, int hid, bool pool, bool last);
 void tc_launch(int in, int hid, bool pool, bool last, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
-               int sm_count, cudaStream_t st);   // optimizer slots and per-step BN state (csrc/train.cu)
+               int sm_count, cudaStream_t st, float* save = nullptr, float* amax = nullptr);   // save != nullptr: also store gates (IG forward)
+// optimizer slots and per-step BN state (csrc/train.cu)
 
 struct DeviceModel {
   HostModel host;

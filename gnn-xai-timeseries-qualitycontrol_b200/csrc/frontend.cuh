@@ -365,6 +365,7 @@ __global__ void __launch_bounds__(256) head_kernel(const float* __restrict__ y7,
   float acc[DQ];
 #pragma unroll
   for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b1 + q * DQ + o);
+#pragma unroll 8
   for (int k = 0; k < HL; ++k) {
     const float h = __ldg(y7 + (tile * HL + k) * kTile + b);
 #pragma unroll
@@ -375,6 +376,7 @@ __global__ void __launch_bounds__(256) head_kernel(const float* __restrict__ y7,
   __syncthreads();
 #pragma unroll
   for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b2 + q * DQ + o);
+#pragma unroll 8
   for (int k = 0; k < D; ++k) {
     const float h = d1_s[k * kTile + b];
 #pragma unroll
@@ -473,6 +475,7 @@ __global__ void __launch_bounds__(256) head_grad_kernel(const float* __restrict_
   float acc[DQ];
 #pragma unroll
   for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b1 + q * DQ + o);
+#pragma unroll 8
   for (int k = 0; k < HL; ++k) {
     const float h = __ldg(y7 + (tile * HL + k) * kTile + b);
 #pragma unroll
@@ -486,6 +489,7 @@ __global__ void __launch_bounds__(256) head_grad_kernel(const float* __restrict_
   __syncthreads();
 #pragma unroll
   for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b2 + q * DQ + o);
+#pragma unroll 8
   for (int k = 0; k < D; ++k) {
     const float h = d1_s[k * kTile + b];
 #pragma unroll

@@ -79,6 +79,7 @@ struct LayerArgs {
   const float* in = nullptr;   // forward: x tile; backward: dy
   float* out = nullptr;        // forward: y tile; backward: dx
   const float* w = nullptr;    // forward: packed; backward: transposed
+  const unsigned char* wtc = nullptr;   // forward: tensor-core operand tiles (null: fp32 kernel)
   float* save = nullptr;
   float* amax = nullptr;
   int T = 0, t_in = 0, t_out = 0;
@@ -93,6 +94,8 @@ void layer_op(Op op, const LayerArgs& a) {
     FwdSave<I, H, POOL, LAST>::configure();
     Bwd<I, H, POOL, LAST>::configure();
   } else if (op == Op::Forward) {
+    if (a.wtc && tc_layer_supported(I, H, POOL, LAST))   // gate contraction on the tensor cores (lstm_tc.cuh, SAVE mode)
+      return tc_launch(I, H, POOL, LAST, a.in, a.out, a.wtc, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax);
     FwdSave<I, H, POOL, LAST>::launch(a.in, a.out, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.save, a.amax, a.st);
   } else {
     Bwd<I, H, POOL, LAST>::launch(a.in, a.save, a.amax, a.w, a.out, a.T, a.n_tiles, a.sm_count, a.st);
@@ -147,6 +150,9 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
   if (B <= 0) return;
   const ModelSpec& s = host.spec;
   GNNQC_CUDA(cudaSetDevice(device));
+  refresh_tc();
+  // GNNQC_IG_TC=0: forward passes on the fp32 CUDA-core kernels (A/B)
+  static const bool ig_tc = [] { const char* e = std::getenv("GNNQC_IG_TC"); return !(e && std::strcmp(e, "0") == 0); }();
   StackPlan plan(s, T);
   const int L = s.n_lstm;
   const long long n_tiles = (B + kTile - 1) / kTile;
@@ -208,6 +214,7 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
         const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
         LayerArgs a;
         a.in = in; a.out = (l % 2 == 0) ? buf_b : buf_a; a.w = d_packed + packed_off[l];
+        a.wtc = ig_tc ? d_packed_tc + packed_tc_off[l] : nullptr;
         a.save = reinterpret_cast<float*>(saves + size_t(chunk) * save_off[l]);
         a.amax = pool ? reinterpret_cast<float*>(saves + size_t(chunk) * amax_off[l]) : nullptr;
         a.T = plan.t_run[l]; a.t_in = t_in; a.t_out = plan.t_out[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;

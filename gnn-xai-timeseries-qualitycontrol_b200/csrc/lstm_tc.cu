@@ -15,12 +15,13 @@
 namespace gnnqc {
 namespace {
 
-template <int I, int H, bool POOL>
+template <int I, int H, bool POOL, bool SAVE>
 struct TcLaunch {
   using Cfg = TcCfg<I, H>;
-  static auto kernel() { return lstm_tc_kernel<I, H, POOL>; }
+  static auto kernel() { return lstm_tc_kernel<I, H, POOL, SAVE>; }
   static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
-  static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st) {
+  static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st,
+                     float* save, float* amax) {
     // One persistent CTA per SM (four window groups inside, lstm_tc.cuh); tiles are dealt evenly.
     if (std::getenv("GNNQC_DEBUG")) {
       cudaFuncAttributes fa;
@@ -28,19 +29,20 @@ struct TcLaunch {
       std::fprintf(stderr, "[gnnqc] tc I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
     }
     const long long grid = std::min<long long>(n_tiles, sm_count);
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles));
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax);
     GNNQC_CUDA(cudaGetLastError());
   }
 };
 
 // Wide layers (lstm_tc_big.cuh): one CTA per SM, weights resident (H = 64) or streamed (H = 128).
-template <int I, int H, bool POOL, bool LAST>
+template <int I, int H, bool POOL, bool LAST, bool SAVE>
 struct TcBigLaunch {
   static constexpr bool STREAM = (H > 64);
   using Cfg = TcBigCfg<I, H, STREAM>;
-  static auto kernel() { return lstm_tc_big_kernel<I, H, POOL, LAST, STREAM>; }
+  static auto kernel() { return lstm_tc_big_kernel<I, H, POOL, LAST, STREAM, SAVE>; }
   static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
-  static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st) {
+  static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st,
+                     float* save, float* amax) {
     const long long n_pairs = (n_tiles + 1) / 2;
     const long long grid = std::min<long long>(n_pairs, sm_count);
     if (std::getenv("GNNQC_DEBUG")) {
@@ -48,7 +50,7 @@ struct TcBigLaunch {
       GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
       std::fprintf(stderr, "[gnnqc] tc-big I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
     }
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles));
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax);
     GNNQC_CUDA(cudaGetLastError());
   }
 };
@@ -62,19 +64,31 @@ struct TcArgs {
   int T = 0, t_in = 0, t_out = 0, sm_count = 0;
   long long n_tiles = 0;
   cudaStream_t st = nullptr;
+  float* save = nullptr;   // non-null: the gate-saving variant (integrated gradients forward)
+  float* amax = nullptr;
 };
 
 template <int I, int H, bool POOL>
 bool tc_case(TcOp op, const TcArgs& a) {
-  if (op == TcOp::Configure) TcLaunch<I, H, POOL>::configure();
-  else if (op == TcOp::Launch) TcLaunch<I, H, POOL>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st);
+  if (op == TcOp::Configure) {
+    TcLaunch<I, H, POOL, false>::configure();
+    TcLaunch<I, H, POOL, true>::configure();
+  } else if (op == TcOp::Launch) {
+    if (a.save) TcLaunch<I, H, POOL, true>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax);
+    else TcLaunch<I, H, POOL, false>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, nullptr, nullptr);
+  }
   return true;
 }
 
 template <int I, int H, bool POOL, bool LAST>
 bool tc_big_case(TcOp op, const TcArgs& a) {
-  if (op == TcOp::Configure) TcBigLaunch<I, H, POOL, LAST>::configure();
-  else if (op == TcOp::Launch) TcBigLaunch<I, H, POOL, LAST>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st);
+  if (op == TcOp::Configure) {
+    TcBigLaunch<I, H, POOL, LAST, false>::configure();
+    TcBigLaunch<I, H, POOL, LAST, true>::configure();
+  } else if (op == TcOp::Launch) {
+    if (a.save) TcBigLaunch<I, H, POOL, LAST, true>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax);
+    else TcBigLaunch<I, H, POOL, LAST, false>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, nullptr, nullptr);
+  }
   return true;
 }
 
@@ -174,8 +188,9 @@ void tc_pack_host(const float* W, const float* U, const float* bias, int in, int
 void tc_configure(int in, int hid, bool pool, bool last) { tc_dispatch(TcOp::Configure, in, hid, pool, last, TcArgs()); }
 
 void tc_launch(int in, int hid, bool pool, bool last, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
-               int sm_count, cudaStream_t st) {
+               int sm_count, cudaStream_t st, float* save, float* amax) {
   TcArgs a;
+  a.save = save; a.amax = amax;
   a.x = x; a.y = y; a.w = w; a.T = T; a.t_in = t_in; a.t_out = t_out; a.n_tiles = n_tiles; a.sm_count = sm_count; a.st = st;
   if (!tc_dispatch(TcOp::Launch, in, hid, pool, last, a)) throw std::invalid_argument("no tensor-core kernel for this layer shape");
 }

@@ -112,12 +112,47 @@ __device__ __forceinline__ float lstm_cell_tc(float ei, float ef, float eg, floa
   return fmaf(-e, r, r);
 }
 
-template <int I, int H, bool POOL>
+// Same update, also returning the gates i, f, g, o and the new cell state for the backward pass of
+// integrated gradients (layout of lstm_fwd.cuh's SAVE mode).  The gates come out of the two merged
+// reciprocals by multiplication, so the MUFU count stays at 5 ex2 + 2 rcp.
+__device__ __forceinline__ float lstm_cell_tc_save(float ei, float ef, float eg, float eo, float& c, float (&sv)[5]) {
+  constexpr float kCap = 36.f;
+  const float a = ex2_approx(fminf(ei, kCap));
+  const float f = ex2_approx(fminf(ef, kCap));
+  const float g = ex2_approx(fminf(eg, kCap));
+  const float o = ex2_approx(fminf(eo, kCap));
+  const float g1 = 1.f + g, a1 = 1.f + a, pf = 1.f + f;
+  const float pa = a1 * g1;
+  const float tg = fmaf(-g, pf, pf);         // (1-g)(1+f)
+  const float r1 = rcp_approx(pf * pa);
+  const float cn = fmaf(c, pa, tg) * r1;
+  c = cn;
+  sv[0] = r1 * pf * g1;                      // 1/(1+a)
+  sv[1] = r1 * pa;                           // 1/(1+f)
+  sv[2] = r1 * tg * a1;                      // (1-g)/(1+g)
+  const float e = ex2_approx(fminf(cn * tc_gate_scale(2), kCap));
+  const float e1 = 1.f + e;
+  const float r2 = rcp_approx(fmaf(o, e1, e1));   // 1 / [(1+o)(1+e)]
+  sv[3] = r2 * e1;                           // 1/(1+o)
+  sv[4] = cn;
+  return fmaf(-e, r2, r2);
+}
+
+// Which of the three pooled steps held the maximum (first one on ties, as lstm_fwd.cuh), two bits per unit.
+__device__ __forceinline__ void pool_arg_update(unsigned long long& bits, int unit, int ph, bool greater) {
+  const unsigned long long m = 3ull << (2 * unit);
+  if (ph == 0) bits &= ~m;
+  else if (greater) bits = (bits & ~m) | (static_cast<unsigned long long>(ph) << (2 * unit));
+}
+
+template <int I, int H, bool POOL, bool SAVE = false>
 __global__ void __launch_bounds__((TcCfg<I, H>::NT), 1)
 lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_stride][I][64]
                float* __restrict__ yout,                 // [n_tiles][t_out_stride][H][64]
                const unsigned char* __restrict__ wpk,    // B_hi | B_lo | bias (TcCfg::PACKED_BYTES)
-               int T, int t_in_stride, int t_out_stride, int n_tiles) {
+               int T, int t_in_stride, int t_out_stride, int n_tiles,
+               float* __restrict__ save = nullptr,       // SAVE: [n_tiles][T][5][H][64] gates i, f, g, o and c
+               float* __restrict__ amax = nullptr) {     // SAVE && POOL: [n_tiles][t_out_stride][H][64] argmax step
   using C = TcCfg<I, H>;
   extern __shared__ __align__(128) unsigned char sm[];
   float* bias = reinterpret_cast<float*>(sm + C::OFF_BIAS);
@@ -185,6 +220,7 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
   const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
   float cst[H];
   float pmax[POOL ? H : 1];
+  unsigned long long parg = 0ull;
   int rho = 0, t = 0;
   for (long long q = 0; q < total; ++q) {
     const long long tile = tile0 + static_cast<long long>(2 * g + half) * R + rho;
@@ -248,17 +284,35 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
         umma::tmem_ld8x4(col0, col0 + H, col0 + 2 * H, col0 + 3 * H, zi, zf, zg, zo);
         const int j0 = b8 * 8;
 #pragma unroll
-        for (int i = 0; i < 8; ++i)
-          hv[i] = lstm_cell_tc(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
-                                  zo[i] + bias[3 * H + j0 + i], cst[j0 + i]);
+        for (int i = 0; i < 8; ++i) {
+          if (SAVE) {
+            float sv[5];
+            hv[i] = lstm_cell_tc_save(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
+                                      zo[i] + bias[3 * H + j0 + i], cst[j0 + i], sv);
+            float* so = save + (((tile * T + t) * 5) * H + j0 + i) * kTile + b;
+#pragma unroll
+            for (int v = 0; v < 5; ++v) so[v * H * kTile] = sv[v];
+          } else {
+            hv[i] = lstm_cell_tc(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
+                                 zo[i] + bias[3 * H + j0 + i], cst[j0 + i]);
+          }
+        }
         if (POOL) {
           const int ph = t % 3;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) pmax[j0 + i] = (ph == 0) ? hv[i] : fmaxf(pmax[j0 + i], hv[i]);
+          for (int i = 0; i < 8; ++i) {
+            if (SAVE) pool_arg_update(parg, j0 + i, ph, hv[i] > pmax[j0 + i]);
+            pmax[j0 + i] = (ph == 0) ? hv[i] : fmaxf(pmax[j0 + i], hv[i]);
+          }
           if (ph == 2) {
             float* yo = yout + ((tile * t_out_stride + t / 3) * H + j0) * kTile + b;
 #pragma unroll
             for (int i = 0; i < 8; ++i) yo[i * kTile] = pmax[j0 + i];
+            if (SAVE) {
+              float* ao = amax + ((tile * t_out_stride + t / 3) * H + j0) * kTile + b;
+#pragma unroll
+              for (int i = 0; i < 8; ++i) ao[i * kTile] = static_cast<float>((parg >> (2 * (j0 + i))) & 3ull);
+            }
           }
         } else {
           float* yo = yout + ((tile * t_out_stride + t) * H + j0) * kTile + b;

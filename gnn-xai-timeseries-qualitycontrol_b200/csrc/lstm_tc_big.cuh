@@ -51,12 +51,14 @@ struct TcBigCfg {
   static_assert(SMEM_BYTES <= 227 * 1024, "operands do not fit in shared memory");
 };
 
-template <int I, int H, bool POOL, bool LAST, bool STREAM>
+template <int I, int H, bool POOL, bool LAST, bool STREAM, bool SAVE = false>
 __global__ void __launch_bounds__((TcBigCfg<I, H, STREAM>::NT), 1)
 lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_stride][I][64]
                    float* __restrict__ yout,                 // [n_tiles][t_out_stride][H][64], LAST: [n_tiles][H][64]
                    const unsigned char* __restrict__ wpk,    // pieces [chunk][K slice]{hi, lo} | bias
-                   int T, int t_in_stride, int t_out_stride, int n_tiles) {
+                   int T, int t_in_stride, int t_out_stride, int n_tiles,
+                   float* __restrict__ save = nullptr,       // SAVE: [n_tiles][T][5][H][64] gates i, f, g, o and c
+                   float* __restrict__ amax = nullptr) {     // SAVE && POOL: [n_tiles][t_out_stride][H][64] argmax step
   using C = TcBigCfg<I, H, STREAM>;
   extern __shared__ __align__(128) unsigned char sm[];
   uint4* Ahi = reinterpret_cast<uint4*>(sm + C::OFF_AHI);   // 16-byte chunk index: kb * ROWS + row
@@ -175,6 +177,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
     const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
     float cst[C::CPG * C::UB];
     float pmax[POOL ? C::CPG * C::UB : 1];
+    unsigned long long parg = 0ull;
     uint4 hold_hi[C::CPG][C::UB / 8], hold_lo[C::CPG][C::UB / 8];
 
     // this thread's share of x_q (fp32, TMA slot) -> bf16 hi/lo chunks of the A operand
@@ -226,17 +229,37 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
           const int j0 = c * C::UB + b8 * 8;       // first unit of this block
           const int l0 = ci * C::UB + b8 * 8;      // its slot in cst / pmax
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            hv[i] = lstm_cell_tc(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
-                                    zo[i] + bias[3 * H + j0 + i], cst[l0 + i]);
+          for (int i = 0; i < 8; ++i) {
+            if (SAVE) {
+              float sv[5];
+              hv[i] = lstm_cell_tc_save(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
+                                        zo[i] + bias[3 * H + j0 + i], cst[l0 + i], sv);
+              if (valid) {
+                float* so = save + (((tile * T + t) * 5) * H + j0 + i) * kTile + b;
+#pragma unroll
+                for (int v = 0; v < 5; ++v) so[v * H * kTile] = sv[v];
+              }
+            } else {
+              hv[i] = lstm_cell_tc(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
+                                   zo[i] + bias[3 * H + j0 + i], cst[l0 + i]);
+            }
+          }
           if (POOL) {
             const int ph = t % 3;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) pmax[l0 + i] = (ph == 0) ? hv[i] : fmaxf(pmax[l0 + i], hv[i]);
+            for (int i = 0; i < 8; ++i) {
+              if (SAVE) pool_arg_update(parg, l0 + i, ph, hv[i] > pmax[l0 + i]);
+              pmax[l0 + i] = (ph == 0) ? hv[i] : fmaxf(pmax[l0 + i], hv[i]);
+            }
             if (ph == 2 && valid) {
               float* yo = yout + ((tile * t_out_stride + t / 3) * H + j0) * kTile + b;
 #pragma unroll
               for (int i = 0; i < 8; ++i) yo[i * kTile] = pmax[l0 + i];
+              if (SAVE) {
+                float* ao = amax + ((tile * t_out_stride + t / 3) * H + j0) * kTile + b;
+#pragma unroll
+                for (int i = 0; i < 8; ++i) ao[i * kTile] = static_cast<float>((parg >> (2 * (l0 + i))) & 3ull);
+              }
             }
           } else if (LAST) {
             if (last_step && valid) {
