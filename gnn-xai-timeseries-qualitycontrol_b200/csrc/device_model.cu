@@ -72,6 +72,7 @@ DeviceModel::~DeviceModel() {
     cudaFree(d_packed);
     cudaFree(d_packed_t);
     cudaFree(d_packed_tc);
+    cudaFree(d_packed_tcb);
     cudaFree(d_scratch);
   }
 }
@@ -140,6 +141,17 @@ void DeviceModel::upload() {
                  s.lstm_in[l], s.lstm_hid[l], packed_tc.data() + packed_tc_off[l]);
   if (!d_packed_tc) GNNQC_CUDA(cudaMalloc(&d_packed_tc, total_tc));
   GNNQC_CUDA(cudaMemcpy(d_packed_tc, packed_tc.data(), total_tc, cudaMemcpyHostToDevice));
+  size_t total_tcb = 0;
+  for (int l = 0; l < s.n_lstm; ++l) {
+    packed_tcb_off[l] = total_tcb;
+    total_tcb += (tc_bwd_packed_bytes(s.lstm_in[l], s.lstm_hid[l]) + 255) / 256 * 256;
+  }
+  std::vector<unsigned char> packed_tcb(total_tcb, 0);
+  for (int l = 0; l < s.n_lstm; ++l)
+    tc_bwd_pack_host(host.params.data() + s.off_lstm_w[l], host.params.data() + s.off_lstm_u[l], s.lstm_in[l], s.lstm_hid[l],
+                     packed_tcb.data() + packed_tcb_off[l]);
+  if (!d_packed_tcb) GNNQC_CUDA(cudaMalloc(&d_packed_tcb, total_tcb));
+  GNNQC_CUDA(cudaMemcpy(d_packed_tcb, packed_tcb.data(), total_tcb, cudaMemcpyHostToDevice));
   tc_stale = false;
 }
 

@@ -50,6 +50,13 @@ void tc_pack_host(const float* W, const float* U, const float* bias, int in, int
 void tc_configure(int in, int hid, bool pool, bool last);
 void tc_launch(int in, int hid, bool pool, bool last, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
                int sm_count, cudaStream_t st, float* save = nullptr, float* amax = nullptr);   // save != nullptr: also store gates (IG forward)
+// Tensor-core LSTM backward (csrc/lstm_tc_bwd.cu).
+bool tc_bwd_supported(int in, int hid, bool pool, bool last);
+size_t tc_bwd_packed_bytes(int in, int hid);
+void tc_bwd_pack_host(const float* W, const float* U, int in, int hid, unsigned char* out);
+void tc_bwd_configure(int in, int hid, bool pool, bool last);
+void tc_bwd_launch(int in, int hid, bool pool, bool last, const float* dy, const float* save, const float* amax, const unsigned char* w,
+                   float* dx, int T, long long n_tiles, int sm_count, cudaStream_t st);
 // optimizer slots and per-step BN state (csrc/train.cu)
 
 struct DeviceModel {
@@ -63,6 +70,8 @@ struct DeviceModel {
   size_t packed_t_off[kMaxLstmLayers] = {0};
   unsigned char* d_packed_tc = nullptr;   // bf16 hi/lo operand tiles for the tensor-core layers
   size_t packed_tc_off[kMaxLstmLayers] = {0};
+  unsigned char* d_packed_tcb = nullptr;  // [W | U]^T operand pieces for the tensor-core backward
+  size_t packed_tcb_off[kMaxLstmLayers] = {0};
   bool tc_stale = false;                   // set by train_apply; refreshed lazily before scoring
   void refresh_tc();
   void* d_scratch = nullptr;

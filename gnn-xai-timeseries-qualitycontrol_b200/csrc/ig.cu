@@ -79,7 +79,7 @@ struct LayerArgs {
   const float* in = nullptr;   // forward: x tile; backward: dy
   float* out = nullptr;        // forward: y tile; backward: dx
   const float* w = nullptr;    // forward: packed; backward: transposed
-  const unsigned char* wtc = nullptr;   // forward: tensor-core operand tiles (null: fp32 kernel)
+  const unsigned char* wtc = nullptr;   // tensor-core operand tiles of this direction (null: fp32 kernel)
   float* save = nullptr;
   float* amax = nullptr;
   int T = 0, t_in = 0, t_out = 0;
@@ -93,11 +93,14 @@ void layer_op(Op op, const LayerArgs& a) {
   if (op == Op::Configure) {
     FwdSave<I, H, POOL, LAST>::configure();
     Bwd<I, H, POOL, LAST>::configure();
+    if (tc_bwd_supported(I, H, POOL, LAST)) tc_bwd_configure(I, H, POOL, LAST);
   } else if (op == Op::Forward) {
     if (a.wtc && tc_layer_supported(I, H, POOL, LAST))   // gate contraction on the tensor cores (lstm_tc.cuh, SAVE mode)
       return tc_launch(I, H, POOL, LAST, a.in, a.out, a.wtc, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax);
     FwdSave<I, H, POOL, LAST>::launch(a.in, a.out, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.save, a.amax, a.st);
   } else {
+    if (a.wtc && tc_bwd_supported(I, H, POOL, LAST))   // contraction on the tensor cores (lstm_tc_bwd.cuh)
+      return tc_bwd_launch(I, H, POOL, LAST, a.in, a.save, a.amax, a.wtc, a.out, a.T, a.n_tiles, a.sm_count, a.st);
     Bwd<I, H, POOL, LAST>::launch(a.in, a.save, a.amax, a.w, a.out, a.T, a.n_tiles, a.sm_count, a.st);
   }
 }
@@ -153,6 +156,7 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
   refresh_tc();
   // GNNQC_IG_TC=0: forward passes on the fp32 CUDA-core kernels (A/B)
   static const bool ig_tc = [] { const char* e = std::getenv("GNNQC_IG_TC"); return !(e && std::strcmp(e, "0") == 0); }();
+  static const bool ig_tc_bwd = [] { const char* e = std::getenv("GNNQC_IG_TC_BWD"); return ig_tc && !(e && std::strcmp(e, "0") == 0); }();
   StackPlan plan(s, T);
   const int L = s.n_lstm;
   const long long n_tiles = (B + kTile - 1) / kTile;
@@ -236,6 +240,7 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
         const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
         LayerArgs a;
         a.in = dy; a.out = (l % 2 == 0) ? g0 : g1; a.w = d_packed_t + packed_t_off[l];
+        a.wtc = ig_tc_bwd ? d_packed_tcb + packed_tcb_off[l] : nullptr;
         a.save = reinterpret_cast<float*>(saves + size_t(chunk) * save_off[l]);
         a.amax = pool ? reinterpret_cast<float*>(saves + size_t(chunk) * amax_off[l]) : nullptr;
         a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;

@@ -1,0 +1,113 @@
+// Host side of the tensor-core LSTM backward kernels (lstm_tc_bwd.cuh): [W | U]^T operand packing
+// (bf16 hi/lo split, UMMA K-major layout, one piece per chunk of 8 units), configuration and launch.
+#include <cuda_bf16.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "device_model.cuh"
+#include "lstm_tc_bwd.cuh"
+
+namespace gnnqc {
+namespace {
+
+template <int I, int H, bool POOL, bool LAST, int GRP, int SPLIT>
+struct TcBwdLaunch {
+  static constexpr bool STREAM = (H > 64);
+  using Cfg = TcBwdCfg<I, H, GRP, SPLIT, STREAM>;
+  static auto kernel() { return lstm_tc_bwd_kernel<I, H, POOL, LAST, GRP, SPLIT, STREAM>; }
+  static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
+  static void launch(const float* dy, const float* save, const float* amax, const unsigned char* wpk, float* dx, int T, long long n_tiles,
+                     int sm_count, cudaStream_t st) {
+    const long long n_pairs = (n_tiles + 1) / 2;
+    const long long grid = std::min<long long>((n_pairs + GRP - 1) / GRP, sm_count);
+    if (std::getenv("GNNQC_DEBUG")) {
+      cudaFuncAttributes fa;
+      GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
+      std::fprintf(stderr, "[gnnqc] tc-bwd I=%d H=%d regs=%d local=%zu smem=%zu threads=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::NT);
+    }
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wpk, dx, T, static_cast<int>(n_tiles));
+    GNNQC_CUDA(cudaGetLastError());
+  }
+};
+
+enum class BwdOp { Query, Configure, Launch };
+
+struct BwdArgs {
+  const float* dy = nullptr;
+  const float* save = nullptr;
+  const float* amax = nullptr;
+  const unsigned char* w = nullptr;
+  float* dx = nullptr;
+  int T = 0, sm_count = 0;
+  long long n_tiles = 0;
+  cudaStream_t st = nullptr;
+};
+
+template <int I, int H, bool POOL, bool LAST, int GRP, int SPLIT>
+bool bwd_case(BwdOp op, const BwdArgs& a) {
+  using L = TcBwdLaunch<I, H, POOL, LAST, GRP, SPLIT>;
+  if (op == BwdOp::Configure) L::configure();
+  else if (op == BwdOp::Launch) L::launch(a.dy, a.save, a.amax, a.w, a.dx, a.T, a.n_tiles, a.sm_count, a.st);
+  return true;
+}
+
+bool bwd_dispatch(BwdOp op, int in, int hid, bool pool, bool last, const BwdArgs& a) {
+  if (in == 18 && hid == 16 && !pool && !last) return bwd_case<18, 16, false, false, 4, 1>(op, a);
+  if (in == 16 && hid == 16 && pool && !last) return bwd_case<16, 16, true, false, 4, 1>(op, a);
+  if (in == 16 && hid == 32 && !pool && !last) return bwd_case<16, 32, false, false, 4, 1>(op, a);
+  if (in == 32 && hid == 32 && pool && !last) return bwd_case<32, 32, true, false, 4, 1>(op, a);
+  if (in == 32 && hid == 64 && !pool && !last) return bwd_case<32, 64, false, false, 2, 1>(op, a);
+  if (in == 64 && hid == 64 && pool && !last) return bwd_case<64, 64, true, false, 2, 1>(op, a);
+  if (in == 64 && hid == 128 && !pool && last) return bwd_case<64, 128, false, true, 1, 2>(op, a);
+  return false;
+}
+
+}  // namespace
+
+bool tc_bwd_supported(int in, int hid, bool pool, bool last) {
+  static const bool off = [] { const char* e = std::getenv("GNNQC_TC"); return e && std::strcmp(e, "0") == 0; }();
+  return !off && bwd_dispatch(BwdOp::Query, in, hid, pool, last, BwdArgs());
+}
+
+size_t tc_bwd_packed_bytes(int in, int hid) {
+  const int n = (in + 15) / 16 * 16 + hid;
+  return size_t(hid / 8) * 128 * n;
+}
+
+// Piece of chunk c: [slice s = 0, 1][hi | lo][kb = 0, 1][n < N][8] bf16 with
+//   k = c*32 + (2 s + kb) * 8 + u  <->  Keras column (2 s + kb) * H + 8 c + u   (gate-major inside a chunk)
+//   n < I: kernel row n;  IP <= n < IP + H: recurrent row n - IP;  zero otherwise.
+void tc_bwd_pack_host(const float* W, const float* U, int in, int hid, unsigned char* out) {
+  const int ip = (in + 15) / 16 * 16, n_out = ip + hid, n4 = 4 * hid;
+  for (int c = 0; c < hid / 8; ++c) {
+    unsigned char* piece = out + size_t(c) * 128 * n_out;
+    for (int s = 0; s < 2; ++s)
+      for (int kb = 0; kb < 2; ++kb)
+        for (int n = 0; n < n_out; ++n)
+          for (int u = 0; u < 8; ++u) {
+            const int col = (2 * s + kb) * hid + 8 * c + u;
+            float v = 0.f;
+            if (n < in) v = W[size_t(n) * n4 + col];
+            else if (n >= ip) v = U[size_t(n - ip) * n4 + col];
+            const __nv_bfloat16 h = __float2bfloat16_rn(v);
+            const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
+            const size_t at = (size_t(kb) * n_out + n) * 8 + u;
+            reinterpret_cast<__nv_bfloat16*>(piece + size_t(s * 2 + 0) * 2 * n_out * 16)[at] = h;
+            reinterpret_cast<__nv_bfloat16*>(piece + size_t(s * 2 + 1) * 2 * n_out * 16)[at] = l;
+          }
+  }
+}
+
+void tc_bwd_configure(int in, int hid, bool pool, bool last) { bwd_dispatch(BwdOp::Configure, in, hid, pool, last, BwdArgs()); }
+
+void tc_bwd_launch(int in, int hid, bool pool, bool last, const float* dy, const float* save, const float* amax, const unsigned char* w,
+                   float* dx, int T, long long n_tiles, int sm_count, cudaStream_t st) {
+  BwdArgs a;
+  a.dy = dy; a.save = save; a.amax = amax; a.w = w; a.dx = dx; a.T = T; a.n_tiles = n_tiles; a.sm_count = sm_count; a.st = st;
+  if (!bwd_dispatch(BwdOp::Launch, in, hid, pool, last, a)) throw std::invalid_argument("no tensor-core backward kernel for this layer shape");
+}
+
+}  // namespace gnnqc
