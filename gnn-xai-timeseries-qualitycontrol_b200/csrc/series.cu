@@ -144,6 +144,12 @@ __global__ void __launch_bounds__(256) series_frontend_kernel(const gnnqc_series
                                                               const float2* __restrict__ w_med, const int* __restrict__ w_count,
                                                               const int* __restrict__ w_tgt_slot, const GcnFolded p, float* __restrict__ out,
                                                               long long n_windows, int t_run) {
+  // The window's node list (sensor row, coefficient, rolling median) is the same for all its steps:
+  // staged once per CTA, one padded row per window so lanes hit distinct banks.
+  constexpr int STR = kMaxNbr + 1;
+  __shared__ int sens_s[kTile * STR];
+  __shared__ float coef_s[kTile * STR];
+  __shared__ float2 med_s[kTile * STR];
   const int b = threadIdx.x & 63, tq = threadIdx.x >> 6;
   const long long tile = blockIdx.x;
   const long long win = tile * kTile + b;
@@ -151,9 +157,12 @@ __global__ void __launch_bounds__(256) series_frontend_kernel(const gnnqc_series
   const bool live = win < n_windows && w_count[win] > 0;
   const int nn = live ? w_count[win] : 0;
   const long long base_t = live ? static_cast<long long>(t_anom[win]) - before : 0;
-  const int* sensors = w_sensor + win * kMaxNbr;
-  const float* coef = w_coef + win * kMaxNbr;
-  const float2* med = w_med + win * kMaxNbr;
+  for (int n = tq; n < nn; n += 4) {
+    sens_s[b * STR + n] = __ldg(w_sensor + win * kMaxNbr + n);
+    coef_s[b * STR + n] = __ldg(w_coef + win * kMaxNbr + n);
+    med_s[b * STR + n] = __ldg(w_med + win * kMaxNbr + n);
+  }
+  __syncthreads();
   const int tslot = live ? w_tgt_slot[win] : 0;
   constexpr int CH = 2 + kGcnChannelsDev;
 #pragma unroll 1
@@ -162,12 +171,13 @@ __global__ void __launch_bounds__(256) series_frontend_kernel(const gnnqc_series
     if (t >= t_run) break;
     PoolAcc acc;
     float2 tv = make_float2(0.f, 0.f);
+#pragma unroll 2
     for (int n = 0; n < nn; ++n) {
-      const float2 raw = __ldg(sr.raw + static_cast<long long>(__ldg(sensors + n)) * sr.Tt + base_t + t);
-      const float2 m = __ldg(med + n);
+      const float2 raw = __ldg(sr.raw + static_cast<long long>(sens_s[b * STR + n]) * sr.Tt + base_t + t);
+      const float2 m = med_s[b * STR + n];
       const float2 v = make_float2(raw.x - m.x, raw.y - m.y);
       if (n == tslot) tv = v;
-      acc.add(p, v, __ldg(coef + n));
+      acc.add_packed(p, v, coef_s[b * STR + n]);
     }
     float* o = out + ((tile * t_run + t) * CH) * kTile + b;
     o[0] = tv.x;
