@@ -297,7 +297,7 @@ void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, l
   }
   const float* p = d_params;
   mark_begin("head", st);
-  head_kernel<128, 64><<<static_cast<unsigned>(n_tiles), 256, 0, st>>>(in, p + s.off_d1_w, p + s.off_d1_b, p + s.off_d2_w,
+  head_kernel<128, 64><<<static_cast<unsigned>(n_tiles), 128, 0, st>>>(in, p + s.off_d1_w, p + s.off_d1_b, p + s.off_d2_w,
                                                                        p + s.off_d2_b, p + s.off_out_w, p + s.off_out_b,
                                                                        s.leaky_alpha, scores, n_seq);
   GNNQC_CUDA(cudaGetLastError());

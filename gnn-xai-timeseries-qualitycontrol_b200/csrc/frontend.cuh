@@ -352,41 +352,52 @@ inline void launch_cml_frontend(const float2* feat, long long feat_rows, const f
 // ---- dense head: [tile][128][64] -> sigmoid(Dense(LeakyReLU(Dense(LeakyReLU(Dense))))) ------
 // libs/create_model.py:235-239 (GCN) and :372-376 (baseline).  One CTA per tile.
 template <int HL, int D>
-__global__ void __launch_bounds__(256) head_kernel(const float* __restrict__ y7, const float* __restrict__ w1,
+__global__ void __launch_bounds__(128) head_kernel(const float* __restrict__ y7, const float* __restrict__ w1,
                                                    const float* __restrict__ b1, const float* __restrict__ w2,
                                                    const float* __restrict__ b2, const float* __restrict__ wo,
                                                    const float* __restrict__ bo, float leaky, float* __restrict__ scores,
                                                    long long n_seq) {
+  // Register tile: thread = 8 outputs x 4 windows (l, l+16, l+32, l+48), so one pair of 16-byte weight
+  // loads feeds 32 FMAs; 128 threads cover the 64 outputs x 64 windows of a tile.
+  static_assert(D == 64, "tile mapping assumes 64 dense units");
   __shared__ float d1_s[D * kTile];
   __shared__ float d2_s[D * kTile];
   const long long tile = blockIdx.x;
-  const int b = threadIdx.x & 63, q = threadIdx.x >> 6;  // q: which quarter of the D outputs
-  constexpr int DQ = D / 4;
-  float acc[DQ];
+  const int l = threadIdx.x & 15, q = threadIdx.x >> 4;
+  float acc[8][4];
+  auto dense = [&](const float* __restrict__ w, const float* __restrict__ bias, int K, auto load_in, float* __restrict__ dst) {
 #pragma unroll
-  for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b1 + q * DQ + o);
-#pragma unroll 8
-  for (int k = 0; k < HL; ++k) {
-    const float h = __ldg(y7 + (tile * HL + k) * kTile + b);
+    for (int o = 0; o < 8; ++o) {
+      const float bv = __ldg(bias + q * 8 + o);
 #pragma unroll
-    for (int o = 0; o < DQ; ++o) acc[o] = fmaf(h, __ldg(w1 + k * D + q * DQ + o), acc[o]);
-  }
+      for (int j = 0; j < 4; ++j) acc[o][j] = bv;
+    }
+#pragma unroll 4
+    for (int k = 0; k < K; ++k) {
+      const float4 wa = __ldg(reinterpret_cast<const float4*>(w + k * D + q * 8));
+      const float4 wb = __ldg(reinterpret_cast<const float4*>(w + k * D + q * 8 + 4));
+      const float wv[8] = {wa.x, wa.y, wa.z, wa.w, wb.x, wb.y, wb.z, wb.w};
+      float h[4];
 #pragma unroll
-  for (int o = 0; o < DQ; ++o) d1_s[(q * DQ + o) * kTile + b] = acc[o] > 0.f ? acc[o] : leaky * acc[o];
+      for (int j = 0; j < 4; ++j) h[j] = load_in(k, l + 16 * j);
+#pragma unroll
+      for (int o = 0; o < 8; ++o)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[o][j] = fmaf(h[j], wv[o], acc[o][j]);
+    }
+#pragma unroll
+    for (int o = 0; o < 8; ++o)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) dst[(q * 8 + o) * kTile + l + 16 * j] = acc[o][j] > 0.f ? acc[o][j] : leaky * acc[o][j];
+  };
+  dense(w1, b1, HL, [&](int k, int b) { return __ldg(y7 + (tile * HL + k) * kTile + b); }, d1_s);
   __syncthreads();
-#pragma unroll
-  for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b2 + q * DQ + o);
-#pragma unroll 8
-  for (int k = 0; k < D; ++k) {
-    const float h = d1_s[k * kTile + b];
-#pragma unroll
-    for (int o = 0; o < DQ; ++o) acc[o] = fmaf(h, __ldg(w2 + k * D + q * DQ + o), acc[o]);
-  }
-#pragma unroll
-  for (int o = 0; o < DQ; ++o) d2_s[(q * DQ + o) * kTile + b] = acc[o] > 0.f ? acc[o] : leaky * acc[o];
+  dense(w2, b2, D, [&](int k, int b) { return d1_s[k * kTile + b]; }, d2_s);
   __syncthreads();
-  if (q == 0) {
+  if (threadIdx.x < kTile) {
+    const int b = threadIdx.x;
     float z = __ldg(bo);
+#pragma unroll 8
     for (int k = 0; k < D; ++k) z = fmaf(d2_s[k * kTile + b], __ldg(wo + k), z);
     const long long seq = tile * kTile + b;
     if (seq < n_seq) scores[seq] = 1.f / (1.f + expf(-z));
