@@ -74,8 +74,13 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   constexpr int kMmaWarp = 4 * C::G, kLoadWarp = 4 * C::G + 1;
 
-  const int n_pairs = (n_tiles + 1) / 2;
-  const int my_pairs = (n_pairs - static_cast<int>(blockIdx.x) + static_cast<int>(gridDim.x) - 1) / static_cast<int>(gridDim.x);
+  // Tiles are dealt to CTAs in contiguous, equal ranges (6 or 7 of 1,024 tiles on 148 SMs) and taken two
+  // at a time; in a CTA's last round the second half may be empty, and its two warps then skip the
+  // cell work.
+  const int n_cta = static_cast<int>(gridDim.x), cta = static_cast<int>(blockIdx.x);
+  const int my_tiles = n_tiles / n_cta + (cta < n_tiles % n_cta ? 1 : 0);
+  const long long tile0 = static_cast<long long>(cta) * (n_tiles / n_cta) + (cta < n_tiles % n_cta ? cta : n_tiles % n_cta);
+  const int my_pairs = (my_tiles + 1) / 2;
   const long long total = static_cast<long long>(my_pairs) * T;
   if (total <= 0) return;
 
@@ -113,11 +118,11 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
     if (lane == 0) {
       auto issue_load = [&](long long q) {
         const int n = static_cast<int>(q / T), t = static_cast<int>(q % T);
-        const long long pair = static_cast<long long>(blockIdx.x) + static_cast<long long>(n) * gridDim.x;
-        const bool second = 2 * pair + 1 < n_tiles;
+        const long long tile_a = tile0 + 2 * n;
+        const bool second = 2 * n + 1 < my_tiles;
         ptx::mbar_arrive_expect_tx(x_full, second ? 2 * C::XBYTES : C::XBYTES);
-        ptx::bulk_load(xs, xin + ((2 * pair) * t_in_stride + t) * (I * kTile), C::XBYTES, x_full);
-        if (second) ptx::bulk_load(xs + I * kTile, xin + ((2 * pair + 1) * t_in_stride + t) * (I * kTile), C::XBYTES, x_full);
+        ptx::bulk_load(xs, xin + (tile_a * t_in_stride + t) * (I * kTile), C::XBYTES, x_full);
+        if (second) ptx::bulk_load(xs + I * kTile, xin + ((tile_a + 1) * t_in_stride + t) * (I * kTile), C::XBYTES, x_full);
       };
       issue_load(0);
       constexpr uint32_t idesc = umma::instr_desc_bf16(C::ROWS, C::NC);
@@ -179,6 +184,10 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
     float pmax[POOL ? C::CPG * C::UB : 1];
     unsigned long long parg = 0ull;
     uint4 hold_hi[C::CPG][C::UB / 8], hold_lo[C::CPG][C::UB / 8];
+#pragma unroll
+    for (int ci = 0; ci < C::CPG; ++ci)
+#pragma unroll
+      for (int b8 = 0; b8 < C::UB / 8; ++b8) hold_hi[ci][b8] = hold_lo[ci][b8] = make_uint4(0u, 0u, 0u, 0u);
 
     // this thread's share of x_q (fp32, TMA slot) -> bf16 hi/lo chunks of the A operand
     auto convert_x = [&](long long q) {
@@ -206,9 +215,8 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
     publish_a();
     int n = 0, t = 0;
     for (long long q = 0; q < total; ++q) {
-      const long long pair = static_cast<long long>(blockIdx.x) + static_cast<long long>(n) * gridDim.x;
-      const long long tile = 2 * pair + half;
-      const bool valid = tile < n_tiles;
+      const long long tile = tile0 + 2 * n + half;
+      const bool valid = 2 * n + half < my_tiles;     // uniform over the two warps of a half
       const uint32_t par = static_cast<uint32_t>(q & 1);
       if (t == 0) {
 #pragma unroll
@@ -221,6 +229,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
         ptx::mbar_wait(&d_full[c], par);
         umma::fence_after_sync();
         const uint32_t col0 = tbase + lane_base + static_cast<uint32_t>(c * C::NC);
+        if (!valid) continue;
 #pragma unroll
         for (int b8 = 0; b8 < C::UB / 8; ++b8) {
           float zi[8], zf[8], zg[8], zo[8], hv[8];
