@@ -325,9 +325,16 @@ def main():
     h2d = d2h = 0
     if wl == "cml_gcn":
         host = {k: batch[k].cpu().pin_memory() for k in keys}
-        scorer = CmlHostScorer(model, chunk_windows=8192)
-        e2e_step = lambda: scorer.score(host["features"], host["anom"], host["edges"], host["node_off"], host["edge_off"])  # noqa: E731
-        e2e_path = "CmlHostScorer (pinned host -> chunked H2D on a copy stream -> gnnqc_score_cml -> D2H)"
+        class _Native:   # the C-ABI call with host buffers; keeps the byte counts like the Python scorers do
+            last_h2d_bytes = last_d2h_bytes = 0
+
+            def score(self):
+                out, moved = model.score_cml_host(host["features"], host["anom"], host["edges"], host["node_off"], host["edge_off"], chunk_windows=8192)
+                self.last_h2d_bytes, self.last_d2h_bytes = moved, out.numel() * 4
+                return out
+        scorer = _Native()
+        e2e_step = scorer.score
+        e2e_path = "gnnqc_score_cml_host (pinned host -> chunked H2D of the live timesteps on a copy stream -> scoring kernels -> D2H)"
     elif wl == "cml_series":
         scorer = None
         slab_raw = np.ascontiguousarray(net["raw"][:, 2000 + 60: 2000 + 60 + per])

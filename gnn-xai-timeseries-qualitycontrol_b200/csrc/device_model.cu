@@ -66,6 +66,7 @@ DeviceModel::~DeviceModel() {
   if (device >= 0) {
     cudaSetDevice(device);
     free_train_state();
+    free_host_stage(host_stage);
     profile_reset();
     for (cudaEvent_t e : event_pool) cudaEventDestroy(e);
     cudaFree(d_params);

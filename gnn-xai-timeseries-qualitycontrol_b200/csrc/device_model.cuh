@@ -42,6 +42,8 @@ struct LaunchRecord {
 };
 
 struct TrainState;
+struct HostStage;   // staging slots and streams of gnnqc_score_cml_host (csrc/host_scoring.cu)
+void free_host_stage(HostStage* h);
 
 // Tensor-core LSTM layers (csrc/lstm_tc.cu).
 bool tc_layer_supported(int in, int hid, bool pool, bool last);
@@ -96,6 +98,7 @@ struct DeviceModel {
   void score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t stream);
   // Training (csrc/train.cu).  After train_apply the device copy of the parameters is the
   // authoritative one; sync_host_params() brings host.params up to date on demand.
+  HostStage* host_stage = nullptr;
   TrainState* train = nullptr;
   bool params_dirty = false;
   void configure_train_kernels();

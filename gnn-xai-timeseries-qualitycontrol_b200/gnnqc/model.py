@@ -169,6 +169,33 @@ class NativeModel:
                                   edge_off.data_ptr(), B, T, n_nodes_total, out.data_ptr(), self._stream()))
         return out
 
+    def score_cml_host(self, features, anom, edges, node_off, edge_off, chunk_windows=8192, out=None):
+        """gnnqc_score_cml_host: the same batch as score_cml but in HOST tensors (pin them for full PCIe
+        speed).  Returns (scores [B] pinned CPU float32, bytes copied host-to-device)."""
+        torch = _torch()
+        import ctypes as C
+
+        def host(t, dtype, name):
+            t = torch.as_tensor(t)
+            if t.is_cuda or t.dtype != dtype or not t.is_contiguous():
+                raise ValueError("%s must be a contiguous CPU %s tensor" % (name, dtype))
+            return t
+        features, anom = host(features, torch.float32, "features"), host(anom, torch.float32, "anom")
+        edges, node_off, edge_off = host(edges, torch.int64, "edges"), host(node_off, torch.int32, "node_off"), host(edge_off, torch.int64, "edge_off")
+        B, T = anom.shape[0], anom.shape[1]
+        if anom.dim() != 3 or anom.shape[2] != 2 or features.dim() != 2 or features.shape[1] != 2:
+            raise ValueError("expected features [Ntot,2] and anom [B,T,2]")
+        if node_off.numel() != B + 1 or edge_off.numel() != B + 1:
+            raise ValueError("node_off / edge_off must have B+1 entries")
+        if features.shape[0] != int(node_off[-1]) * T or edges.shape[0] != int(edge_off[-1]):
+            raise ValueError("features / edges do not match node_off / edge_off")
+        if out is None:
+            out = torch.empty(B, dtype=torch.float32).pin_memory()
+        moved = C.c_int64(0)
+        check(lib.gnnqc_score_cml_host(self._h, features.data_ptr(), anom.data_ptr(), edges.data_ptr(), node_off.data_ptr(), edge_off.data_ptr(),
+                                       B, T, int(chunk_windows), out.data_ptr(), C.addressof(moved)))
+        return out, int(moved.value)
+
     def score_soilnet(self, features, edges, node_off, edge_off, T, n_nodes_total=None):
         """SoilNet GCN: features cuda f32 [sum N_b*T, 3] -> scores cuda f32 [sum N_b]."""
         torch = _torch()

@@ -247,6 +247,19 @@ int gnnqc_train_apply(gnnqc_model* m, float* rvec_dev, const double* moments_dev
 int gnnqc_score_seq_noalloc(gnnqc_model* m, const float* x_dev, int64_t n_seq, int32_t T,
                             float* scores_dev, void* stream);
 
+/* The same call for windows that live in HOST memory - the shape model.predict has in the reference
+ * (numpy batches from prepare_batch_cml, libs/preprocessing_functions.py:638-666, scored at
+ * libs/test_model.py:29).  Arguments as gnnqc_score_cml but host pointers (pinned memory for full PCIe
+ * speed); the batch is cut into chunks of `chunk_windows` (0 = 8192) that are staged to the device on a
+ * copy stream while the previous chunk is scored, and scores_host [B] is complete when the call
+ * returns.  Timesteps that cannot reach the score (past 162 of 181 for the shipped models) are not
+ * transferred when the windows of a chunk have equal node counts.  h2d_bytes_out (optional): bytes copied
+ * host-to-device by this call. */
+int gnnqc_score_cml_host(gnnqc_model* m, const float* features_host, const float* anom_host,
+                         const int64_t* edges_host, const int32_t* node_off_host,
+                         const int64_t* edge_off_host, int64_t B, int32_t T, int64_t chunk_windows,
+                         float* scores_host, int64_t* h2d_bytes_out);
+
 /* Replaces GCNClassifier.call for ds_type 'soilnet' (libs/create_model.py:224-240), i.e.
  * model.predict on batches from prepare_batch_soilnet / wrapper_batch_mapping_soilnet
  * (libs/preprocessing_functions.py:861-897).

@@ -195,3 +195,23 @@ def test_roc_auc_matches_oracle_to_3_decimals(models):
     got = score_cml(models["model_cml"], batch)
     want = oracle_cml(models["model_cml"].named_params(), batch)
     assert round(roc_auc_score(labels, got), 3) == round(roc_auc_score(labels, want), 3)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ragged", [False, True])
+def test_host_entry_point_matches_device_call(ragged):
+    """gnnqc_score_cml_host (chunked staging, live timesteps only) == gnnqc_score_cml on the same batch, bit for bit."""
+    from gnnqc import NativeModel
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    batch = synth.make_cml_batch(700, seed=77, ragged=ragged, n_nodes=11)
+    dev = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+    want = m.score_cml(dev["features"], dev["anom"], dev["edges"], dev["node_off"], dev["edge_off"]).cpu()
+    host = {k: batch[k].contiguous().pin_memory() for k in ("features", "anom", "edges", "node_off", "edge_off")}
+    for chunk in (256, 8192):
+        got, moved = m.score_cml_host(host["features"], host["anom"], host["edges"], host["node_off"], host["edge_off"], chunk_windows=chunk)
+        assert torch.equal(got, want)
+        full = host["features"].numel() * 4 + host["anom"].numel() * 4
+        assert moved < full + host["edges"].numel() * 8 + 12 * 701 * 4
+        if not ragged:
+            assert moved < 0.93 * full + host["edges"].numel() * 8 + 12 * 701 * 4   # 162 of 181 steps cross PCIe
+    m.close()
