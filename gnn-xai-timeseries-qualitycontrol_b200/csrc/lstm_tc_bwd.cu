@@ -22,7 +22,7 @@ struct TcBwdLaunch {
   static void launch(const float* dy, const float* save, const float* amax, const unsigned char* wpk, float* dx, int T, long long n_tiles,
                      int sm_count, cudaStream_t st) {
     const long long n_pairs = (n_tiles + 1) / 2;
-    const long long grid = std::min<long long>((n_pairs + GRP - 1) / GRP, sm_count);
+    const long long grid = std::min<long long>(n_pairs, sm_count);
     if (std::getenv("GNNQC_DEBUG")) {
       cudaFuncAttributes fa;
       GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));

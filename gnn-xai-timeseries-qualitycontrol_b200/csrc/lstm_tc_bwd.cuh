@@ -100,7 +100,7 @@ lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this lay
   const int n_pairs = (n_tiles + 1) / 2;
   const int n_slots = static_cast<int>(gridDim.x) * GRP;
   auto slot_steps = [&](int g) -> long long {
-    const int slot = static_cast<int>(blockIdx.x) * GRP + g;
+    const int slot = g * static_cast<int>(gridDim.x) + static_cast<int>(blockIdx.x);   // group-major: every SM gets 3-4 of 512 pairs
     const int mine = slot < n_pairs ? (n_pairs - slot + n_slots - 1) / n_slots : 0;
     return static_cast<long long>(mine) * T;
   };
@@ -169,7 +169,7 @@ lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this lay
     uint64_t* d_full = a_ready + 2 * C::NBUF;
     const uint32_t tlane = tmem_slot + static_cast<uint32_t>(g * C::TMEM_GROUP) + (static_cast<uint32_t>((warp & 3) * 32) << 16);
     unsigned char* abase = sm + C::OFF_A + size_t(g) * C::NBUF * C::A_BUF;
-    const int slot = static_cast<int>(blockIdx.x) * GRP + g;
+    const int slot = g * static_cast<int>(gridDim.x) + static_cast<int>(blockIdx.x);
     const long long total = slot_steps(g);
     const int t_dy = POOL ? T / 3 : T;
     constexpr int NBLK = (I + 7) / 8;   // 8-column blocks of dx
