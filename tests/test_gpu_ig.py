@@ -100,3 +100,19 @@ def test_explainer_writes_the_six_files_per_sample(model, tmp_path):
         for k in range(n):                       # the reference's a[i::n_neighbors]
             np.testing.assert_array_equal(arr[k], rows[k::n])
     assert split_work(list(range(7)), 1, 3) == [1, 4]
+
+
+@pytest.mark.gpu
+def test_ig_large_batch_equals_its_chunks(model):
+    """602 tile pairs: more than the 592 group slots of the tensor-core backward kernels, so they run a
+    second round; attributions must not depend on the dealing (one call == 8,192-window calls)."""
+    from test_gpu_scoring import _slice_cml
+    T, B = 181, 77000
+    batch = synth.make_cml_batch(B, seed=6, n_nodes=4, device="cuda")
+    af, aa, p = model.ig_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"], m_steps=1)
+    for w0 in range(0, B, 8192):
+        w1 = min(B, w0 + 8192)
+        s = _slice_cml(batch, w0, w1, T)
+        bf, ba, bp = model.ig_cml(s["features"], s["anom"], s["edges"], s["node_off"], s["edge_off"], m_steps=1)
+        n0, n1 = int(batch["node_off"][w0]), int(batch["node_off"][w1])
+        assert torch.equal(bf, af[n0 * T:n1 * T]) and torch.equal(ba, aa[w0:w1]) and torch.equal(bp, p[w0:w1])

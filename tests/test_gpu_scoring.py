@@ -215,3 +215,28 @@ def test_host_entry_point_matches_device_call(ragged):
         if not ragged:
             assert moved < 0.93 * full + host["edges"].numel() * 8 + 12 * 701 * 4   # 162 of 181 steps cross PCIe
     m.close()
+
+
+def _slice_cml(batch, w0, w1, T):
+    """Windows [w0, w1) of an offsets-layout CML batch (device tensors), re-based to start at 0."""
+    no, eo = batch["node_off"], batch["edge_off"]
+    n0, n1, e0, e1 = int(no[w0]), int(no[w1]), int(eo[w0]), int(eo[w1])
+    return {"features": batch["features"][n0 * T:n1 * T], "anom": batch["anom"][w0:w1], "edges": batch["edges"][e0:e1],
+            "node_off": (no[w0:w1 + 1] - n0).to(torch.int32), "edge_off": eo[w0:w1 + 1] - e0}
+
+
+@pytest.mark.gpu
+def test_large_batch_equals_its_chunks():
+    """More than 8 tiles per SM: the persistent kernels run several rounds per CTA.  The score of a window
+    must not depend on how tiles are dealt, so one 80,037-window call == the same windows in 4,096-window calls."""
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    T = 181
+    batch = synth.make_cml_batch(80037, seed=5, n_nodes=5, device="cuda")
+    full = m.score_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"])
+    parts = []
+    for w0 in range(0, 80037, 4096):
+        s = _slice_cml(batch, w0, min(80037, w0 + 4096), T)
+        parts.append(m.score_cml(s["features"], s["anom"], s["edges"], s["node_off"], s["edge_off"]))
+    assert torch.equal(full, torch.cat(parts))
+    assert torch.isfinite(full).all()
+    m.close()
