@@ -196,7 +196,8 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   const size_t o_head = take(size_t(nt) * kHeadTrainFloats * 4);
   const size_t o_lossp = take(size_t(nt) * 4);
   const dim3 grid_fe(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
-  const size_t o_gcnp = take(size_t(grid_fe.x) * grid_fe.y * kGcnSums * 4);
+  const dim3 grid_feb(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + kFeBwdSteps - 1) / kFeBwdSteps));
+  const size_t o_gcnp = take(size_t(grid_feb.x) * grid_feb.y * kGcnSums * 4);
   const size_t o_part = take(kPartialBytes);
   char* base = static_cast<char*>(scratch(off));
   auto F = [base](size_t o) { return reinterpret_cast<float*>(base + o); };
@@ -306,12 +307,12 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   }
   if (gcn) {
     mark_begin("train_frontend_bwd", st);
-    cml_frontend_train_bwd_kernel<<<grid_fe, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), F(o_coef), node_off, prm + s.off_gcn_kernel,
+    cml_frontend_train_bwd_kernel<<<grid_feb, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), F(o_coef), node_off, prm + s.off_gcn_kernel,
                                                            prm + s.off_gcn_bias, ts->folded, ts->stats, s.bn_eps, dx1, F(o_gcnp), B, T,
                                                            plan.t_run[0]);
     GNNQC_CUDA(cudaGetLastError());
     mark_end(st);
-    sum_partials_kernel<<<1, 128, 0, st>>>(F(o_gcnp), static_cast<long long>(grid_fe.x) * grid_fe.y, kGcnSums, rvec + np);
+    sum_partials_kernel<<<1, 128, 0, st>>>(F(o_gcnp), static_cast<long long>(grid_feb.x) * grid_feb.y, kGcnSums, rvec + np);
     GNNQC_CUDA(cudaGetLastError());
   }
   sum_partials_kernel<<<1, 128, 0, st>>>(F(o_lossp), nt, 1, rvec + np + kGcnSums);

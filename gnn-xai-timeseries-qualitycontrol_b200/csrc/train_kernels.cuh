@@ -293,6 +293,7 @@ __global__ void __launch_bounds__(256) head_train_kernel(const float* __restrict
 //   sums[48..63] S_x1dy[c]      sums[64..79] d prelu alpha[c]
 // One partial row per CTA; summed afterwards in double in a fixed order.
 constexpr int kGcnSums = 5 * kGcnChannelsDev;
+constexpr int kFeBwdSteps = 8;   // timesteps per CTA: 4 thread rows x 2 steps (small batches need the CTAs)
 static __global__ void __launch_bounds__(256) cml_frontend_train_bwd_kernel(const float2* __restrict__ feat, const float* __restrict__ coef,
                                                                             const int* __restrict__ node_off, const float* __restrict__ w,
                                                                             const float* __restrict__ bias, const GcnFolded* __restrict__ pp,
@@ -300,10 +301,25 @@ static __global__ void __launch_bounds__(256) cml_frontend_train_bwd_kernel(cons
                                                                             const float* __restrict__ dx1, float* __restrict__ partial,
                                                                             long long n_windows, int T, int t_run) {
   __shared__ float red[kGcnSums][8];
+  // per-channel constants, staged once: y = x0*ya0 + x1*ya1 + yc (BN folded, pp), z_hat the same way with
+  // (w - mu) / sigma, and the PReLU slope
+  __shared__ float cst_s[7][kGcnChannelsDev];
+  if (threadIdx.x < kGcnChannelsDev) {
+    const int c = threadIdx.x;
+    const float rstd = rsqrtf(stats->var[c] + eps);
+    cst_s[0][c] = pp->a[0][c];
+    cst_s[1][c] = pp->a[1][c];
+    cst_s[2][c] = pp->c[c];
+    cst_s[3][c] = w[c] * rstd;
+    cst_s[4][c] = w[kGcnChannelsDev + c] * rstd;
+    cst_s[5][c] = (bias[c] - stats->mu[c]) * rstd;
+    cst_s[6][c] = pp->alpha[c];
+  }
+  __syncthreads();
   const int b = threadIdx.x & 63, tq = threadIdx.x >> 6;
   const long long tile = blockIdx.x;
   const long long win = tile * kTile + b;
-  const int t0 = blockIdx.y * 32 + tq * 8;
+  const int t0 = blockIdx.y * kFeBwdSteps + tq * (kFeBwdSteps / 4);
   constexpr int CH = 2 + kGcnChannelsDev;
   float s_dy[kGcnChannelsDev], s_dyz[kGcnChannelsDev], s_x0[kGcnChannelsDev], s_x1[kGcnChannelsDev], s_al[kGcnChannelsDev];
 #pragma unroll
@@ -311,21 +327,23 @@ static __global__ void __launch_bounds__(256) cml_frontend_train_bwd_kernel(cons
   if (win < n_windows) {
     const int n0 = node_off[win], nn = node_off[win + 1] - n0;
 #pragma unroll 1
-    for (int dt = 0; dt < 8; ++dt) {
+    for (int dt = 0; dt < kFeBwdSteps / 4; ++dt) {
       const int t = t0 + dt;
       if (t >= t_run) break;
       const float* g = dx1 + ((tile * t_run + t) * CH) * kTile + b;
+      float gv[kGcnChannelsDev];
+#pragma unroll
+      for (int c = 0; c < kGcnChannelsDev; ++c) gv[c] = __ldg(g + (2 + c) * kTile);
       const float2* row = feat + (static_cast<long long>(n0) * T + static_cast<long long>(t) * nn);
       for (int n = 0; n < nn; ++n) {
         const float2 v = __ldg(row + n);
         const float cf = __ldg(coef + n0 + n);
 #pragma unroll
         for (int c = 0; c < kGcnChannelsDev; ++c) {
-          const float zraw = fmaf(v.x, __ldg(w + c), fmaf(v.y, __ldg(w + kGcnChannelsDev + c), __ldg(bias + c)));
-          const float zh = (zraw - stats->mu[c]) * rsqrtf(stats->var[c] + eps);
-          const float y = fmaf(v.x, pp->a[0][c], fmaf(v.y, pp->a[1][c], pp->c[c]));
-          const float up = g[(2 + c) * kTile] * cf;
-          const float dy = up * (y > 0.f ? 1.f : pp->alpha[c]);
+          const float zh = fmaf(v.x, cst_s[3][c], fmaf(v.y, cst_s[4][c], cst_s[5][c]));
+          const float y = fmaf(v.x, cst_s[0][c], fmaf(v.y, cst_s[1][c], cst_s[2][c]));
+          const float up = gv[c] * cf;
+          const float dy = up * (y > 0.f ? 1.f : cst_s[6][c]);
           s_dy[c] += dy;
           s_dyz[c] = fmaf(dy, zh, s_dyz[c]);
           s_x0[c] = fmaf(dy, v.x, s_x0[c]);
