@@ -224,19 +224,26 @@ static __global__ void __launch_bounds__(256) cml_frontend_devparam_kernel(const
 constexpr int kFsWin = 16;                                  // windows per item
 constexpr int kFsSteps = 8;                                 // timesteps per item
 constexpr int kFsThreads = kFsWin * kFsSteps;
-constexpr int kFsCap = 32;                                  // nodes per window staged through smem
-constexpr int kFsSlot = kFsSteps * kFsCap * 8 + 16;         // bytes per window slot (16 * odd)
-constexpr int kFsSlab = kFsWin * kFsSlot;
-constexpr int kFsCoefStride = kFsCap + 1;                   // per-window coefficient row in smem (odd: no bank conflicts)
-constexpr size_t kFsSmem = 2 * size_t(kFsSlab) + 2 * kFsWin * sizeof(int) + 2 * 8 + 16 + kFsWin * kFsCoefStride * sizeof(float);
-constexpr int kFsCtasPerSm = 3;
+// CAP = nodes per window staged through smem (windows with more take direct loads).  Two builds: 24 nodes
+// (50 kB per CTA, four CTAs per SM) for batches that average at most 24 nodes per window, 32 otherwise
+// (three CTAs per SM).
+template <int CAP>
+struct FsCfg {
+  static constexpr int kSlot = kFsSteps * CAP * 8 + 16;     // bytes per window slot (16 * odd)
+  static constexpr int kSlab = kFsWin * kSlot;
+  static constexpr int kCoefStride = CAP + 1;               // per-window coefficient row in smem (odd: no bank conflicts)
+  static constexpr size_t kSmem = 2 * size_t(kSlab) + 2 * kFsWin * sizeof(int) + 2 * 8 + 16 + kFsWin * kCoefStride * sizeof(float);
+  static constexpr int kCtasPerSm = CAP <= 24 ? 4 : 3;
+};
 
+template <int CAP>
 static __global__ void __launch_bounds__(kFsThreads) cml_frontend_stream_kernel(const float2* __restrict__ feat, long long feat_rows,
                                                                                 const float2* __restrict__ anom, const float* __restrict__ coef,
                                                                                 const int* __restrict__ node_off, const GcnFolded p,
                                                                                 float* __restrict__ out, long long n_windows, int T, int t_run,
                                                                                 int n_tiles, float alpha) {
   extern __shared__ __align__(128) unsigned char fs_smem[];
+  constexpr int kFsCap = CAP, kFsSlot = FsCfg<CAP>::kSlot, kFsSlab = FsCfg<CAP>::kSlab, kFsCoefStride = FsCfg<CAP>::kCoefStride;
   int* lead_s = reinterpret_cast<int*>(fs_smem + 2 * kFsSlab);                         // [2][kFsWin]
   uint64_t* full = reinterpret_cast<uint64_t*>(fs_smem + 2 * kFsSlab + 2 * kFsWin * sizeof(int));   // [2]
   float* coef_s = reinterpret_cast<float*>(fs_smem + 2 * kFsSlab + 2 * kFsWin * sizeof(int) + 32);  // [kFsWin][kFsCoefStride]
@@ -338,15 +345,27 @@ static __global__ void __launch_bounds__(kFsThreads) cml_frontend_stream_kernel(
 
 // Launch helper: grid sized to the SM count, dynamic shared memory opted in by configure_cml_frontend().
 inline void configure_cml_frontend() {
-  cudaFuncSetAttribute(cml_frontend_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kFsSmem));
+  cudaFuncSetAttribute(cml_frontend_stream_kernel<24>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(FsCfg<24>::kSmem));
+  cudaFuncSetAttribute(cml_frontend_stream_kernel<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(FsCfg<32>::kSmem));
 }
+template <int CAP>
+inline void launch_cml_frontend_cap(const float2* feat, long long feat_rows, const float2* anom, const float* coef, const int* node_off,
+                                    const GcnFolded& p, float* out, long long n_windows, int T, int t_run, long long n_tiles, float alpha,
+                                    int sm_count, cudaStream_t st) {
+  const long long items = n_tiles * (kTile / kFsWin) * ((t_run + kFsSteps - 1) / kFsSteps);
+  const long long slots = static_cast<long long>(sm_count) * FsCfg<CAP>::kCtasPerSm;
+  const long long grid = items < slots ? items : slots;
+  cml_frontend_stream_kernel<CAP><<<static_cast<unsigned>(grid > 0 ? grid : 1), kFsThreads, FsCfg<CAP>::kSmem, st>>>(
+      feat, feat_rows, anom, coef, node_off, p, out, n_windows, T, t_run, static_cast<int>(n_tiles), alpha);
+}
+// feat_rows = T * (total nodes): the average node count per window picks the build.
 inline void launch_cml_frontend(const float2* feat, long long feat_rows, const float2* anom, const float* coef, const int* node_off,
                                 const GcnFolded& p, float* out, long long n_windows, int T, int t_run, long long n_tiles, float alpha,
                                 int sm_count, cudaStream_t st) {
-  const long long items = n_tiles * (kTile / kFsWin) * ((t_run + kFsSteps - 1) / kFsSteps);
-  const long long grid = items < static_cast<long long>(sm_count) * kFsCtasPerSm ? items : static_cast<long long>(sm_count) * kFsCtasPerSm;
-  cml_frontend_stream_kernel<<<static_cast<unsigned>(grid > 0 ? grid : 1), kFsThreads, kFsSmem, st>>>(feat, feat_rows, anom, coef, node_off, p, out,
-                                                                                                     n_windows, T, t_run, static_cast<int>(n_tiles), alpha);
+  if (feat_rows <= 24LL * T * n_windows)
+    launch_cml_frontend_cap<24>(feat, feat_rows, anom, coef, node_off, p, out, n_windows, T, t_run, n_tiles, alpha, sm_count, st);
+  else
+    launch_cml_frontend_cap<32>(feat, feat_rows, anom, coef, node_off, p, out, n_windows, T, t_run, n_tiles, alpha, sm_count, st);
 }
 
 // ---- dense head: [tile][128][64] -> sigmoid(Dense(LeakyReLU(Dense(LeakyReLU(Dense))))) ------
