@@ -307,7 +307,7 @@ void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, l
 
 static size_t scratch_budget_bytes() {
   const char* env = std::getenv("GNNQC_SCRATCH_MB");
-  size_t mb = env ? std::strtoull(env, nullptr, 10) : 2048;
+  size_t mb = env ? std::strtoull(env, nullptr, 10) : 8192;
   return std::max<size_t>(mb, 16) << 20;
 }
 
@@ -320,7 +320,7 @@ void DeviceModel::score_seq(const float* x, long long n_seq, int T, float* score
   StackPlan plan(s, T);
   const long long n_tiles = (n_seq + kTile - 1) / kTile;
   const size_t sa = align_up(plan.bytes_a, 256), sb = align_up(plan.bytes_b, 256);
-  const long long chunk = std::max<long long>(1, std::min<long long>(n_tiles, static_cast<long long>(scratch_budget_bytes() / (sa + sb))));
+  const long long chunk = balanced_chunk(n_tiles, static_cast<long long>(scratch_budget_bytes() / (sa + sb)));
   char* base = static_cast<char*>(scratch(size_t(chunk) * (sa + sb)));
   float* buf_a = reinterpret_cast<float*>(base);
   float* buf_b = reinterpret_cast<float*>(base + size_t(chunk) * sa);
@@ -366,7 +366,7 @@ void DeviceModel::score_cml(const float* feat, const float* anom, const long lon
   const long long n_tiles = (B + kTile - 1) / kTile;
   const size_t sa = align_up(plan.bytes_a, 256), sb = align_up(plan.bytes_b, 256);
   const size_t coef_bytes = align_up(size_t(n_nodes) * sizeof(float), 256);
-  const long long chunk = std::max<long long>(1, std::min<long long>(n_tiles, static_cast<long long>(scratch_budget_bytes() / (sa + sb))));
+  const long long chunk = balanced_chunk(n_tiles, static_cast<long long>(scratch_budget_bytes() / (sa + sb)));
   char* base = static_cast<char*>(scratch(2 * coef_bytes + size_t(chunk) * (sa + sb)));
   int* deg = reinterpret_cast<int*>(base);
   float* coef = reinterpret_cast<float*>(base + coef_bytes);

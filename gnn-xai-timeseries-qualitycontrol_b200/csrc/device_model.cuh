@@ -41,6 +41,15 @@ struct LaunchRecord {
   cudaEvent_t start, stop;
 };
 
+// Tiles per launch when a batch does not fit the scratch budget: as few chunks as needed, all the same size
+// (a short last chunk would leave most SMs idle for a full sequence length).
+inline long long balanced_chunk(long long n_tiles, long long max_tiles) {
+  if (max_tiles < 1) max_tiles = 1;
+  if (n_tiles <= max_tiles) return n_tiles < 1 ? 1 : n_tiles;
+  const long long parts = (n_tiles + max_tiles - 1) / max_tiles;
+  return (n_tiles + parts - 1) / parts;
+}
+
 struct TrainState;
 struct HostStage;   // staging slots and streams of gnnqc_score_cml_host (csrc/host_scoring.cu)
 void free_host_stage(HostStage* h);

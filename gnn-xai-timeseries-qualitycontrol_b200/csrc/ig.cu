@@ -176,7 +176,7 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
   const size_t s7 = size_t(s.lstm_hid[L - 1]) * kTile * sizeof(float);
   const size_t per_tile = sa + sb + 2 * sg + s7 + per_tile_save;
   const size_t coef_bytes = align_up(size_t(n_nodes) * sizeof(float), 256);
-  const long long chunk = std::max<long long>(1, std::min<long long>(n_tiles, static_cast<long long>(ig_scratch_budget_bytes() / per_tile)));
+  const long long chunk = balanced_chunk(n_tiles, static_cast<long long>(ig_scratch_budget_bytes() / per_tile));
   char* base = static_cast<char*>(scratch(2 * coef_bytes + size_t(chunk) * per_tile));
   int* deg = reinterpret_cast<int*>(base);
   float* coef = reinterpret_cast<float*>(base + coef_bytes);

@@ -324,8 +324,8 @@ int gnnqc_score_cml_series(gnnqc_model* m, const gnnqc_series* series, const int
     const size_t sa = align_up(plan.bytes_a, 256), sb = align_up(plan.bytes_b, 256);
     const size_t per_win = align_up(size_t(kMaxNbr) * (4 + 4 + 8) + 8, 16);
     const char* env = std::getenv("GNNQC_SCRATCH_MB");
-    const size_t budget = std::max<size_t>(env ? std::strtoull(env, nullptr, 10) : 2048, 16) << 20;
-    const long long chunk = std::max<long long>(1, std::min<long long>(n_tiles, static_cast<long long>(budget / (sa + sb))));
+    const size_t budget = std::max<size_t>(env ? std::strtoull(env, nullptr, 10) : 8192, 16) << 20;
+    const long long chunk = balanced_chunk(n_tiles, static_cast<long long>(budget / (sa + sb)));
     const size_t meta = align_up(size_t(B) * kMaxNbr * 4, 256) * 2 + align_up(size_t(B) * kMaxNbr * 8, 256) + 2 * align_up(size_t(B) * 4, 256);
     (void)per_win;
     char* base = static_cast<char*>(dm.scratch(meta + size_t(chunk) * (sa + sb)));

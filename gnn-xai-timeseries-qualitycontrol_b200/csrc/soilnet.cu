@@ -140,7 +140,7 @@ GcnFolded fold(const HostModel& m) {
 
 size_t budget_bytes() {
   const char* env = std::getenv("GNNQC_SCRATCH_MB");
-  size_t mb = env ? std::strtoull(env, nullptr, 10) : 2048;
+  size_t mb = env ? std::strtoull(env, nullptr, 10) : 8192;
   return std::max<size_t>(mb, 16) << 20;
 }
 
@@ -160,7 +160,7 @@ void DeviceModel::score_soilnet(const float* feat, const long long* edges, const
   scan_bytes = align_up(scan_bytes, 256);
   const size_t nbr_bytes = align_up(size_t(std::max<long long>(n_edges, 1)) * sizeof(int), 256);
   const size_t graph_bytes = 4 * nb + scan_bytes + nbr_bytes;
-  const long long chunk = std::max<long long>(1, std::min<long long>(n_tiles, static_cast<long long>(budget_bytes() / (sa + sb))));
+  const long long chunk = balanced_chunk(n_tiles, static_cast<long long>(budget_bytes() / (sa + sb)));
   char* base = static_cast<char*>(scratch(graph_bytes + size_t(chunk) * (sa + sb)));
   int* deg = reinterpret_cast<int*>(base);
   int* cursor = reinterpret_cast<int*>(base + nb);
