@@ -356,6 +356,13 @@ def main():
         scorer = None
         if wl == "train":
             host_labels = labels.cpu().pin_memory()
+        pinned_out = {}
+
+        def to_host(name, t):   # device -> pinned host buffer (allocated once), asynchronous
+            if name not in pinned_out:
+                pinned_out[name] = torch.empty(t.shape, dtype=t.dtype).pin_memory()
+            pinned_out[name].copy_(t, non_blocking=True)
+            return pinned_out[name]
 
         def e2e_step():
             d = {k: host[k].to(dev, non_blocking=True) for k in keys}
@@ -363,7 +370,9 @@ def main():
                 return model.score_soilnet(d["features"], d["edges"], d["node_off"], d["edge_off"], T, n_nodes_total).cpu()
             if wl == "ig":
                 af, aa, p = model.ig_cml(d["features"], d["anom"], d["edges"], d["node_off"], d["edge_off"], args.m_steps, n_nodes_total)
-                return af.cpu(), aa.cpu(), p.cpu()
+                res = to_host("af", af), to_host("aa", aa), to_host("p", p)
+                torch.cuda.synchronize()
+                return res
             lab = host_labels.to(dev, non_blocking=True)
             mom = model.train_moments_cml(d["features"])
             dp.all_reduce_sum(mom)
