@@ -63,6 +63,8 @@ def _load():
         "gnnqc_score_seq_noalloc": (C.c_int, [vp, vp, i64, i32, vp, vp]),
         "gnnqc_score_cml": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, vp, vp]),
         "gnnqc_score_cml_host": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, vp, vp]),
+        "gnnqc_select_threshold": (C.c_int, [C.c_int, vp, vp, i64, vp, vp, vp, vp]),
+        "gnnqc_roc_auc": (C.c_int, [C.c_int, vp, vp, i64, vp, vp]),
         "gnnqc_score_soilnet": (C.c_int, [vp, vp, vp, vp, vp, i64, i32, i64, i64, vp, vp]),
         "gnnqc_series_create": (C.c_int, [C.c_int, vp, vp, i64, i64, vp, vp, vp, vp, C.POINTER(vp)]),
         "gnnqc_series_update": (C.c_int, [vp, i64, i64, vp, vp]),

@@ -29,6 +29,12 @@ def _mcc(tp, fp, tn, fn):
 def select_threshold(predictions, anomaly_flags_true):
     """Candidate thresholds are the distinct scores rounded to 3 decimals; the one with the highest
     Matthews correlation wins, the smallest on ties (reference :9-17)."""
+    if getattr(predictions, "is_cuda", False):          # scores still on the GPU: sweep there (gnnqc_select_threshold)
+        import torch
+        from gnnqc import metrics
+        thr, mcc, _ = metrics.select_threshold(predictions, torch.as_tensor(anomaly_flags_true).to(predictions.device))
+        print("Max MCC: {:.3f} for threshold: {:.3f}".format(mcc, thr))
+        return np.float32(thr)
     scores = np.asarray(predictions).reshape(-1)          # keep the dtype: `score > thr` is evaluated in it
     truth = np.asarray(anomaly_flags_true).reshape(-1)
     candidates = np.unique(np.round(scores, 3))
@@ -65,7 +71,8 @@ def roc_auc(truth, scores):
     tpr = np.r_[0.0, tps / max(int(y.sum()), 1)]
     fpr = np.r_[0.0, fps / max(int(len(y) - y.sum()), 1)]
     thr = np.r_[np.inf, s[last_of_run]]
-    return fpr, tpr, thr, float(np.trapz(tpr, fpr))
+    trapezoid = getattr(np, "trapezoid", None) or np.trapz
+    return fpr, tpr, thr, float(trapezoid(tpr, fpr))
 
 
 def calculate_metrics(anomaly_flags_true, anomaly_flags_pred, predictions, model_config=None, threshold=0.5, baseline=False,

@@ -197,6 +197,21 @@ int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_de
                  int64_t B, int32_t T, int64_t n_nodes_total, int32_t m_steps,
                  float* attr_features_dev, float* attr_anom_dev, float* scores_dev, void* stream);
 
+/* ---- evaluation on the device -------------------------------------------
+ * gnnqc_select_threshold replaces select_threshold (libs/test_model.py:9-17): candidates are the
+ * distinct values of round(score, 3); `score > candidate` is evaluated in float32 and the candidate with
+ * the highest Matthews correlation wins, the smallest on ties.  scores_dev f32 [n] in [0, 1] (sigmoid
+ * outputs; anything else, NaN included, is an error), labels_dev i64 [n] (non-zero = anomaly).
+ * Outputs are HOST pointers, valid on return: threshold_out, mcc_out (optional), confusion_out
+ * (optional) i64 [4] = TP, FP, TN, FN at that threshold.
+ * gnnqc_roc_auc replaces sklearn.metrics.roc_auc_score as used by calculate_metrics
+ * (libs/test_model.py:49; libs/metrics.py:195-211): trapezoid area under the ROC curve whose points
+ * are the distinct scores; 0 when one class is absent.  n < 2^31. */
+int gnnqc_select_threshold(int device, const float* scores_dev, const int64_t* labels_dev, int64_t n,
+                           float* threshold_out, double* mcc_out, int64_t* confusion_out, void* stream);
+int gnnqc_roc_auc(int device, const float* scores_dev, const int64_t* labels_dev, int64_t n,
+                  double* auc_out, void* stream);
+
 /* ---- training ------------------------------------------------------------------------- */
 
 /* Together these replace one train_step of model.fit as train_model sets it up
