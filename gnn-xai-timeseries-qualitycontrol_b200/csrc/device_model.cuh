@@ -60,14 +60,16 @@ size_t tc_packed_bytes(int in, int hid);
 void tc_pack_host(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out);
 void tc_configure(int in, int hid, bool pool, bool last);
 void tc_launch(int in, int hid, bool pool, bool last, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
-               int sm_count, cudaStream_t st, float* save = nullptr, float* amax = nullptr);   // save != nullptr: also store gates (IG forward)
+               int sm_count, cudaStream_t st, float* save = nullptr, float* amax = nullptr, int nsave = 5);   // save != nullptr: also store gates (IG / training forward)
+void tc_repack_device(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out, cudaStream_t st);
 // Tensor-core LSTM backward (csrc/lstm_tc_bwd.cu).
 bool tc_bwd_supported(int in, int hid, bool pool, bool last);
 size_t tc_bwd_packed_bytes(int in, int hid);
 void tc_bwd_pack_host(const float* W, const float* U, int in, int hid, unsigned char* out);
 void tc_bwd_configure(int in, int hid, bool pool, bool last);
 void tc_bwd_launch(int in, int hid, bool pool, bool last, const float* dy, const float* save, const float* amax, const unsigned char* w,
-                   float* dx, int T, long long n_tiles, int sm_count, cudaStream_t st);
+                   float* dx, int T, long long n_tiles, int sm_count, cudaStream_t st, int nsave = 5, float* dz_out = nullptr);
+void tc_bwd_repack_device(const float* W, const float* U, int in, int hid, unsigned char* out, cudaStream_t st);
 // optimizer slots and per-step BN state (csrc/train.cu)
 
 struct DeviceModel {

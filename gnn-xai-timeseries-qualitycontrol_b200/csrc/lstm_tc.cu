@@ -21,7 +21,7 @@ struct TcLaunch {
   static auto kernel() { return lstm_tc_kernel<I, H, POOL, SAVE>; }
   static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
   static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st,
-                     float* save, float* amax) {
+                     float* save, float* amax, int nsave) {
     // One persistent CTA per SM (four window groups inside, lstm_tc.cuh); tiles are dealt evenly.
     if (std::getenv("GNNQC_DEBUG")) {
       cudaFuncAttributes fa;
@@ -29,7 +29,7 @@ struct TcLaunch {
       std::fprintf(stderr, "[gnnqc] tc I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
     }
     const long long grid = std::min<long long>(n_tiles, sm_count);
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax);
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
     GNNQC_CUDA(cudaGetLastError());
   }
 };
@@ -42,7 +42,7 @@ struct TcBigLaunch {
   static auto kernel() { return lstm_tc_big_kernel<I, H, POOL, LAST, STREAM, SAVE>; }
   static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
   static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st,
-                     float* save, float* amax) {
+                     float* save, float* amax, int nsave) {
     const long long n_pairs = (n_tiles + 1) / 2;
     const long long grid = std::min<long long>(n_pairs, sm_count);
     if (std::getenv("GNNQC_DEBUG")) {
@@ -50,7 +50,7 @@ struct TcBigLaunch {
       GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
       std::fprintf(stderr, "[gnnqc] tc-big I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
     }
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax);
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
     GNNQC_CUDA(cudaGetLastError());
   }
 };
@@ -66,6 +66,7 @@ struct TcArgs {
   cudaStream_t st = nullptr;
   float* save = nullptr;   // non-null: the gate-saving variant (integrated gradients forward)
   float* amax = nullptr;
+  int nsave = 5;
 };
 
 template <int I, int H, bool POOL>
@@ -74,8 +75,8 @@ bool tc_case(TcOp op, const TcArgs& a) {
     TcLaunch<I, H, POOL, false>::configure();
     TcLaunch<I, H, POOL, true>::configure();
   } else if (op == TcOp::Launch) {
-    if (a.save) TcLaunch<I, H, POOL, true>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax);
-    else TcLaunch<I, H, POOL, false>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, nullptr, nullptr);
+    if (a.save) TcLaunch<I, H, POOL, true>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax, a.nsave);
+    else TcLaunch<I, H, POOL, false>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, nullptr, nullptr, 5);
   }
   return true;
 }
@@ -86,8 +87,8 @@ bool tc_big_case(TcOp op, const TcArgs& a) {
     TcBigLaunch<I, H, POOL, LAST, false>::configure();
     TcBigLaunch<I, H, POOL, LAST, true>::configure();
   } else if (op == TcOp::Launch) {
-    if (a.save) TcBigLaunch<I, H, POOL, LAST, true>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax);
-    else TcBigLaunch<I, H, POOL, LAST, false>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, nullptr, nullptr);
+    if (a.save) TcBigLaunch<I, H, POOL, LAST, true>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax, a.nsave);
+    else TcBigLaunch<I, H, POOL, LAST, false>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, nullptr, nullptr, 5);
   }
   return true;
 }
@@ -185,12 +186,55 @@ void tc_pack_host(const float* W, const float* U, const float* bias, int in, int
   for (int col = 0; col < n; ++col) bout[col] = bias[col] * tc_gate_scale(col / hid);
 }
 
+namespace {
+// Device twin of tc_pack_host (same index maps, same fp32 scaling and bf16 rounding), for the refresh after an optimizer step.
+__global__ void __launch_bounds__(256) tc_repack_kernel(const float* __restrict__ W, const float* __restrict__ U, const float* __restrict__ bias,
+                                                        int in, int hid, unsigned char* __restrict__ out) {
+  const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, n = 4 * hid;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  const long long n_main = static_cast<long long>(kp) * n;
+  const bool big = hid >= 64;
+  const size_t main_bytes = big ? size_t(hid / 32) * (kp / 16) * 8192 : size_t(2) * kp * n * 2;
+  if (i < n_main) {
+    const int k = static_cast<int>(i / n), col = static_cast<int>(i % n);   // col: Keras gate column
+    float v = 0.f;
+    if (k < in) v = W[static_cast<long long>(k) * n + col];
+    else if (k >= ip && k < ip + hid) v = U[static_cast<long long>(k - ip) * n + col];
+    v *= tc_gate_scale(col / hid);
+    const __nv_bfloat16 h = __float2bfloat16_rn(v);
+    const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
+    if (big) {
+      const int gate = col / hid, unit = col % hid, c = unit / 32, nrow = gate * 32 + unit % 32, kc = k / 16, kk = k % 16;
+      __nv_bfloat16* hi = reinterpret_cast<__nv_bfloat16*>(out + (static_cast<size_t>(c) * (kp / 16) + kc) * 8192);
+      const size_t at = (static_cast<size_t>(kk / 8) * 128 + nrow) * 8 + (kk % 8);
+      hi[at] = h;
+      hi[2048 + at] = l;
+    } else {
+      __nv_bfloat16* bhi = reinterpret_cast<__nv_bfloat16*>(out);
+      const size_t at = (static_cast<size_t>(k / 8) * n + col) * 8 + (k % 8);
+      bhi[at] = h;
+      bhi[static_cast<size_t>(kp) * n + at] = l;
+    }
+  } else if (i < n_main + n) {
+    const int col = static_cast<int>(i - n_main);
+    reinterpret_cast<float*>(out + main_bytes)[col] = bias[col] * tc_gate_scale(col / hid);
+  }
+}
+}  // namespace
+
+void tc_repack_device(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out, cudaStream_t st) {
+  const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, n = 4 * hid;
+  const long long total = static_cast<long long>(kp) * n + n;
+  tc_repack_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(W, U, bias, in, hid, out);
+  GNNQC_CUDA(cudaGetLastError());
+}
+
 void tc_configure(int in, int hid, bool pool, bool last) { tc_dispatch(TcOp::Configure, in, hid, pool, last, TcArgs()); }
 
 void tc_launch(int in, int hid, bool pool, bool last, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
-               int sm_count, cudaStream_t st, float* save, float* amax) {
+               int sm_count, cudaStream_t st, float* save, float* amax, int nsave) {
   TcArgs a;
-  a.save = save; a.amax = amax;
+  a.save = save; a.amax = amax; a.nsave = nsave;
   a.x = x; a.y = y; a.w = w; a.T = T; a.t_in = t_in; a.t_out = t_out; a.n_tiles = n_tiles; a.sm_count = sm_count; a.st = st;
   if (!tc_dispatch(TcOp::Launch, in, hid, pool, last, a)) throw std::invalid_argument("no tensor-core kernel for this layer shape");
 }

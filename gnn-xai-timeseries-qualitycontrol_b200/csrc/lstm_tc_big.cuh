@@ -58,7 +58,8 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
                    const unsigned char* __restrict__ wpk,    // pieces [chunk][K slice]{hi, lo} | bias
                    int T, int t_in_stride, int t_out_stride, int n_tiles,
                    float* __restrict__ save = nullptr,       // SAVE: [n_tiles][T][5][H][64] gates i, f, g, o and c
-                   float* __restrict__ amax = nullptr) {     // SAVE && POOL: [n_tiles][t_out_stride][H][64] argmax step
+                   float* __restrict__ amax = nullptr,       // SAVE && POOL: [n_tiles][t_out_stride][H][64] argmax step
+               int nsave = 5) {                          // SAVE: 5, or 6 to store h_t as well (training)
   using C = TcBigCfg<I, H, STREAM>;
   extern __shared__ __align__(128) unsigned char sm[];
   uint4* Ahi = reinterpret_cast<uint4*>(sm + C::OFF_AHI);   // 16-byte chunk index: kb * ROWS + row
@@ -244,9 +245,10 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
               hv[i] = lstm_cell_tc_save(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
                                         zo[i] + bias[3 * H + j0 + i], cst[l0 + i], sv);
               if (valid) {
-                float* so = save + (((tile * T + t) * 5) * H + j0 + i) * kTile + b;
+                float* so = save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b;
 #pragma unroll
                 for (int v = 0; v < 5; ++v) so[v * H * kTile] = sv[v];
+              if (nsave > 5) so[5 * H * kTile] = hv[i];
               }
             } else {
               hv[i] = lstm_cell_tc(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],

@@ -20,7 +20,7 @@ struct TcBwdLaunch {
   static auto kernel() { return lstm_tc_bwd_kernel<I, H, POOL, LAST, GRP, SPLIT, STREAM>; }
   static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
   static void launch(const float* dy, const float* save, const float* amax, const unsigned char* wpk, float* dx, int T, long long n_tiles,
-                     int sm_count, cudaStream_t st) {
+                     int sm_count, cudaStream_t st, int nsave, float* dz_out) {
     const long long n_pairs = (n_tiles + 1) / 2;
     const long long grid = std::min<long long>(n_pairs, sm_count);
     if (std::getenv("GNNQC_DEBUG")) {
@@ -28,7 +28,7 @@ struct TcBwdLaunch {
       GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
       std::fprintf(stderr, "[gnnqc] tc-bwd I=%d H=%d regs=%d local=%zu smem=%zu threads=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::NT);
     }
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wpk, dx, T, static_cast<int>(n_tiles));
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wpk, dx, T, static_cast<int>(n_tiles), nsave, dz_out);
     GNNQC_CUDA(cudaGetLastError());
   }
 };
@@ -44,17 +44,20 @@ struct BwdArgs {
   int T = 0, sm_count = 0;
   long long n_tiles = 0;
   cudaStream_t st = nullptr;
+  int nsave = 5;
+  float* dz_out = nullptr;
 };
 
 template <int I, int H, bool POOL, bool LAST, int GRP, int SPLIT>
 bool bwd_case(BwdOp op, const BwdArgs& a) {
   using L = TcBwdLaunch<I, H, POOL, LAST, GRP, SPLIT>;
   if (op == BwdOp::Configure) L::configure();
-  else if (op == BwdOp::Launch) L::launch(a.dy, a.save, a.amax, a.w, a.dx, a.T, a.n_tiles, a.sm_count, a.st);
+  else if (op == BwdOp::Launch) L::launch(a.dy, a.save, a.amax, a.w, a.dx, a.T, a.n_tiles, a.sm_count, a.st, a.nsave, a.dz_out);
   return true;
 }
 
 bool bwd_dispatch(BwdOp op, int in, int hid, bool pool, bool last, const BwdArgs& a) {
+  if (in == 2 && hid == 16 && !pool && !last) return bwd_case<2, 16, false, false, 4, 1>(op, a);
   if (in == 18 && hid == 16 && !pool && !last) return bwd_case<18, 16, false, false, 4, 1>(op, a);
   if (in == 16 && hid == 16 && pool && !last) return bwd_case<16, 16, true, false, 4, 1>(op, a);
   if (in == 16 && hid == 32 && !pool && !last) return bwd_case<16, 32, false, false, 4, 1>(op, a);
@@ -101,11 +104,39 @@ void tc_bwd_pack_host(const float* W, const float* U, int in, int hid, unsigned 
   }
 }
 
+namespace {
+// Device twin of tc_bwd_pack_host.
+__global__ void __launch_bounds__(256) tc_bwd_repack_kernel(const float* __restrict__ W, const float* __restrict__ U, int in, int hid,
+                                                            unsigned char* __restrict__ out) {
+  const int ip = (in + 15) / 16 * 16, n_out = ip + hid, n4 = 4 * hid;
+  const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
+  if (i >= static_cast<long long>(n_out) * n4) return;
+  const int n = static_cast<int>(i / n4), col = static_cast<int>(i % n4);
+  float v = 0.f;
+  if (n < in) v = W[static_cast<long long>(n) * n4 + col];
+  else if (n >= ip) v = U[static_cast<long long>(n - ip) * n4 + col];
+  const __nv_bfloat16 h = __float2bfloat16_rn(v);
+  const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
+  const int gate = col / hid, unit = col % hid, c = unit / 8, u = unit % 8, s = gate / 2, kb = gate % 2;
+  unsigned char* piece = out + static_cast<size_t>(c) * 128 * n_out;
+  const size_t at = (static_cast<size_t>(kb) * n_out + n) * 8 + u;
+  reinterpret_cast<__nv_bfloat16*>(piece + static_cast<size_t>(s * 2 + 0) * 2 * n_out * 16)[at] = h;
+  reinterpret_cast<__nv_bfloat16*>(piece + static_cast<size_t>(s * 2 + 1) * 2 * n_out * 16)[at] = l;
+}
+}  // namespace
+
+void tc_bwd_repack_device(const float* W, const float* U, int in, int hid, unsigned char* out, cudaStream_t st) {
+  const long long total = static_cast<long long>((in + 15) / 16 * 16 + hid) * 4 * hid;
+  tc_bwd_repack_kernel<<<static_cast<unsigned>((total + 255) / 256), 256, 0, st>>>(W, U, in, hid, out);
+  GNNQC_CUDA(cudaGetLastError());
+}
+
 void tc_bwd_configure(int in, int hid, bool pool, bool last) { bwd_dispatch(BwdOp::Configure, in, hid, pool, last, BwdArgs()); }
 
 void tc_bwd_launch(int in, int hid, bool pool, bool last, const float* dy, const float* save, const float* amax, const unsigned char* w,
-                   float* dx, int T, long long n_tiles, int sm_count, cudaStream_t st) {
+                   float* dx, int T, long long n_tiles, int sm_count, cudaStream_t st, int nsave, float* dz_out) {
   BwdArgs a;
+  a.nsave = nsave; a.dz_out = dz_out;
   a.dy = dy; a.save = save; a.amax = amax; a.w = w; a.dx = dx; a.T = T; a.n_tiles = n_tiles; a.sm_count = sm_count; a.st = st;
   if (!bwd_dispatch(BwdOp::Launch, in, hid, pool, last, a)) throw std::invalid_argument("no tensor-core backward kernel for this layer shape");
 }

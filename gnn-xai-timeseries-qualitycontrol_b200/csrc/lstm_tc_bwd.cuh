@@ -59,7 +59,9 @@ lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this lay
                    const float* __restrict__ amax,          // POOL: [n_tiles][T/3][H][64]
                    const unsigned char* __restrict__ wpk,   // B pieces per chunk (TcBwdCfg::PACKED_BYTES)
                    float* __restrict__ dx,                  // [n_tiles][T][I][64]
-                   int T, int n_tiles) {
+                   int T, int n_tiles,
+                   int nsave = 5,                           // quantities per step in `save` (6 in training)
+                   float* __restrict__ dz_out = nullptr) {  // training: [n_tiles][T][4H][64] gate pre-activation gradients
   using C = TcBwdCfg<I, H, GRP, SPLIT, STREAM>;
   extern __shared__ __align__(128) unsigned char sm[];
   __shared__ uint32_t tmem_slot;
@@ -219,12 +221,12 @@ lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this lay
         if (!new_seq) umma::tmem_ld8(tlane + sprev * C::N + C::IP + j0, dh);
         float zi[8], zf[8], zg[8], zo[8];
         if (valid) {
-          const float* sv = save + (((tile * T + t) * 5) * H + j0) * kTile + b;
+          const float* sv = save + (((tile * T + t) * nsave) * H + j0) * kTile + b;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const float ig = __ldg(sv + (0 * H + i) * kTile), fg = __ldg(sv + (1 * H + i) * kTile), gg = __ldg(sv + (2 * H + i) * kTile),
                         og = __ldg(sv + (3 * H + i) * kTile), ct = __ldg(sv + (4 * H + i) * kTile);
-            const float cp = (t > 0) ? __ldg(sv + (i - H) * kTile) : 0.f;   // c of step t-1: quantity 4 of the previous step's block
+            const float cp = (t > 0) ? __ldg(sv + (i - (nsave - 4) * H) * kTile) : 0.f;   // c of step t-1: quantity 4 of the previous step's block
             float d = dh[i];
             if (POOL) {
               const long long o = ((tile * t_dy + t / 3) * H + j0 + i) * kTile + b;
@@ -242,6 +244,16 @@ lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this lay
             zg[i] = dcc * ig * (1.f - gg * gg);
             zo[i] = d * th * og * (1.f - og);
             dcv[ci * C::UB + i] = dcc * fg;
+          }
+          if (dz_out) {
+            float* dzo = dz_out + ((tile * T + t) * 4 * H + j0) * kTile + b;
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              dzo[(0 * H + i) * kTile] = zi[i];
+              dzo[(1 * H + i) * kTile] = zf[i];
+              dzo[(2 * H + i) * kTile] = zg[i];
+              dzo[(3 * H + i) * kTile] = zo[i];
+            }
           }
         } else {
 #pragma unroll

@@ -59,6 +59,7 @@ struct LayerArgs {
   const float* in = nullptr;
   float* out = nullptr;
   const float* w = nullptr;
+  const unsigned char* wtc = nullptr;   // tensor-core operand tiles of this direction (null: fp32 kernel)
   float* save = nullptr;
   float* amax = nullptr;
   float* dz = nullptr;
@@ -73,9 +74,14 @@ void layer_op(Op op, const LayerArgs& a) {
   if (op == Op::Configure) {
     TrainFwd<I, H, POOL, LAST>::configure();
     TrainBwd<I, H, POOL, LAST>::configure();
+    if (tc_bwd_supported(I, H, POOL, LAST)) tc_bwd_configure(I, H, POOL, LAST);
   } else if (op == Op::Forward) {
+    if (a.wtc && tc_layer_supported(I, H, POOL, LAST))   // lstm_tc*.cuh in SAVE mode with h_t as sixth quantity
+      return tc_launch(I, H, POOL, LAST, a.in, a.out, a.wtc, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax, 6);
     TrainFwd<I, H, POOL, LAST>::launch(a.in, a.out, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.save, a.amax, a.st);
   } else {
+    if (a.wtc && tc_bwd_supported(I, H, POOL, LAST))     // lstm_tc_bwd.cuh, also writing dz for the weight-gradient kernel
+      return tc_bwd_launch(I, H, POOL, LAST, a.in, a.save, a.amax, a.wtc, a.out, a.T, a.n_tiles, a.sm_count, a.st, 6, a.dz);
     TrainBwd<I, H, POOL, LAST>::launch(a.in, a.save, a.amax, a.w, a.out, a.T, a.n_tiles, a.sm_count, a.dz, a.st);
   }
 }
@@ -171,7 +177,10 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   const ModelSpec& s = host.spec;
   const bool gcn = s.has_gcn;
   GNNQC_CUDA(cudaSetDevice(device));
+  refresh_tc();   // no-op inside a training loop: train_apply refreshes the operand tiles on the device
   TrainState* ts = train_state();
+  // GNNQC_TRAIN_TC=0: forward/backward on the fp32 CUDA-core kernels (A/B)
+  static const bool train_tc = [] { const char* e = std::getenv("GNNQC_TRAIN_TC"); return !(e && std::strcmp(e, "0") == 0); }();
   StackPlan plan(s, T);
   const int L = s.n_lstm;
   const long long nt = (B + kTile - 1) / kTile;
@@ -234,6 +243,7 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
     LayerArgs a;
     a.in = in; a.out = F(o_y[l]); a.w = d_packed + packed_off[l]; a.save = F(o_save[l]); a.amax = pool ? F(o_amax[l]) : nullptr;
+    a.wtc = train_tc ? d_packed_tc + packed_tc_off[l] : nullptr;
     a.T = plan.t_run[l]; a.t_in = t_in; a.t_out = plan.t_out[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
     mark_begin(kFwd[l], st);
     dispatch(Op::Forward, s.lstm_in[l], s.lstm_hid[l], pool, last, a);
@@ -255,6 +265,9 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
     LayerArgs a;
     a.in = dy; a.out = (l % 2 == 0) ? F(o_g0) : F(o_g1); a.w = d_packed_t + packed_t_off[l]; a.save = F(o_save[l]);
+    // the tensor-core backward needs many tile pairs in flight to cover its per-chunk MMA round trips; a small
+    // training batch (4,096 windows = 32 pairs) is faster on the fp32 kernel
+    a.wtc = (train_tc && nt >= 2LL * sm_count) ? d_packed_tcb + packed_tcb_off[l] : nullptr;
     a.amax = pool ? F(o_amax[l]) : nullptr; a.dz = F(o_dz[l]);
     a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
     mark_begin(kBwd[l], st);
@@ -348,9 +361,12 @@ void DeviceModel::train_apply(float* rvec, const double* moments, float lr, cuda
                                                                           d_params + s.off_lstm_b[l], in, h, d_packed + packed_off[l],
                                                                           d_packed_t + packed_t_off[l], kpad);
     GNNQC_CUDA(cudaGetLastError());
+    // the tensor-core operand tiles too, so neither the next training step nor the next scoring call goes through the host
+    tc_repack_device(d_params + s.off_lstm_w[l], d_params + s.off_lstm_u[l], d_params + s.off_lstm_b[l], in, h, d_packed_tc + packed_tc_off[l], st);
+    tc_bwd_repack_device(d_params + s.off_lstm_w[l], d_params + s.off_lstm_u[l], in, h, d_packed_tcb + packed_tcb_off[l], st);
   }
   params_dirty = true;
-  tc_stale = true;
+  tc_stale = false;
 }
 
 }  // namespace gnnqc

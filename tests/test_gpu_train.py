@@ -142,3 +142,50 @@ def test_loss_goes_down_on_a_fixed_batch():
         assert torch.isfinite(s).all()
     finally:
         m.close()
+
+
+def test_large_batch_gradients_equal_the_sum_of_their_parts():
+    """19,200 windows = 300 tiles: the backward pass runs on the tensor-core kernels (with dz for the weight
+    gradients), 6,400-window calls on the fp32 ones.  With the same global batch size and BN moments the
+    reduction vectors are additive, so the two must agree to rounding."""
+    from test_gpu_scoring import _slice_cml
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    try:
+        B, T = 19200, 181
+        batch = synth.make_cml_batch(B, seed=8, n_nodes=4, device="cuda")
+        labels = make_labels(B, 8).cuda()
+        mom = m.train_moments_cml(batch["features"])
+        full = m.train_grads_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"], labels, mom,
+                                 global_batch=B).double()
+        parts = torch.zeros_like(full)
+        for w0 in range(0, B, 6400):
+            s = _slice_cml(batch, w0, w0 + 6400, T)
+            parts += m.train_grads_cml(s["features"], s["anom"], s["edges"], s["node_off"], s["edge_off"], labels[w0:w0 + 6400], mom,
+                                       global_batch=B).double()
+        for name, off, shape, _ in m.segments():
+            n = int(np.prod(shape))
+            a, b = full[off:off + n].cpu().numpy(), parts[off:off + n].cpu().numpy()
+            tol = 2e-4 * np.abs(b).max() + 1e-3 * np.abs(b) + 1e-9
+            assert (np.abs(a - b) <= tol).all(), "%s: max err %.3e vs max |g| %.3e" % (name, np.abs(a - b).max(), np.abs(b).max())
+        tail_a, tail_b = full[m.n_params:].cpu().numpy(), parts[m.n_params:].cpu().numpy()
+        assert np.all(np.abs(tail_a - tail_b) <= 1e-3 * np.abs(tail_b) + 2e-4 * np.abs(tail_b).max())
+    finally:
+        m.close()
+
+
+def test_device_refresh_of_tensor_core_operands_equals_host_packing():
+    """After an optimizer step the bf16 operand tiles are re-derived on the device; re-uploading the same
+    parameters from the host (host-side packing) must give bit-identical scores."""
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    try:
+        batch = cuda(synth.make_cml_batch(300, seed=3, n_nodes=5))
+        labels = make_labels(300, 3).cuda()
+        mom = m.train_moments_cml(batch["features"])
+        rvec = m.train_grads_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"], labels, mom)
+        m.train_apply(rvec, mom, 1e-3)
+        after_step = m.score_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"]).clone()
+        m.set_params(m.get_params())
+        from_host = m.score_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"])
+        assert torch.equal(after_step, from_host)
+    finally:
+        m.close()
