@@ -426,9 +426,9 @@ def main():
     for name, (ms, cnt) in sorted(prof.items(), key=lambda kv: -kv[1][0]):
         k = {"name": name, "ms_per_step": ms / prof_steps, "launches_per_step": cnt / prof_steps}
         if "_l" in name and name[-1].isdigit() and ("lstm" in name or "fwd" in name or "bwd" in name):
-            i = int(name[-1]) - 1
-            k["tflops_executed"] = fl_live[i] * units * passes / (ms / prof_steps * 1e-3) / 1e12
-            k["tflops_algorithmic"] = fl_alg[i] * units * passes / (ms / prof_steps * 1e-3) / 1e12
+            layers = [0, 1] if name.endswith("_l1_l2") else [int(name[-1]) - 1]     # lstm_l1_l2: the fused first pair
+            k["tflops_executed"] = sum(fl_live[i] for i in layers) * units * passes / (ms / prof_steps * 1e-3) / 1e12
+            k["tflops_algorithmic"] = sum(fl_alg[i] for i in layers) * units * passes / (ms / prof_steps * 1e-3) / 1e12
         kernels.append(k)
     timed = [k for k in kernels if "tflops_executed" in k]
     total_kernel_ms = sum(k["ms_per_step"] for k in kernels)

@@ -269,6 +269,7 @@ void DeviceModel::configure_kernels() {
     layer_dispatch<true>(s.lstm_in[l], s.lstm_hid[l], pool, last, nullptr, nullptr, nullptr, 0, 0, 0, 0, 0, nullptr);
     if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last)) tc_configure(s.lstm_in[l], s.lstm_hid[l], pool, last);
   }
+  if (s.n_lstm >= 3 && tc_pair_supported(s.lstm_in[0], s.lstm_hid[0], s.lstm_in[1], s.lstm_hid[1])) tc_pair_configure(s.lstm_in[0]);
   configure_cml_frontend();
   GNNQC_CUDA(cudaGetLastError());
   if (s.lstm_hid[s.n_lstm - 1] != 128 || s.dense_units != 64)
@@ -279,12 +280,31 @@ void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, l
                             float* scores, cudaStream_t st) {
   const ModelSpec& s = host.spec;
   const float* in = buf_a;
+  float* bufs[2] = {buf_a, buf_b};
+  int cur = 0;                       // `in` lives in bufs[cur]; every layer writes the other buffer
   int t_in = plan.t_run[0];
-  for (int l = 0; l < s.n_lstm; ++l) {
+  static const char* const kNames[kMaxLstmLayers] = {"lstm_l1", "lstm_l2", "lstm_l3", "lstm_l4", "lstm_l5", "lstm_l6", "lstm_l7"};
+  int l = 0;
+  // Layers 1 + 2 as one kernel when the shapes allow it.  It reads buffer A and writes B, which swaps the
+  // roles the two buffers have in the one-kernel-per-layer schedule, so both must hold any later layer.
+  if (s.n_lstm >= 3 && plan.t_run[0] == plan.t_run[1] && tc_pair_supported(s.lstm_in[0], s.lstm_hid[0], s.lstm_in[1], s.lstm_hid[1])) {
+    size_t need = 0;
+    for (int k = 1; k < s.n_lstm; ++k) need = std::max(need, size_t(plan.t_out[k]) * s.lstm_hid[k] * kTile * sizeof(float));
+    if (need <= std::min(plan.bytes_a, plan.bytes_b)) {
+      mark_begin("lstm_l1_l2", st);
+      tc_pair_launch(s.lstm_in[0], in, bufs[1], d_packed_tc + packed_tc_off[0], d_packed_tc + packed_tc_off[1], plan.t_run[0], t_in,
+                     plan.t_out[1], n_tiles, sm_count, st);
+      mark_end(st);
+      in = bufs[1];
+      cur = 1;
+      t_in = plan.t_out[1];
+      l = 2;
+    }
+  }
+  for (; l < s.n_lstm; ++l) {
     const bool last = (l == s.n_lstm - 1);
     const bool pool = !last && (l % 2 == 1);
-    float* out = (l % 2 == 0) ? buf_b : buf_a;
-    static const char* const kNames[kMaxLstmLayers] = {"lstm_l1", "lstm_l2", "lstm_l3", "lstm_l4", "lstm_l5", "lstm_l6", "lstm_l7"};
+    float* out = bufs[cur ^ 1];
     mark_begin(kNames[l], st);
     if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last))
       tc_launch(s.lstm_in[l], s.lstm_hid[l], pool, last, in, out, d_packed_tc + packed_tc_off[l], plan.t_run[l], t_in, plan.t_out[l], n_tiles,
@@ -294,6 +314,7 @@ void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, l
                             plan.t_out[l], n_tiles, sm_count, st);
     mark_end(st);
     in = out;
+    cur ^= 1;
     t_in = plan.t_out[l];
   }
   const float* p = d_params;

@@ -11,6 +11,7 @@
 #include "device_model.cuh"
 #include "lstm_tc.cuh"
 #include "lstm_tc_big.cuh"
+#include "lstm_tc_pair.cuh"
 
 namespace gnnqc {
 namespace {
@@ -124,6 +125,42 @@ int tc_max_hidden() {
 }
 
 }  // namespace
+
+namespace {
+template <int I>
+bool pair_case(TcOp op, const TcArgs& a, const unsigned char* w2) {
+  using Cfg = TcPairCfg<I>;
+  if (op == TcOp::Configure) {
+    GNNQC_CUDA(cudaFuncSetAttribute(lstm_tc_pair_kernel<I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+  } else if (op == TcOp::Launch) {
+    const long long grid = std::min<long long>(a.n_tiles, a.sm_count);
+    lstm_tc_pair_kernel<I><<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, a.st>>>(a.x, a.y, a.w, w2, a.T, a.t_in, a.t_out,
+                                                                                            static_cast<int>(a.n_tiles));
+    GNNQC_CUDA(cudaGetLastError());
+  }
+  return true;
+}
+bool pair_dispatch(TcOp op, int in, const TcArgs& a, const unsigned char* w2) {
+  if (in == 2) return pair_case<2>(op, a, w2);
+  if (in == 3) return pair_case<3>(op, a, w2);
+  if (in == 18) return pair_case<18>(op, a, w2);
+  if (in == 19) return pair_case<19>(op, a, w2);
+  return false;
+}
+}  // namespace
+
+// Layers 1 and 2 of the stack (I -> 16, 16 -> 16 + pool) as one kernel (lstm_tc_pair.cuh).  GNNQC_TC_PAIR=0: two launches (A/B).
+bool tc_pair_supported(int in0, int hid0, int in1, int hid1) {
+  static const bool off = [] { const char* e = std::getenv("GNNQC_TC_PAIR"); return e && std::strcmp(e, "0") == 0; }();
+  return !off && tc_max_hidden() >= 16 && hid0 == 16 && in1 == 16 && hid1 == 16 && pair_dispatch(TcOp::Query, in0, TcArgs(), nullptr);
+}
+void tc_pair_configure(int in0) { pair_dispatch(TcOp::Configure, in0, TcArgs(), nullptr); }
+void tc_pair_launch(int in0, const float* x, float* y, const unsigned char* w1, const unsigned char* w2, int T, int t_in, int t_out,
+                    long long n_tiles, int sm_count, cudaStream_t st) {
+  TcArgs a;
+  a.x = x; a.y = y; a.w = w1; a.T = T; a.t_in = t_in; a.t_out = t_out; a.n_tiles = n_tiles; a.sm_count = sm_count; a.st = st;
+  if (!pair_dispatch(TcOp::Launch, in0, a, w2)) throw std::invalid_argument("no fused tensor-core kernel for this first layer");
+}
 
 bool tc_layer_supported(int in, int hid, bool pool, bool last) {
   if (hid > tc_max_hidden()) return false;
