@@ -469,17 +469,24 @@ def main():
     live0 = LIVE_STEPS[0]
     fe_bytes = {"cml_frontend": 8 * live0 * (N_NODES + 1) + 4 * N_NODES + 8 + 4 * 18 * live0,
                 "ig_frontend_bwd": 3 * 8 * live0 * (N_NODES + 1) + 4 * 18 * live0 + 4 * N_NODES}
-    if top["name"] in fe_bytes and wl in ("cml_gcn", "ig"):
-        per_launch = fe_bytes[top["name"]] * units
-        ach = per_launch * top["launches_per_step"] / (top["ms_per_step"] * 1e-3) / 1e9
-        roofline = {"bound": "hbm", "kernel": top["name"], "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
-                    "traffic": None, "peak_source": hbm_src,
-                    "note": "largest single kernel of the step (%.0f%% of kernel time); algorithmic bytes per launch %d (live steps of the "
-                            "features, coefficients, output tile)" % (100 * top["ms_per_step"] / total_kernel_ms, per_launch)}
+    fe_roof = None
+    fe_k = next((k for k in kernels if k["name"] in fe_bytes), None) if wl in ("cml_gcn", "ig") else None
+    if fe_k is not None:
+        per_launch = fe_bytes[fe_k["name"]] * units
+        ach = per_launch * fe_k["launches_per_step"] / (fe_k["ms_per_step"] * 1e-3) / 1e9
+        fe_roof = {"bound": "hbm", "kernel": fe_k["name"], "achieved": ach, "peak": hbm_peak, "unit": "GB/s", "frac": ach / hbm_peak,
+                   "traffic": None, "peak_source": hbm_src,
+                   "note": "%.0f%% of kernel time; algorithmic bytes per launch %d (live steps of the features, coefficients, "
+                           "output tile)" % (100 * fe_k["ms_per_step"] / total_kernel_ms, per_launch)}
+    if fe_roof is not None and top["name"] == fe_roof["kernel"]:
+        roofline = dict(fe_roof)
     else:
         roofline = {"bound": "tensor", "kernel": tensor["kernel"], "achieved": tensor["achieved"], "peak": tensor_peak, "unit": "TFLOP/s",
                     "frac": tensor["frac"], "traffic": None, "peak_source": tensor_src,
-                    "note": "split-bf16 (3 MMA passes) tcgen05 LSTM layers; the binding unit is the MUFU pipe, see xu"}
+                    "note": "split-bf16 (3 MMA passes) tcgen05 LSTM layers, %.0f%% of kernel time (largest single kernel: %s); the binding "
+                            "unit is the MUFU pipe, see xu" % (100 * lstm_ms / total_kernel_ms, top["name"])}
+    if fe_roof is not None:
+        roofline["frontend"] = fe_roof
     roofline["tensor"] = tensor
     roofline["xu"] = xu
     roofline["hbm"] = step_hbm

@@ -17,8 +17,12 @@ template <int I, int H, bool POOL, bool LAST, int GRP, int SPLIT>
 struct TcBwdLaunch {
   static constexpr bool STREAM = (H > 64);
   using Cfg = TcBwdCfg<I, H, GRP, SPLIT, STREAM>;
-  static auto kernel() { return lstm_tc_bwd_kernel<I, H, POOL, LAST, GRP, SPLIT, STREAM>; }
-  static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
+  static auto kernel() { return lstm_tc_bwd_kernel<I, H, POOL, LAST, GRP, SPLIT, STREAM, false>; }
+  static auto kernel_train() { return lstm_tc_bwd_kernel<I, H, POOL, LAST, GRP, SPLIT, STREAM, true>; }
+  static void configure() {
+    GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+    GNNQC_CUDA(cudaFuncSetAttribute(kernel_train(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+  }
   static void launch(const float* dy, const float* save, const float* amax, const unsigned char* wpk, float* dx, int T, long long n_tiles,
                      int sm_count, cudaStream_t st, int nsave, float* dz_out) {
     const long long n_pairs = (n_tiles + 1) / 2;
@@ -28,7 +32,12 @@ struct TcBwdLaunch {
       GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
       std::fprintf(stderr, "[gnnqc] tc-bwd I=%d H=%d regs=%d local=%zu smem=%zu threads=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::NT);
     }
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wpk, dx, T, static_cast<int>(n_tiles), nsave, dz_out);
+    if (nsave == 6 && dz_out)
+      kernel_train()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wpk, dx, T, static_cast<int>(n_tiles), dz_out);
+    else if (nsave == 5 && !dz_out)
+      kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wpk, dx, T, static_cast<int>(n_tiles), nullptr);
+    else
+      throw std::invalid_argument("tensor-core backward: nsave/dz_out combination not built");
     GNNQC_CUDA(cudaGetLastError());
   }
 };

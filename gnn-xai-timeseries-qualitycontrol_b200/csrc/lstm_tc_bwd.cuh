@@ -52,7 +52,8 @@ struct TcBwdCfg {
   static_assert(SMEM_BYTES <= 227 * 1024, "operands do not fit in shared memory");
 };
 
-template <int I, int H, bool POOL, bool LAST, int GRP, int SPLIT, bool STREAM>
+// TRAIN: the forward saved six quantities per step (h_t too) and dz is also written for the weight-gradient kernel.
+template <int I, int H, bool POOL, bool LAST, int GRP, int SPLIT, bool STREAM, bool TRAIN = false>
 __global__ void __launch_bounds__((TcBwdCfg<I, H, GRP, SPLIT, STREAM>::NT), 1)
 lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this layer's output (layouts of lstm_bwd.cuh)
                    const float* __restrict__ save,          // [n_tiles][T][5][H][64]
@@ -60,9 +61,9 @@ lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this lay
                    const unsigned char* __restrict__ wpk,   // B pieces per chunk (TcBwdCfg::PACKED_BYTES)
                    float* __restrict__ dx,                  // [n_tiles][T][I][64]
                    int T, int n_tiles,
-                   int nsave = 5,                           // quantities per step in `save` (6 in training)
-                   float* __restrict__ dz_out = nullptr) {  // training: [n_tiles][T][4H][64] gate pre-activation gradients
+                   float* __restrict__ dz_out = nullptr) {  // TRAIN: [n_tiles][T][4H][64] gate pre-activation gradients
   using C = TcBwdCfg<I, H, GRP, SPLIT, STREAM>;
+  constexpr int nsave = TRAIN ? 6 : 5;
   extern __shared__ __align__(128) unsigned char sm[];
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -245,7 +246,7 @@ lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this lay
             zo[i] = d * th * og * (1.f - og);
             dcv[ci * C::UB + i] = dcc * fg;
           }
-          if (dz_out) {
+          if (TRAIN) {
             float* dzo = dz_out + ((tile * T + t) * 4 * H + j0) * kTile + b;
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
