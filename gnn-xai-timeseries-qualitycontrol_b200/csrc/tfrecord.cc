@@ -245,8 +245,103 @@ void append_example(const SequenceExample& ex, const std::string& mode, CmlBatch
   b->dates.push_back(dates);
 }
 
+// ---- SoilNet windows (create_example, ds_type == 'soilnet'; parse_soilnet_tfrecord_fn) ---------------
+// One parsed file = one batch in the offsets layout of gnnqc_score_soilnet: features [sum T*N_b, 3]
+// (moisture, temp, battv), one label and one sensor id per (window, sensor).
+struct SoilBatch {
+  int64_t T = 0;
+  std::vector<float> features;
+  std::vector<int64_t> edges, edge_off, labels, sensor_ids;
+  std::vector<int32_t> node_off;
+  std::vector<std::string> dates;
+};
+
+// parse_soilnet_tfrecord_fn's normalisation modes (reference :821-852): out = (x - sub[n]) / div[n].
+void soil_normaliser(const SequenceExample& ex, const std::string& mode, int ch, size_t n_nodes, std::vector<float>* sub,
+                     std::vector<float>* div) {
+  static const char* const kNames[3] = {"moisture_", "temp_", "battv_"};
+  const std::string p = kNames[ch];
+  sub->assign(n_nodes, 0.f);
+  div->assign(n_nodes, 1.f);
+  auto load = [&](const std::string& key, std::vector<float>* dst) {
+    const Feature& f = need(ex.context, p + key);
+    if (f.floats.size() != n_nodes) fail("context feature '" + p + key + "' has the wrong length");
+    *dst = f.floats;
+  };
+  if (mode == "scale_range") {   // fixed physical ranges: moisture / 60, temp in [-20, 40], battv in [2800, 3600]
+    static const float kSub[3] = {0.f, -20.f, 2800.f}, kDiv[3] = {60.f, 60.f, 800.f};
+    sub->assign(n_nodes, kSub[ch]);
+    div->assign(n_nodes, kDiv[ch]);
+  } else if (mode == "standarization") { load("mean", sub); load("std", div); }
+  else if (mode == "median") load("median", sub);                 // the reference's division is commented out
+  else if (mode == "rolling_median") load("rolling_median", sub);
+  else if (mode == "rolling_median_fractional") { load("rolling_median", sub); load("rolling_median", div); }
+  else if (mode == "rolling_mean") { load("rolling_mean", sub); load("rolling_std", div); }
+  else if (mode == "scale") {
+    std::vector<float> mx;
+    load("min", sub);
+    load("max", &mx);
+    for (size_t i = 0; i < n_nodes; ++i) (*div)[i] = mx[i] - (*sub)[i];
+  } else if (mode != "none" && !mode.empty()) fail("unknown normalisation '" + mode + "'");
+}
+
+const std::vector<Feature>& need_list(const SequenceExample& ex, const std::string& key) {
+  auto it = ex.lists.find(key);
+  if (it == ex.lists.end()) fail("SequenceExample has no feature list '" + key + "'");
+  return it->second;
+}
+
+void append_soil_example(const SequenceExample& ex, const std::string& mode, SoilBatch* b) {
+  static const char* const kLists[3] = {"moisture", "temp", "battv"};
+  const std::vector<Feature>* ch[3];
+  for (int c = 0; c < 3; ++c) ch[c] = &need_list(ex, kLists[c]);
+  const size_t T = ch[0]->size();
+  if (T == 0 || ch[1]->size() != T || ch[2]->size() != T) fail("moisture / temp / battv have different lengths");
+  if (b->T == 0) b->T = static_cast<int64_t>(T);
+  if (static_cast<size_t>(b->T) != T) fail("windows of different lengths in one file");
+  const size_t N = (*ch[0])[0].floats.size();
+  if (N == 0) fail("window without sensors");
+  std::vector<float> sub[3], div[3];
+  for (int c = 0; c < 3; ++c) soil_normaliser(ex, mode, c, N, &sub[c], &div[c]);
+  const size_t f0 = b->features.size();
+  b->features.resize(f0 + T * N * 3);
+  for (size_t t = 0; t < T; ++t)
+    for (int c = 0; c < 3; ++c) {
+      const std::vector<float>& row = (*ch[c])[t].floats;
+      if (row.size() != N) fail("ragged timestep inside a window");
+      for (size_t n = 0; n < N; ++n) b->features[f0 + (t * N + n) * 3 + c] = (row[n] - sub[c][n]) / div[c][n];
+    }
+  const std::vector<Feature>& nodes = need_list(ex, "nodes");
+  const std::vector<Feature>& nbrs = need_list(ex, "neighbours");
+  if (nodes.size() != nbrs.size()) fail("nodes / neighbours malformed");
+  for (size_t e = 0; e < nodes.size(); ++e) {
+    if (nodes[e].ints.size() != 1 || nbrs[e].ints.size() != 1) fail("edge feature without exactly one index");
+    b->edges.push_back(nodes[e].ints[0]);
+    b->edges.push_back(nbrs[e].ints[0]);
+  }
+  const std::vector<Feature>& flags = need_list(ex, "anomaly_flag");
+  const std::vector<Feature>& sids = need_list(ex, "sensor_ids");
+  if (flags.size() != N || sids.size() != N) fail("anomaly_flag / sensor_ids do not have one entry per sensor");
+  for (size_t n = 0; n < N; ++n) {
+    if (flags[n].ints.size() != 1 || sids[n].ints.size() != 1) fail("anomaly_flag / sensor_ids feature without exactly one value");
+    b->labels.push_back(flags[n].ints[0]);
+    b->sensor_ids.push_back(sids[n].ints[0]);
+  }
+  b->node_off.push_back(b->node_off.back() + static_cast<int32_t>(N));
+  b->edge_off.push_back(b->edge_off.back() + static_cast<int64_t>(nodes.size()));
+  std::string dates;
+  auto d = ex.context.find("dates");
+  if (d != ex.context.end())
+    for (size_t i = 0; i < d->second.bytes.size(); ++i) dates += (i ? "," : "") + d->second.bytes[i];
+  b->dates.push_back(dates);
+}
+
 }  // namespace
 }  // namespace gnnqc
+
+struct gnnqc_soilnet_records {
+  gnnqc::SoilBatch batch;
+};
 
 struct gnnqc_cml_records {
   gnnqc::CmlBatch batch;
@@ -302,5 +397,51 @@ const char* gnnqc_cml_records_dates(const gnnqc_cml_records* r, int64_t i) {
 }
 
 void gnnqc_cml_records_free(gnnqc_cml_records* r) { delete r; }
+
+int gnnqc_tfrecord_read_soilnet(const char* path, const char* normalization, gnnqc_soilnet_records** out) {
+  if (!path || !out) return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_tfrecord_read_soilnet: null argument");
+  *out = nullptr;
+  gnnqc_soilnet_records* r = new gnnqc_soilnet_records();
+  try {
+    r->batch.node_off.push_back(0);
+    r->batch.edge_off.push_back(0);
+    const std::string mode = normalization ? normalization : "scale_range";
+    for (const std::string& rec : gnnqc::read_records(path, true))
+      gnnqc::append_soil_example(gnnqc::parse_sequence_example(rec), mode, &r->batch);
+  } catch (const std::exception& e) {
+    delete r;
+    return gnnqc_internal_fail(GNNQC_ERR_CKPT, e.what());
+  }
+  *out = r;
+  return GNNQC_OK;
+}
+
+int gnnqc_soilnet_records_info(const gnnqc_soilnet_records* r, int64_t* n_windows, int64_t* T, int64_t* n_nodes_total, int64_t* n_edges_total) {
+  if (!r) return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_soilnet_records_info: null handle");
+  if (n_windows) *n_windows = static_cast<int64_t>(r->batch.dates.size());
+  if (T) *T = r->batch.T;
+  if (n_nodes_total) *n_nodes_total = r->batch.node_off.back();
+  if (n_edges_total) *n_edges_total = r->batch.edge_off.back();
+  return GNNQC_OK;
+}
+
+int gnnqc_soilnet_records_copy(const gnnqc_soilnet_records* r, float* features_host, int64_t* edges_host, int32_t* node_off_host,
+                               int64_t* edge_off_host, int64_t* labels_host, int64_t* sensor_ids_host) {
+  if (!r) return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_soilnet_records_copy: null handle");
+  const gnnqc::SoilBatch& b = r->batch;
+  if (features_host) std::memcpy(features_host, b.features.data(), b.features.size() * sizeof(float));
+  if (edges_host) std::memcpy(edges_host, b.edges.data(), b.edges.size() * sizeof(int64_t));
+  if (node_off_host) std::memcpy(node_off_host, b.node_off.data(), b.node_off.size() * sizeof(int32_t));
+  if (edge_off_host) std::memcpy(edge_off_host, b.edge_off.data(), b.edge_off.size() * sizeof(int64_t));
+  if (labels_host) std::memcpy(labels_host, b.labels.data(), b.labels.size() * sizeof(int64_t));
+  if (sensor_ids_host) std::memcpy(sensor_ids_host, b.sensor_ids.data(), b.sensor_ids.size() * sizeof(int64_t));
+  return GNNQC_OK;
+}
+
+const char* gnnqc_soilnet_records_dates(const gnnqc_soilnet_records* r, int64_t i) {
+  return (r && i >= 0 && i < static_cast<int64_t>(r->batch.dates.size())) ? r->batch.dates[static_cast<size_t>(i)].c_str() : "";
+}
+
+void gnnqc_soilnet_records_free(gnnqc_soilnet_records* r) { delete r; }
 
 }  // extern "C"

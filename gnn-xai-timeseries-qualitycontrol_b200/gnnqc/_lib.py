@@ -76,6 +76,11 @@ def _load():
         "gnnqc_cml_records_id": (C.c_char_p, [vp, i64]),
         "gnnqc_cml_records_dates": (C.c_char_p, [vp, i64]),
         "gnnqc_cml_records_free": (None, [vp]),
+        "gnnqc_tfrecord_read_soilnet": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(vp)]),
+        "gnnqc_soilnet_records_info": (C.c_int, [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]),
+        "gnnqc_soilnet_records_copy": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),
+        "gnnqc_soilnet_records_dates": (C.c_char_p, [vp, i64]),
+        "gnnqc_soilnet_records_free": (None, [vp]),
         "gnnqc_ig_cml": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, i32, vp, vp, vp, vp]),
         "gnnqc_train_vector_len": (i64, [vp]),
         "gnnqc_train_moments_cml": (C.c_int, [vp, vp, i64, vp, vp]),

@@ -178,6 +178,22 @@ const char* gnnqc_cml_records_id(const gnnqc_cml_records* r, int64_t i);
 const char* gnnqc_cml_records_dates(const gnnqc_cml_records* r, int64_t i);
 void gnnqc_cml_records_free(gnnqc_cml_records* r);
 
+/* The same for SoilNet files (create_example with ds_type == 'soilnet', :284-341; parse_soilnet_tfrecord_fn
+ * :772-857; prepare_batch_soilnet :861-897): features [sum_b T*N_b, 3] = (moisture, temp, battv) in the
+ * layout of gnnqc_score_soilnet, labels and sensor ids one per (window, sensor) in the order of the scores.
+ * normalization: "scale_range" (default: moisture/60, temp in [-20, 40], battv in [2800, 3600]),
+ * "standarization", "scale", "median" (subtraction only, as in the reference), "rolling_median",
+ * "rolling_median_fractional", "rolling_mean", "none". */
+typedef struct gnnqc_soilnet_records gnnqc_soilnet_records;
+int gnnqc_tfrecord_read_soilnet(const char* path, const char* normalization, gnnqc_soilnet_records** out);
+int gnnqc_soilnet_records_info(const gnnqc_soilnet_records* r, int64_t* n_windows, int64_t* T,
+                               int64_t* n_nodes_total, int64_t* n_edges_total);
+int gnnqc_soilnet_records_copy(const gnnqc_soilnet_records* r, float* features_host, int64_t* edges_host,
+                               int32_t* node_off_host, int64_t* edge_off_host, int64_t* labels_host,
+                               int64_t* sensor_ids_host);
+const char* gnnqc_soilnet_records_dates(const gnnqc_soilnet_records* r, int64_t i);
+void gnnqc_soilnet_records_free(gnnqc_soilnet_records* r);
+
 /* ---- attribution ---------------------------------------------------------------------- */
 
 /* Replaces IntegratedGradientsExplainer._get_gradients_single_batch for the CML GCN model

@@ -9,7 +9,7 @@ from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
 from tensorboard.summary.writer.record_writer import RecordWriter
 
 from gnnqc import GnnqcError
-from gnnqc.tfrecord import read_cml_tfrecord
+from gnnqc.tfrecord import read_cml_tfrecord, read_soilnet_tfrecord
 
 
 def _example_classes():
@@ -156,3 +156,71 @@ def test_corrupt_and_truncated_files_are_rejected(tmp_path):
         read_cml_tfrecord(bad)
     with pytest.raises(GnnqcError):
         read_cml_tfrecord(tmp_path / "missing.tfrec")
+
+
+def make_soil_window(rng, n_nodes, T):
+    """A SoilNet SequenceExample with the schema of create_example(ds_type='soilnet') (reference :284-341)."""
+    raw = {"moisture": rng.uniform(5, 55, size=(n_nodes, T)), "temp": rng.uniform(-10, 35, size=(n_nodes, T)),
+           "battv": rng.uniform(2900, 3500, size=(n_nodes, T))}
+    raw = {k: v.astype(np.float32) for k, v in raw.items()}
+    adj = rng.random((n_nodes, n_nodes)) < 0.4
+    adj |= adj.T | np.eye(n_nodes, dtype=bool)
+    nodes, nbrs = np.nonzero(adj)
+    flags = (rng.random(n_nodes) < 0.3).astype(np.int64)
+    sids = rng.permutation(1000)[:n_nodes]
+    ex = SequenceExample()
+    _ctx(ex, "node_numb", ints=[n_nodes])
+    _ctx(ex, "link_numb", ints=[len(nodes)])
+    _ctx(ex, "dates", strings=["2014-06-01T%02d:%02d:00" % ((15 * t // 60) % 24, (15 * t) % 60) for t in range(T)])
+    for k, v in raw.items():
+        _ctx(ex, k + "_mean", floats=v.mean(axis=1))
+        _ctx(ex, k + "_std", floats=v.std(axis=1))
+        _ctx(ex, k + "_rolling_median", floats=np.median(v, axis=1))
+        _flist(ex, k, v.T, "float")                                   # T features of N floats
+    _flist(ex, "nodes", [[v] for v in nodes], "int")
+    _flist(ex, "neighbours", [[v] for v in nbrs], "int")
+    _flist(ex, "anomaly_flag", [[v] for v in flags], "int")
+    _flist(ex, "sensor_ids", [[v] for v in sids], "int")
+    return ex, raw, np.stack([nodes, nbrs], axis=1), flags, sids
+
+
+def test_soilnet_reader_against_independent_encoders(tmp_path):
+    rng = np.random.default_rng(5)
+    T = 49
+    path = str(tmp_path / "2014-06-01.tfrec")
+    windows = []
+    with open(path, "wb") as f:
+        w = RecordWriter(f)
+        for n_nodes in (6, 11, 4):
+            ex, raw, edges, flags, sids = make_soil_window(rng, n_nodes, T)
+            w.write(ex.SerializeToString())
+            windows.append((n_nodes, raw, edges, flags, sids))
+        w.flush()
+    batch, labels, sensor_ids, dates = read_soilnet_tfrecord(path)
+    assert batch["node_off"].tolist() == [0, 6, 17, 21] and batch["T"] == T and len(dates) == 3 and len(dates[2]) == T
+    no, eo = batch["node_off"].numpy(), batch["edge_off"].numpy()
+    f32 = np.float32
+    for i, (n, raw, edges, flags, sids) in enumerate(windows):
+        want = np.stack([raw["moisture"].T / f32(60), (raw["temp"].T - f32(-20)) / f32(60), (raw["battv"].T - f32(2800)) / f32(800)], axis=-1)
+        got = batch["features"].numpy()[no[i] * T: no[i + 1] * T].reshape(T, n, 3)
+        np.testing.assert_array_equal(got, want)                      # scale_range in float32, like the reference's tf ops
+        np.testing.assert_array_equal(batch["edges"].numpy()[eo[i]: eo[i + 1]], edges)
+        np.testing.assert_array_equal(labels.numpy()[no[i]: no[i + 1]], flags)
+        np.testing.assert_array_equal(sensor_ids.numpy()[no[i]: no[i + 1]], sids)
+    b2, _, _, _ = read_soilnet_tfrecord(path, "standarization")
+    n, raw, _, _, _ = windows[1]
+    v = raw["temp"]
+    want = (v - v.mean(axis=1, dtype=f32)[:, None]) / v.std(axis=1, dtype=f32)[:, None]
+    np.testing.assert_allclose(b2["features"].numpy()[no[1] * T: no[2] * T].reshape(T, n, 3)[:, :, 1], want.T, rtol=1e-5, atol=1e-5)
+    b3, _, _, _ = read_soilnet_tfrecord(path, "rolling_median")
+    np.testing.assert_array_equal(b3["features"].numpy()[: T * 6].reshape(T, 6, 3)[:, :, 0],
+                                  (windows[0][1]["moisture"] - np.median(windows[0][1]["moisture"], axis=1).astype(f32)[:, None]).T)
+    with pytest.raises(GnnqcError):
+        read_soilnet_tfrecord(path, "no_such_mode")
+    with pytest.raises(GnnqcError, match="moisture"):
+        cml = tmp_path / "cml.tfrec"
+        with open(cml, "wb") as f:
+            w = RecordWriter(f)
+            w.write(make_window(rng, 4, 30, 1, 0)[0].SerializeToString())
+            w.flush()
+        read_soilnet_tfrecord(cml)
