@@ -17,7 +17,7 @@ NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 ARCH = ["-gencode", "arch=compute_100a,code=sm_100a"]
 COMMON = ["-O3", "-std=c++17", "-lineinfo", "-Xcompiler", "-fPIC,-Wall", "--expt-relaxed-constexpr"]
 
-SOURCES = ["tf_bundle.cc", "model_spec.cc", "device_model.cu", "capi.cu", "fma_probe.cu", "no_alloc.cu", "ig.cu", "soilnet.cu", "train.cu", "series.cu", "tfrecord.cc", "umma_selftest.cu", "lstm_tc.cu", "lstm_tc_bwd.cu", "host_scoring.cu", "metrics.cu"]
+SOURCES = ["tf_bundle.cc", "model_spec.cc", "device_model.cu", "capi.cu", "fma_probe.cu", "no_alloc.cu", "ig.cu", "soilnet.cu", "train.cu", "series.cu", "tfrecord.cc", "umma_selftest.cu", "lstm_tc.cu", "lstm_tc_bwd.cu", "host_scoring.cu", "metrics.cu", "soil_series.cu"]
 
 
 def _newer(src_list, target):

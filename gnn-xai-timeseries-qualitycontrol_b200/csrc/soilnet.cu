@@ -17,6 +17,7 @@
 
 #include "device_model.cuh"
 #include "frontend.cuh"
+#include "soil_frontend.cuh"
 
 namespace gnnqc {
 namespace {
@@ -100,45 +101,16 @@ __global__ void __launch_bounds__(256) soil_frontend_kernel(const float* __restr
   for (int dt = 0; dt < 8; ++dt) {
     const int t = t0 + dt;
     if (t >= t_run) break;
-    // prelu(z) = k1*z + k2*|z| (k1 = (1+alpha)/2, k2 = (1-alpha)/2) and z is affine in the three features, so the
-    // neighbour sum needs |z| per (edge, channel) only: z two channels at a time (fma.rn.f32x2), one add with |z|
-    // as operand modifier; the linear part closes from the three feature sums.
-    float sabs[kGcnChannelsDev];
-#pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) sabs[c] = 0.f;
-    float s0 = 0.f, s1 = 0.f, s2 = 0.f;
+    SoilAcc acc;   // soil_frontend.cuh
     const float* row = feat + (static_cast<long long>(n0) * T + static_cast<long long>(t) * nn) * 3;
     for (int e = 0; e < d; ++e) {
       const float* v = row + 3 * __ldg(nbr + rp + e);
-      const float v0 = __ldg(v), v1 = __ldg(v + 1), v2 = __ldg(v + 2);
-      s0 += v0; s1 += v1; s2 += v2;
-      unsigned long long x0, x1, x2;
-      asm("mov.b64 %0, {%1, %1};" : "=l"(x0) : "f"(v0));
-      asm("mov.b64 %0, {%1, %1};" : "=l"(x1) : "f"(v1));
-      asm("mov.b64 %0, {%1, %1};" : "=l"(x2) : "f"(v2));
-#pragma unroll
-      for (int c = 0; c < kGcnChannelsDev; c += 2) {
-        unsigned long long z, a0, a1, a2;
-        asm("mov.b64 %0, {%1, %2};" : "=l"(z) : "f"(p.c[c]), "f"(p.c[c + 1]));
-        asm("mov.b64 %0, {%1, %2};" : "=l"(a0) : "f"(p.a[0][c]), "f"(p.a[0][c + 1]));
-        asm("mov.b64 %0, {%1, %2};" : "=l"(a1) : "f"(p.a[1][c]), "f"(p.a[1][c + 1]));
-        asm("mov.b64 %0, {%1, %2};" : "=l"(a2) : "f"(p.a[2][c]), "f"(p.a[2][c + 1]));
-        asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(z) : "l"(x2), "l"(a2));
-        asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(z) : "l"(x1), "l"(a1));
-        asm("fma.rn.f32x2 %0, %1, %2, %0;" : "+l"(z) : "l"(x0), "l"(a0));
-        float z0, z1;
-        asm("mov.b64 {%0, %1}, %2;" : "=f"(z0), "=f"(z1) : "l"(z));
-        sabs[c] += fabsf(z0);
-        sabs[c + 1] += fabsf(z1);
-      }
+      acc.add(p, __ldg(v), __ldg(v + 1), __ldg(v + 2));
     }
     float* o = out + ((tile * t_run + t) * CH) * kTile + b;
     const float fd = static_cast<float>(d);
 #pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) {
-      const float lin = fmaf(p.a[0][c], s0, fmaf(p.a[1][c], s1, fmaf(p.a[2][c], s2, p.c[c] * fd)));
-      o[c * kTile] = fmaf(0.5f * (1.f + p.alpha[c]), lin, 0.5f * (1.f - p.alpha[c]) * sabs[c]) * inv;
-    }
+    for (int c = 0; c < kGcnChannelsDev; ++c) o[c * kTile] = acc.mean(p, c, fd, inv);
     const float* own = row + 3 * me;
     o[16 * kTile] = live ? __ldg(own) : 0.f;
     o[17 * kTile] = live ? __ldg(own + 1) : 0.f;

@@ -70,6 +70,9 @@ def _load():
         "gnnqc_series_update": (C.c_int, [vp, i64, i64, vp, vp]),
         "gnnqc_series_free": (None, [vp]),
         "gnnqc_score_cml_series": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, vp, vp, vp]),
+        "gnnqc_soil_series_create": (C.c_int, [C.c_int, vp, vp, i64, i64, vp, C.POINTER(vp)]),
+        "gnnqc_soil_series_free": (None, [vp]),
+        "gnnqc_score_soilnet_series": (C.c_int, [vp, vp, vp, i64, i32, i32, vp, vp, vp, vp, vp]),
         "gnnqc_tfrecord_read_cml": (C.c_int, [C.c_char_p, C.c_char_p, C.POINTER(vp)]),
         "gnnqc_cml_records_info": (C.c_int, [vp, C.POINTER(i64), C.POINTER(i64), C.POINTER(i64), C.POINTER(i64)]),
         "gnnqc_cml_records_copy": (C.c_int, [vp, vp, vp, vp, vp, vp, vp]),

@@ -59,3 +59,53 @@ class CmlSeries:
             self.close()
         except Exception:
             pass
+
+
+def soilnet_adjacency(dist, depth_diff, max_distance, max_depth):
+    """The reference's SoilNet adjacency over the whole network (libs/preprocessing_functions.py:474-477)."""
+    dist, depth_diff = np.asarray(dist), np.asarray(depth_diff)
+    return (((dist <= max_distance) & (depth_diff == 0)) | ((dist == 0) & (depth_diff <= max_depth))).astype(np.uint8)
+
+
+class SoilSeries:
+    """Resident SoilNet network: raw float32 [n_sensors, n_times, 3] (moisture, temp, battv; NaN = missing),
+    target float32 [n_sensors, n_times] (NaN = no label), adjacency uint8 [n_sensors, n_sensors]."""
+
+    def __init__(self, raw, target, adjacency, device=0):
+        raw = np.ascontiguousarray(raw, dtype=np.float32)
+        target = np.ascontiguousarray(target, dtype=np.float32)
+        adjacency = np.ascontiguousarray(adjacency, dtype=np.uint8)
+        if raw.ndim != 3 or raw.shape[2] != 3 or target.shape != raw.shape[:2] or adjacency.shape != (raw.shape[0], raw.shape[0]):
+            raise ValueError("expected raw [S, Tt, 3], target [S, Tt], adjacency [S, S]")
+        self.n_sensors, self.n_times, self.device = raw.shape[0], raw.shape[1], int(device)
+        h = C.c_void_p()
+        check(lib.gnnqc_soil_series_create(self.device, raw.ctypes.data, target.ctypes.data, self.n_sensors, self.n_times,
+                                           adjacency.ctypes.data, C.byref(h)))
+        self._h = h
+
+    def score(self, model, t_anom, steps_before=240, steps_after=96, norm=None):
+        """t_anom: cuda int32 [B].  Returns (scores [B, n_sensors] with NaN for dropped sensors, valid uint8 [B, n_sensors])."""
+        import torch
+        t_anom = t_anom.to(torch.int32).contiguous()
+        B = t_anom.numel()
+        scores = torch.empty((B, self.n_sensors), dtype=torch.float32, device=t_anom.device)
+        valid = torch.empty((B, self.n_sensors), dtype=torch.uint8, device=t_anom.device)
+        sub = div = None
+        if norm is not None:
+            sub = np.ascontiguousarray(norm[0], np.float32)
+            div = np.ascontiguousarray(norm[1], np.float32)
+        check(lib.gnnqc_score_soilnet_series(model._h, self._h, t_anom.data_ptr(), B, int(steps_before), int(steps_after),
+                                             sub.ctypes.data if sub is not None else None, div.ctypes.data if div is not None else None,
+                                             scores.data_ptr(), valid.data_ptr(), torch.cuda.current_stream(t_anom.device).cuda_stream))
+        return scores, valid
+
+    def close(self):
+        if self._h:
+            lib.gnnqc_soil_series_free(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

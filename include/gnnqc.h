@@ -157,6 +157,29 @@ int gnnqc_score_cml_series(gnnqc_model* m, const gnnqc_series* series, const int
                            const int32_t* t_anom_dev, int64_t B, int32_t timestep_before,
                            int32_t timestep_after, float* scores_dev, int32_t* n_nodes_dev, void* stream);
 
+/* The same for SoilNet (create_tfrecords_dataset's soilnet branch, libs/preprocessing_functions.py:418-480;
+ * parse_soilnet_tfrecord_fn :772-857; prepare_batch_soilnet :861-897): one window per date over ALL sensors.
+ * gnnqc_soil_series_create copies to `device`:
+ *   raw_host     f32 [n_sensors, n_times, 3]  moisture, temp, battv (NaN = missing sample)
+ *   target_host  f32 [n_sensors, n_times]     anomaly flag (NaN = no label: the sensor is left out of the
+ *                                             windows dated there, :461-464)
+ *   adjacency_host u8 [n_sensors, n_sensors]  the reference's rule over the whole network,
+ *       (distance <= max_sample_distance & depth difference == 0) | (distance == 0 & depth difference <=
+ *       max_neighbour_depth) (:474-477); row = receiving sensor.
+ * gnnqc_score_soilnet_series: t_anom_dev i32 [B] time indices -> scores_dev f32 [B, n_sensors]; a sensor the
+ * reference drops from a window (no label at the date, or a NaN in one of its features inside the window), and
+ * every sensor of a window that does not fit the series, gets NaN.  The window spans steps_before samples
+ * before and steps_after after the date.  norm_sub3_host / norm_div3_host (both or neither): x -> (x - sub) /
+ * div per feature; NULL = 'scale_range'.  valid_dev (optional) u8 [B, n_sensors]. */
+typedef struct gnnqc_soil_series gnnqc_soil_series;
+int gnnqc_soil_series_create(int device, const float* raw_host, const float* target_host, int64_t n_sensors,
+                             int64_t n_times, const uint8_t* adjacency_host, gnnqc_soil_series** out);
+void gnnqc_soil_series_free(gnnqc_soil_series* s);
+int gnnqc_score_soilnet_series(gnnqc_model* m, const gnnqc_soil_series* series, const int32_t* t_anom_dev,
+                               int64_t B, int32_t steps_before, int32_t steps_after,
+                               const float* norm_sub3_host, const float* norm_div3_host, float* scores_dev,
+                               uint8_t* valid_dev, void* stream);
+
 /* ---- reading the reference's TFRecord window files (host only) -------------------------------- */
 
 /* Replaces tf.data.TFRecordDataset + parse_cml_tfrecord_fn + batch + prepare_batch_cml for one file

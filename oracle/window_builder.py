@@ -53,3 +53,35 @@ def materialise_windows(raw, rmed, nbr_off, nbr_idx, edge_off, edges, targets, t
                  "edges": np.concatenate(all_edges).astype(np.int64).reshape(-1, 2), "node_off": np.asarray(node_off, np.int32),
                  "edge_off": np.asarray(eoff, np.int64), "T": T}
     return batch, np.asarray(kept), np.asarray(counts)
+
+
+def materialise_soilnet_windows(raw, target, adjacency, t_anom, before, after, sub=(0.0, -20.0, 2800.0), div=(60.0, 60.0, 800.0)):
+    """SoilNet windows as create_tfrecords_dataset builds them (reference libs/preprocessing_functions.py:449-480)
+    and parse_soilnet_tfrecord_fn normalises them (:825-832, 'scale_range' by default), in the offsets layout of
+    gnnqc_score_soilnet.  raw [S, Tt, 3], target [S, Tt] (NaN = no label), adjacency [S, S] bool.
+    Returns (batch dict, kept): kept[i] = global sensor ids of window i (None for a window that does not fit)."""
+    raw = np.asarray(raw, np.float32)
+    S, Tt, _ = raw.shape
+    sub, div = np.asarray(sub, np.float32), np.asarray(div, np.float32)
+    feats, edges, node_off, edge_off, kept = [], [], [0], [0], []
+    for ta in t_anom:
+        t0, t1 = int(ta) - before, int(ta) + after
+        if t0 < 0 or t1 >= Tt:
+            kept.append(None)
+            node_off.append(node_off[-1])
+            edge_off.append(edge_off[-1])
+            continue
+        win = raw[:, t0:t1 + 1]                                            # [S, T, 3]
+        ok = ~np.isnan(target[:, int(ta)]) & ~np.isnan(win).any(axis=(1, 2))
+        ids = np.nonzero(ok)[0]
+        kept.append(ids)
+        x = (win[ids] - sub) / div                                         # float32 arithmetic, like the tf ops
+        feats.append(np.transpose(x, (1, 0, 2)).reshape(-1, 3))            # rows in (timestep, node) order
+        r, c = np.nonzero(np.asarray(adjacency, bool)[np.ix_(ids, ids)])
+        edges.append(np.stack([r, c], axis=1))
+        node_off.append(node_off[-1] + len(ids))
+        edge_off.append(edge_off[-1] + len(r))
+    batch = {"features": np.concatenate(feats).astype(np.float32) if feats else np.zeros((0, 3), np.float32),
+             "edges": np.concatenate(edges).astype(np.int64).reshape(-1, 2) if edges else np.zeros((0, 2), np.int64),
+             "node_off": np.asarray(node_off, np.int32), "edge_off": np.asarray(edge_off, np.int64)}
+    return batch, kept

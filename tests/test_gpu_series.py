@@ -65,3 +65,47 @@ def test_series_scoring_matches_materialised_windows():
     finally:
         series.close()
         m.close()
+
+
+def test_soilnet_series_scoring_matches_materialised_windows():
+    """gnnqc_score_soilnet_series == build the windows on the host as the reference does, then gnnqc_score_soilnet."""
+    from gnnqc.series import SoilSeries, soilnet_adjacency
+    rng = np.random.default_rng(3)
+    S, Tt, before, after = 23, 700, 240, 96                           # T = 337 samples, as model_soilnet expects
+    xy = rng.uniform(0, 60, size=(S // 2 + 1, 2))
+    place = rng.integers(0, len(xy), size=S)                           # several sensors (depths) per location
+    depth = rng.choice([5.0, 20.0, 50.0], size=S)
+    dist = np.linalg.norm(xy[place][:, None] - xy[place][None], axis=-1)
+    adjacency = soilnet_adjacency(dist, np.abs(depth[:, None] - depth[None]), 25.0, 45.0)
+    raw = np.stack([rng.uniform(5, 55, size=(S, Tt)), rng.uniform(-10, 35, size=(S, Tt)), rng.uniform(2900, 3500, size=(S, Tt))], axis=-1)
+    raw = raw.astype(np.float32)
+    raw[rng.random((S, Tt)) < 0.0015] = np.nan                          # sporadic gaps
+    raw[4, 300:420, 1] = np.nan                                        # a long gap in one feature of one sensor
+    target = (rng.random((S, Tt)) < 0.1).astype(np.float32)
+    target[rng.random((S, Tt)) < 0.02] = np.nan                        # unlabelled samples
+    target[7, :] = np.nan                                              # a sensor that never has a label
+    t_anom = np.concatenate([rng.integers(before, Tt - after, size=40), [before - 1, Tt - after, before, Tt - after - 1]]).astype(np.int32)
+    m = NativeModel.load(os.path.join(MODELS, "model_soilnet"), device=0)
+    series = SoilSeries(raw, target, adjacency, device=0)
+    try:
+        scores, valid = series.score(m, torch.from_numpy(t_anom).cuda(), before, after)
+        scores, valid = scores.cpu().numpy(), valid.cpu().numpy().astype(bool)
+        batch, kept = WB.materialise_soilnet_windows(raw, target, adjacency, t_anom, before, after)
+        b = {k: torch.from_numpy(v).cuda() for k, v in batch.items()}
+        want = m.score_soilnet(b["features"], b["edges"], b["node_off"], b["edge_off"], before + after + 1).cpu().numpy()
+        no = batch["node_off"]
+        dropped_some = False
+        for i, ids in enumerate(kept):
+            if ids is None:                                            # window does not fit the series
+                assert not valid[i].any() and np.isnan(scores[i]).all()
+                continue
+            mask = np.zeros(S, bool)
+            mask[ids] = True
+            dropped_some |= not mask.all()
+            np.testing.assert_array_equal(valid[i], mask)
+            np.testing.assert_array_equal(scores[i][ids], want[no[i]:no[i + 1]])   # same arithmetic, same order: bit-identical
+            assert np.isnan(scores[i][~mask]).all()
+        assert dropped_some and sum(k is None for k in kept) == 2
+    finally:
+        series.close()
+        m.close()
