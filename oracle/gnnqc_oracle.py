@@ -8,8 +8,11 @@ PARITY UNPINNED: the reference (timohouben/GNN-XAI-TimeSeries-QualityControl) is
 installable in the build image, and the example datasets are missing from the mount.  This file
 is therefore a restatement of the reference's arithmetic from its source and from the layer
 configs recorded in model_*/keras_metadata.pb; it has never been compared with TF output.
-What *is* pinned: the weights (read from the reference's own checkpoints), and internal
-consistency (fp32 vs fp64, a second independent NumPy implementation, finite differences, the
+What *is* pinned (tests/test_reference_pins.py): the weights (parsed from the reference's own
+checkpoints by oracle/ckpt_reader.py, independently of the product's reader, and hashed against the
+original bytes), every layer hyper-parameter and the layer order / inter-layer shapes against the
+Keras-serialised configs in model_*/keras_metadata.pb (tests/golden/keras_layer_configs.json), and
+internal consistency (fp32 vs fp64, a second independent NumPy implementation, finite differences, the
 IG completeness axiom) - see tests/test_oracle.py.
 
 Restated (reference file:line):
@@ -37,6 +40,19 @@ POOL = 3           # MaxPooling1D pool_size = strides = 3, padding 'valid'
 
 def to_torch_weights(named, dtype=torch.float32):
     return {k: torch.as_tensor(np.asarray(v)).to(dtype) for k, v in named.items()}
+
+
+def load_named(savedmodel_dir):
+    """Weights of a reference SavedModel directory as {attribute path: float32 ndarray}, read by the
+    oracle's OWN checkpoint parser (oracle/ckpt_reader.py) - never through libgnnqc's reader, so a
+    mapping error in either reader shows up as a parity failure instead of cancelling out."""
+    import ckpt_reader
+
+    return ckpt_reader.load_named(savedmodel_dir)[0]
+
+
+def load_weights(savedmodel_dir, dtype=torch.float32):
+    return to_torch_weights(load_named(savedmodel_dir), dtype)
 
 
 # ---- GeneralConv (spektral 1.3.0), inference mode ------------------------------------------------

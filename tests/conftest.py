@@ -28,5 +28,13 @@ def models_dir():
     return MODELS
 
 
+def oracle_named(name):
+    """Shipped weights for the ORACLE side of a parity test: parsed by oracle/ckpt_reader.py, not by the
+    library under test."""
+    import gnnqc_oracle
+
+    return gnnqc_oracle.load_named(os.path.join(MODELS, name))
+
+
 def model_path(name):
     return os.path.join(MODELS, name)

@@ -38,7 +38,7 @@ def strip_models():
 
 
 def golden_cml():
-    named = NativeModel.load(os.path.join(REF, "model_cml"), device=None).named_params()
+    named = O.load_named(os.path.join(REF, "model_cml"))
     w = O.to_torch_weights(named, torch.float64)
     b = synth.make_cml_batch(12, seed=44, ragged=True)
     feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(b), 2)
@@ -49,13 +49,13 @@ def golden_cml():
         node_off=b["node_off"].numpy(), edge_off=b["edge_off"].numpy(), scores=p.reshape(-1).numpy())
     print("cml gcn", p.reshape(-1).numpy())
 
-    nb = NativeModel.load(os.path.join(REF, "model_cml_baseline"), device=None).named_params()
+    nb = O.load_named(os.path.join(REF, "model_cml_baseline"))
     x = synth.make_seq_batch(24, 2, 181, seed=45)
     pb = O.baseline_forward(x.double(), O.to_torch_weights(nb, torch.float64))
     np.savez_compressed(os.path.join(OUT, "cml_baseline_scores.npz"), x=x.numpy(), scores=pb.reshape(-1).numpy())
     print("cml baseline", pb.reshape(-1).numpy())
 
-    ns = NativeModel.load(os.path.join(REF, "model_soilnet_baseline"), device=None).named_params()
+    ns = O.load_named(os.path.join(REF, "model_soilnet_baseline"))
     xs = synth.make_seq_batch(10, 3, 337, seed=46)
     ps = O.baseline_forward(xs.double(), O.to_torch_weights(ns, torch.float64))
     np.savez_compressed(os.path.join(OUT, "soilnet_baseline_scores.npz"), x=xs.numpy(), scores=ps.reshape(-1).numpy())

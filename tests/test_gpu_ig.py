@@ -8,7 +8,7 @@ import pytest
 import torch
 
 import gnnqc_oracle as O
-from conftest import MODELS
+from conftest import MODELS, oracle_named
 from gnnqc import NativeModel, synth
 
 pytestmark = pytest.mark.gpu
@@ -29,7 +29,7 @@ def run_gpu(model, batch, m_steps):
 
 def run_oracle(model, batch, m_steps):
     feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 2)
-    w = O.to_torch_weights(model.named_params(), torch.float64)
+    w = O.to_torch_weights(oracle_named("model_cml"), torch.float64)
     af, aa, p = O.integrated_gradients_cml(torch.tensor(feat).double(), batch["anom"].double(), torch.tensor(idx), torch.tensor(samp), w, m_steps=m_steps)
     return af.numpy(), aa.numpy(), p.numpy()
 

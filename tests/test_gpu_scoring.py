@@ -7,7 +7,7 @@ import pytest
 import torch
 
 import gnnqc_oracle as O
-from conftest import GOLDEN, MODELS
+from conftest import GOLDEN, MODELS, oracle_named
 from gnnqc import NativeModel, synth
 
 pytestmark = pytest.mark.gpu
@@ -67,14 +67,14 @@ def test_cml_gcn_golden(models):
 @pytest.mark.parametrize("n,ragged", [(1, False), (63, True), (65, False), (200, True)])
 def test_cml_gcn_vs_oracle(models, n, ragged):
     batch = synth.make_cml_batch(n, seed=100 + n, ragged=ragged)
-    want = oracle_cml(models["model_cml"].named_params(), batch)
+    want = oracle_cml(oracle_named("model_cml"), batch)
     close(score_cml(models["model_cml"], batch), want)
 
 
 @pytest.mark.parametrize("model,F,T,n", [("model_cml_baseline", 2, 181, 130), ("model_soilnet_baseline", 3, 337, 70)])
 def test_baseline_vs_oracle(models, model, F, T, n):
     x = synth.make_seq_batch(n, F, T, seed=5)
-    w = O.to_torch_weights(models[model].named_params(), torch.float32)
+    w = O.to_torch_weights(oracle_named(model), torch.float32)
     want = O.baseline_forward(x, w).reshape(-1).numpy()
     close(models[model].score_seq(x.cuda()).cpu().numpy(), want)
 
@@ -92,7 +92,7 @@ def test_soilnet_gcn_vs_oracle(models, n, nodes, ragged):
     batch = synth.make_soilnet_batch(n, seed=31 + n, n_nodes=nodes, ragged=ragged, min_nodes=7)
     b = cuda(batch)
     got = models["model_soilnet"].score_soilnet(b["features"], b["edges"], b["node_off"], b["edge_off"], batch["T"]).cpu().numpy()
-    close(got, oracle_soilnet(models["model_soilnet"].named_params(), batch))
+    close(got, oracle_soilnet(oracle_named("model_soilnet"), batch))
 
 
 def test_soilnet_edge_order_does_not_matter(models):
@@ -115,7 +115,7 @@ def test_other_sequence_lengths(models):
     """T is a runtime argument (the reference bakes it into the graph)."""
     for T in (27, 100, 243):
         x = synth.make_seq_batch(9, 2, T, seed=T)
-        w = O.to_torch_weights(models["model_cml_baseline"].named_params(), torch.float32)
+        w = O.to_torch_weights(oracle_named("model_cml_baseline"), torch.float32)
         close(models["model_cml_baseline"].score_seq(x.cuda()).cpu().numpy(), O.baseline_forward(x, w).reshape(-1).numpy())
     from gnnqc import GnnqcError
     with pytest.raises(GnnqcError, match="too short"):
@@ -177,13 +177,13 @@ def test_isolated_node_and_duplicate_edges(models):
     edges = torch.tensor([[0, 0], [0, 1], [0, 1], [1, 0], [2, 3], [2, 2]], dtype=torch.int64)  # node 3 receives nothing
     batch = {"features": x.reshape(-1, 2), "anom": x[:, :, 0].contiguous(), "edges": edges,
              "node_off": torch.tensor([0, n], dtype=torch.int32), "edge_off": torch.tensor([0, len(edges)], dtype=torch.int64), "T": T}
-    close(score_cml(m, batch), oracle_cml(m.named_params(), batch))
+    close(score_cml(m, batch), oracle_cml(oracle_named("model_cml"), batch))
 
 
 def test_large_graph_uses_general_coefficient_path(models):
     """More than 32 nodes per window: the node-coefficient kernel's global-scratch path."""
     batch = synth.make_cml_batch(5, seed=77, n_nodes=40)
-    close(score_cml(models["model_cml"], batch), oracle_cml(models["model_cml"].named_params(), batch))
+    close(score_cml(models["model_cml"], batch), oracle_cml(oracle_named("model_cml"), batch))
 
 
 def test_roc_auc_matches_oracle_to_3_decimals(models):
@@ -193,7 +193,7 @@ def test_roc_auc_matches_oracle_to_3_decimals(models):
     if labels.sum() == 0:
         labels[::7] = 1
     got = score_cml(models["model_cml"], batch)
-    want = oracle_cml(models["model_cml"].named_params(), batch)
+    want = oracle_cml(oracle_named("model_cml"), batch)
     assert round(roc_auc_score(labels, got), 3) == round(roc_auc_score(labels, want), 3)
 
 

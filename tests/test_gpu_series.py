@@ -51,7 +51,7 @@ def test_series_scoring_matches_materialised_windows():
         assert np.array_equal(got[kept], ref)                                      # same arithmetic, same order
         tb = {k: (torch.as_tensor(v) if k != "T" else v) for k, v in batch.items()}
         feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(tb), 2)
-        w = O.to_torch_weights(m.named_params(), torch.float32)
+        w = O.load_weights(os.path.join(MODELS, "model_cml"), torch.float32)
         oracle = O.gcn_forward_cml(torch.tensor(feat), tb["anom"], torch.tensor(idx), torch.tensor(samp), w).reshape(-1).numpy()
         assert np.all(np.abs(got[kept] - oracle) <= 1e-4 + 1e-4 * np.abs(oracle))
         # streaming update: overwrite a range, scores of windows that do not touch it are unchanged

@@ -55,7 +55,7 @@ def test_gcn_gradients_match_oracle(n, ragged):
         m.train_apply(fin, mom, 1e-4)      # closes the BN backward: `fin` now holds the GeneralConv gradients too
         got, loss = split_rvec(m, fin)
         feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 2)
-        named = NativeModel.load(os.path.join(MODELS, "model_cml"), device=None).named_params()
+        named = O.load_named(os.path.join(MODELS, "model_cml"))
         oloss, ograds, mu, var = O.train_grads_cml(torch.tensor(feat), batch["anom"], torch.tensor(idx), torch.tensor(samp), labels, named)
         assert abs(loss - oloss.item()) <= 1e-5 * abs(oloss.item()) + 1e-7
         check_grads(got, ograds, skip=("gcn_layer/bias",))
@@ -77,7 +77,7 @@ def test_baseline_gradients_and_adam_step():
         before = m.get_params()
         rvec = m.train_grads_seq(x.cuda(), labels.cuda())
         got, loss = split_rvec(m, rvec)
-        named = NativeModel.load(os.path.join(MODELS, "model_cml_baseline"), device=None).named_params()
+        named = O.load_named(os.path.join(MODELS, "model_cml_baseline"))
         oloss, ograds = O.train_grads_baseline(x, labels, named)
         assert abs(loss - oloss.item()) <= 1e-5 * abs(oloss.item()) + 1e-7
         check_grads(got, ograds)

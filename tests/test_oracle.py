@@ -11,7 +11,7 @@ from gnnqc import NativeModel, synth
 
 
 def _named(name):
-    return NativeModel.load(os.path.join(MODELS, name), device=None).named_params()
+    return O.load_named(os.path.join(MODELS, name))
 
 
 def _cml_inputs(g):
