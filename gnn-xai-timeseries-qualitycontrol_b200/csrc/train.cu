@@ -181,6 +181,10 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   TrainState* ts = train_state();
   // GNNQC_TRAIN_TC=0: forward/backward on the fp32 CUDA-core kernels (A/B)
   static const bool train_tc = [] { const char* e = std::getenv("GNNQC_TRAIN_TC"); return !(e && std::strcmp(e, "0") == 0); }();
+  // GNNQC_TRAIN_TC_BWD_MIN_TILES: smallest step (in 64-window tiles) whose backward runs on the tensor-core kernels
+  // (default 2 per SM); read per call so a test can send a small batch down that path
+  long long tc_bwd_min_tiles = 2LL * sm_count;
+  if (const char* e = std::getenv("GNNQC_TRAIN_TC_BWD_MIN_TILES")) tc_bwd_min_tiles = std::max(1LL, std::atoll(e));
   StackPlan plan(s, T);
   const int L = s.n_lstm;
   const long long nt = (B + kTile - 1) / kTile;
@@ -267,7 +271,7 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     a.in = dy; a.out = (l % 2 == 0) ? F(o_g0) : F(o_g1); a.w = d_packed_t + packed_t_off[l]; a.save = F(o_save[l]);
     // the tensor-core backward needs many tile pairs in flight to cover its per-chunk MMA round trips; a small
     // training batch (4,096 windows = 32 pairs) is faster on the fp32 kernel
-    a.wtc = (train_tc && nt >= 2LL * sm_count) ? d_packed_tcb + packed_tcb_off[l] : nullptr;
+    a.wtc = (train_tc && nt >= tc_bwd_min_tiles) ? d_packed_tcb + packed_tcb_off[l] : nullptr;
     a.amax = pool ? F(o_amax[l]) : nullptr; a.dz = F(o_dz[l]);
     a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
     mark_begin(kBwd[l], st);

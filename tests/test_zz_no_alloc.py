@@ -4,15 +4,16 @@ path: fixed-budget real-time loops, processes whose device memory belongs to ano
 Collected last on purpose (file name), so a `-x` run has already exercised everything else when
 it gets here.  Compares the no-allocation variant with gnnqc_score_seq through the C ABI on two
 calls in a row - the second with a different batch, so contents the first call left in the shared
-built-in scratch array cannot leak into the result - and checks that an oversized call is
-refused with a message that names the limit."""
+built-in scratch array cannot leak into the result - and with the CPU oracle directly, and checks
+that an oversized call is refused with a message that names the limit."""
 import os
 
 import numpy as np
 import pytest
 import torch
 
-from conftest import MODELS
+import gnnqc_oracle as O
+from conftest import MODELS, oracle_named
 from gnnqc import GnnqcError, NativeModel, synth
 
 pytestmark = pytest.mark.gpu
@@ -41,6 +42,7 @@ def test_noalloc_matches_score_seq_twice_in_a_row(name, F, T, sizes):
             if call > 0:   # the very first use makes the driver load the module that holds the array
                 assert torch.cuda.mem_get_info()[0] >= free_before, "the no-allocation entry point allocated device memory"
             _close(out, want)
+            _close(out, O.baseline_forward(x.cpu(), O.to_torch_weights(oracle_named(name), torch.float32)).reshape(-1))
     finally:
         m.close()
 
