@@ -27,7 +27,13 @@ def _newer(src_list, target):
     return any(os.path.getmtime(s) > t for s in src_list)
 
 
-def build(verbose=False, force=False):
+def build(verbose=False, force=False, variant=None, defines=()):
+    """variant / defines: an A/B build (e.g. variant="p3", defines=["-DGNNQC_POLY_EXPS=3"]) lands in
+    gnnqc/libgnnqc_<variant>.so with its own object directory; GNNQC_LIB selects it at import."""
+    global OBJ_DIR, OUT
+    if variant:
+        OBJ_DIR = os.path.join(CSRC, "build", "variant_" + variant)
+        OUT = os.path.join(HERE, "gnnqc", "libgnnqc_%s.so" % variant)
     os.makedirs(OBJ_DIR, exist_ok=True)
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".h", ".cuh"))]
     headers.append(os.path.normpath(os.path.join(HERE, "..", "include", "gnnqc.h")))
@@ -39,7 +45,7 @@ def build(verbose=False, force=False):
         obj = os.path.join(OBJ_DIR, os.path.splitext(name)[0] + ".o")
         objs.append(obj)
         if force or _newer([src] + headers, obj):
-            cmd = [NVCC] + ARCH + COMMON + ["-Xptxas", "-v", "-c", src, "-o", obj]
+            cmd = [NVCC] + ARCH + COMMON + list(defines) + ["-Xptxas", "-v", "-c", src, "-o", obj]
             res = subprocess.run(cmd, capture_output=True, text=True)
             with open(obj + ".log", "w") as f:
                 f.write(" ".join(cmd) + "\n" + res.stdout + res.stderr)
@@ -57,4 +63,5 @@ def build(verbose=False, force=False):
 
 
 if __name__ == "__main__":
-    print(build(verbose="-v" in sys.argv, force="-f" in sys.argv))
+    var = next((a.split("=", 1)[1] for a in sys.argv if a.startswith("--variant=")), None)
+    print(build(verbose="-v" in sys.argv, force="-f" in sys.argv, variant=var, defines=[a for a in sys.argv if a.startswith("-D")]))

@@ -1,6 +1,7 @@
 // Host side of the tensor-core LSTM layers (lstm_tc.cuh): weight packing (bf16 hi/lo split, UMMA
 // K-major layout), kernel configuration and launch.
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <algorithm>
 #include <cstdio>
@@ -170,91 +171,90 @@ bool tc_layer_supported(int in, int hid, bool pool, bool last) {
 size_t tc_packed_bytes(int in, int hid) {
   if (tc_is_big(hid)) {
     const int kp = ((in + 7) / 8 * 8 + hid + 15) / 16 * 16;
-    return size_t(hid / 32) * (kp / 16) * 8192 + size_t(4 * hid) * 4;
+    return size_t(hid / 32) * (kp / 16) * 8192 + size_t(hid / 32) * tc_bias_tile_bytes(128);
   }
   const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, n = 4 * hid;
-  return size_t(2) * kp * n * 2 + size_t(n) * 4;
-}
-
-// Gate columns are pre-multiplied by the factor of their exponential (lstm_cell_tc).
-// B_hi | B_lo in [KP/8][N][8] bf16 (row n = Keras gate column, k = [inputs | pad | hidden | pad]), then bias.
-void tc_pack_host(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out) {
-  if (tc_is_big(hid)) {
-    // pieces [chunk of 32 units][K slice of 16]{hi, lo}, each half [2][128][8] bf16 with operand row
-    // n = gate * 32 + unit-in-chunk (lstm_tc_big.cuh), then the bias in Keras column order.
-    const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, kc_n = kp / 16, n4 = 4 * hid;
-    for (int c = 0; c < hid / 32; ++c)
-      for (int kc = 0; kc < kc_n; ++kc) {
-        __nv_bfloat16* hi = reinterpret_cast<__nv_bfloat16*>(out + (size_t(c) * kc_n + kc) * 8192);
-        __nv_bfloat16* lo = hi + 2048;
-        for (int kk = 0; kk < 16; ++kk)
-          for (int nrow = 0; nrow < 128; ++nrow) {
-            const int k = kc * 16 + kk, col = (nrow / 32) * hid + c * 32 + (nrow % 32);
-            float v = 0.f;
-            if (k < in) v = W[size_t(k) * n4 + col];
-            else if (k >= ip && k < ip + hid) v = U[size_t(k - ip) * n4 + col];
-            v *= tc_gate_scale(nrow / 32);
-            const __nv_bfloat16 h = __float2bfloat16_rn(v);
-            const size_t at = (size_t(kk / 8) * 128 + nrow) * 8 + (kk % 8);
-            hi[at] = h;
-            lo[at] = __float2bfloat16_rn(v - __bfloat162float(h));
-          }
-      }
-    float* bout = reinterpret_cast<float*>(out + size_t(hid / 32) * kc_n * 8192);
-    for (int col = 0; col < n4; ++col) bout[col] = bias[col] * tc_gate_scale(col / hid);
-    return;
-  }
-  const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, n = 4 * hid;
-  __nv_bfloat16* bhi = reinterpret_cast<__nv_bfloat16*>(out);
-  __nv_bfloat16* blo = bhi + size_t(kp) * n;
-  for (int k = 0; k < kp; ++k)
-    for (int col = 0; col < n; ++col) {
-      float v = 0.f;
-      if (k < in) v = W[size_t(k) * n + col];
-      else if (k >= ip && k < ip + hid) v = U[size_t(k - ip) * n + col];
-      v *= tc_gate_scale(col / hid);
-      const __nv_bfloat16 h = __float2bfloat16_rn(v);
-      const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
-      const size_t at = (size_t(k / 8) * n + col) * 8 + (k % 8);
-      bhi[at] = h;
-      blo[at] = l;
-    }
-  float* bout = reinterpret_cast<float*>(out + size_t(2) * kp * n * 2);
-  for (int col = 0; col < n; ++col) bout[col] = bias[col] * tc_gate_scale(col / hid);
+  return size_t(2) * kp * n * 2 + tc_bias_tile_bytes(n);
 }
 
 namespace {
-// Device twin of tc_pack_host (same index maps, same fp32 scaling and bf16 rounding), for the refresh after an optimizer step.
+// One packed value: where the hi and lo halves of the fp16 split go (element index inside the blob, in halfs).
+// Shared by the host packer and its device twin so that the two are bit-identical by construction.
+struct TcSlot { size_t hi, lo; };
+__host__ __device__ inline TcSlot tc_weight_slot(int k, int col, int hid, int kp) {   // col: Keras gate column
+  const int n = 4 * hid;
+  if (hid >= 64) {   // pieces [chunk of 32 units][K slice of 16]{hi, lo}, each half [2][128][8], operand row = gate * 32 + unit-in-chunk
+    const int gate = col / hid, unit = col % hid, c = unit / 32, nrow = gate * 32 + unit % 32, kc = k / 16, kk = k % 16;
+    const size_t base = (size_t(c) * (kp / 16) + kc) * 4096 + (size_t(kk / 8) * 128 + nrow) * 8 + (kk % 8);
+    return {base, base + 2048};
+  }
+  const size_t at = (size_t(k / 8) * n + col) * 8 + (k % 8);   // B_hi | B_lo, each [KP/8][N][8]
+  return {at, size_t(kp) * n + at};
+}
+__host__ __device__ inline TcSlot tc_bias_slot(int col, int hid, int kp) {            // row of the bias tile: k = 0 hi, k = 1 lo
+  const int n = 4 * hid;
+  if (hid >= 64) {
+    const int gate = col / hid, unit = col % hid, c = unit / 32, nrow = gate * 32 + unit % 32;
+    const size_t base = size_t(hid / 32) * (kp / 16) * 4096 + size_t(c) * (tc_bias_tile_bytes(128) / 2) + size_t(nrow) * 8;
+    return {base, base + 1};
+  }
+  const size_t base = size_t(2) * kp * n + size_t(col) * 8;
+  return {base, base + 1};
+}
+__host__ __device__ inline float tc_weight_value(const float* W, const float* U, int k, int col, int in, int hid) {
+  const int ip = (in + 7) / 8 * 8, n = 4 * hid;
+  float v = 0.f;
+  if (k < in) v = W[size_t(k) * n + col];
+  else if (k >= ip && k < ip + hid) v = U[size_t(k - ip) * n + col];
+  return v * tc_gate_scale(col / hid);
+}
+}  // namespace
+
+// Gate columns are pre-multiplied by the factor of their exponential (lstm_cell2).  Weights: fp16 hi / lo of
+// [W ; U] in the UMMA K-major layout (k = [inputs | pad | hidden | pad]); biases: one more operand tile (lstm_tc.cuh).
+void tc_pack_host(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out) {
+  const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, n = 4 * hid;
+  std::memset(out, 0, tc_packed_bytes(in, hid));
+  __half* o = reinterpret_cast<__half*>(out);
+  for (int k = 0; k < kp; ++k)
+    for (int col = 0; col < n; ++col) {
+      const float v = tc_weight_value(W, U, k, col, in, hid);
+      const __half h = __float2half_rn(v);
+      const TcSlot s = tc_weight_slot(k, col, hid, kp);
+      o[s.hi] = h;
+      o[s.lo] = __float2half_rn(v - __half2float(h));
+    }
+  for (int col = 0; col < n; ++col) {
+    const float v = bias[col] * tc_gate_scale(col / hid);
+    const __half h = __float2half_rn(v);
+    const TcSlot s = tc_bias_slot(col, hid, kp);
+    o[s.hi] = h;
+    o[s.lo] = __float2half_rn(v - __half2float(h));
+  }
+}
+
+namespace {
+// Device twin of tc_pack_host (same slot maps, same fp32 scaling and fp16 rounding), for the refresh after an optimizer step.
 __global__ void __launch_bounds__(256) tc_repack_kernel(const float* __restrict__ W, const float* __restrict__ U, const float* __restrict__ bias,
                                                         int in, int hid, unsigned char* __restrict__ out) {
   const int ip = (in + 7) / 8 * 8, kp = (ip + hid + 15) / 16 * 16, n = 4 * hid;
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   const long long n_main = static_cast<long long>(kp) * n;
-  const bool big = hid >= 64;
-  const size_t main_bytes = big ? size_t(hid / 32) * (kp / 16) * 8192 : size_t(2) * kp * n * 2;
+  __half* o = reinterpret_cast<__half*>(out);
   if (i < n_main) {
-    const int k = static_cast<int>(i / n), col = static_cast<int>(i % n);   // col: Keras gate column
-    float v = 0.f;
-    if (k < in) v = W[static_cast<long long>(k) * n + col];
-    else if (k >= ip && k < ip + hid) v = U[static_cast<long long>(k - ip) * n + col];
-    v *= tc_gate_scale(col / hid);
-    const __nv_bfloat16 h = __float2bfloat16_rn(v);
-    const __nv_bfloat16 l = __float2bfloat16_rn(v - __bfloat162float(h));
-    if (big) {
-      const int gate = col / hid, unit = col % hid, c = unit / 32, nrow = gate * 32 + unit % 32, kc = k / 16, kk = k % 16;
-      __nv_bfloat16* hi = reinterpret_cast<__nv_bfloat16*>(out + (static_cast<size_t>(c) * (kp / 16) + kc) * 8192);
-      const size_t at = (static_cast<size_t>(kk / 8) * 128 + nrow) * 8 + (kk % 8);
-      hi[at] = h;
-      hi[2048 + at] = l;
-    } else {
-      __nv_bfloat16* bhi = reinterpret_cast<__nv_bfloat16*>(out);
-      const size_t at = (static_cast<size_t>(k / 8) * n + col) * 8 + (k % 8);
-      bhi[at] = h;
-      bhi[static_cast<size_t>(kp) * n + at] = l;
-    }
+    const int k = static_cast<int>(i / n), col = static_cast<int>(i % n);
+    const float v = tc_weight_value(W, U, k, col, in, hid);
+    const __half h = __float2half_rn(v);
+    const TcSlot s = tc_weight_slot(k, col, hid, kp);
+    o[s.hi] = h;
+    o[s.lo] = __float2half_rn(v - __half2float(h));
   } else if (i < n_main + n) {
     const int col = static_cast<int>(i - n_main);
-    reinterpret_cast<float*>(out + main_bytes)[col] = bias[col] * tc_gate_scale(col / hid);
+    const float v = bias[col] * tc_gate_scale(col / hid);
+    const __half h = __float2half_rn(v);
+    const TcSlot s = tc_bias_slot(col, hid, kp);
+    o[s.hi] = h;
+    o[s.lo] = __float2half_rn(v - __half2float(h));   // the other entries of the bias tile were zeroed when the blob was first packed
   }
 }
 }  // namespace

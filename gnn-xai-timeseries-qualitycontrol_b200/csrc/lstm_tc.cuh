@@ -30,6 +30,7 @@
 // [input channels padded to 8 | hidden units | zero padding to 16].
 #pragma once
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 
 #include <cstdint>
 
@@ -37,6 +38,16 @@
 #include "umma.cuh"
 
 namespace gnnqc {
+
+// Bias through the tensor core: one extra K = 16 MMA per step opens each chain with accumulate = false,
+//   A = the constant "ones" tile (k = 0, 1 hold 1.0), B = the bias tile (k = 0: bias_hi, k = 1: bias_lo),
+// so the accumulators arrive with the bias already added (no shared-memory bias reads, no adds in the cell update).
+constexpr int kOnesTileBytes = 2 * 128 * 16;            // [2 core-matrix columns][128 rows][8] fp16
+__device__ __forceinline__ void fill_ones_tile(unsigned char* dst, int tid, int nthreads) {
+  uint4* d = reinterpret_cast<uint4*>(dst);
+  for (int i = tid; i < 256; i += nthreads) d[i] = (i < 128) ? make_uint4(0x3C003C00u, 0u, 0u, 0u) : make_uint4(0u, 0u, 0u, 0u);
+}
+__host__ __device__ constexpr size_t tc_bias_tile_bytes(int n) { return size_t(2) * n * 16; }   // [2][n][8] fp16
 
 template <int I, int H>
 struct TcCfg {
@@ -51,21 +62,28 @@ struct TcCfg {
   static constexpr int XBYTES = I * kTile * 4;            // one 64-window half of one step
   static constexpr size_t B_BYTES = size_t(KP) * N * 2;   // one of hi / lo
   static constexpr size_t A_BYTES = size_t(KP) * ROWS * 2;
-  static constexpr size_t OFF_BHI = 0, OFF_BLO = B_BYTES, OFF_BIAS = 2 * B_BYTES;
-  static constexpr size_t OFF_GROUPS = OFF_BIAS + size_t(N) * 4;
+  static constexpr size_t BT_BYTES = tc_bias_tile_bytes(N);
   static constexpr size_t G_AHI = 0, G_ALO = A_BYTES, G_X = 2 * A_BYTES;          // within a group's block
   static constexpr size_t GROUP_BYTES = (2 * A_BYTES + size_t(NST) * 2 * XBYTES + 127) / 128 * 128;
+  // 32 -> 32 units is the one shape whose operands leave no room for the two extra tiles: it keeps fp32 biases in
+  // shared memory (rebuilt from the packed hi + lo rows) and adds them in the cell update.
+  static constexpr bool BIAS_MMA = 2 * B_BYTES + BT_BYTES + kOnesTileBytes + GROUPS * GROUP_BYTES + 256 <= 227 * 1024;
+  static constexpr size_t OFF_BHI = 0, OFF_BLO = B_BYTES, OFF_BIAS = 2 * B_BYTES;
+  static constexpr size_t OFF_ONES = OFF_BIAS + (BIAS_MMA ? BT_BYTES : size_t(N) * 4);
+  static constexpr size_t OFF_GROUPS = OFF_ONES + (BIAS_MMA ? kOnesTileBytes : 0);
   static constexpr size_t OFF_BAR = OFF_GROUPS + GROUPS * GROUP_BYTES;
   static constexpr int BARS_PER_GROUP = NST + 2;          // x_full[NST], a_ready, d_full
   static constexpr size_t SMEM_BYTES = OFF_BAR + size_t(GROUPS) * BARS_PER_GROUP * 8 + 16;
-  // packed weights in global memory: B_hi | B_lo | bias (fp32, Keras column order)
-  static constexpr size_t PACKED_BYTES = 2 * B_BYTES + size_t(N) * 4;
+  // packed weights in global memory: B_hi | B_lo | bias tile (fp16 hi / lo rows, Keras column order)
+  static constexpr size_t PACKED_BYTES = 2 * B_BYTES + BT_BYTES;
   static_assert(N <= 256 && (N & (N - 1)) == 0 && TMEM_COLS <= 512, "one MMA covers at most 256 gate columns");
   static_assert(SMEM_BYTES <= 227 * 1024, "operands do not fit in shared memory");
 };
 
-// hi/lo bf16 split of eight floats into two 16-byte operand chunks (two values per cvt).
-__device__ __forceinline__ void split8(const float (&v)[8], uint4& hi, uint4& lo) {
+// hi/lo bf16 split of eight floats into two 16-byte operand chunks (two values per cvt).  bf16 keeps fp32's
+// exponent range, which the BACKWARD kernels need (their operand is dz, down to 1e-10); the forward kernels use
+// the fp16 split below.
+__device__ __forceinline__ void split8_bf16(const float (&v)[8], uint4& hi, uint4& lo) {
   uint32_t h[4], l[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -80,62 +98,120 @@ __device__ __forceinline__ void split8(const float (&v)[8], uint4& hi, uint4& lo
   lo = make_uint4(l[0], l[1], l[2], l[3]);
 }
 
-// Cell update on pre-scaled pre-activations.  The packed weights and biases of the tensor-core
-// layers carry the factors of the exponentials (-log2 e for the i, f, o columns, -2 log2 e for the
-// candidate column, kTcGateScale), so the accumulator plus bias IS the ex2 argument:
+// ---- packed fp32x2 arithmetic (FADD2 / FMUL2 / FFMA2: one issue slot for two lanes) -----------------------------
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pk2(float a, float b) { f32x2 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b)); return r; }
+__device__ __forceinline__ void up2(f32x2 p, float& a, float& b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(p)); }
+__device__ __forceinline__ f32x2 add2(f32x2 a, f32x2 b) { f32x2 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 sub2(f32x2 a, f32x2 b) { f32x2 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 mul2(f32x2 a, f32x2 b) { f32x2 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) { f32x2 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
+// hi/lo fp16 split (forward kernels): x = hi + lo with 11 + 11 mantissa bits, so hi*hi + hi*lo + lo*hi carries ~2^-22
+// per product instead of bf16's ~2^-16 - measured on the scores: 1e-4 -> ~1e-6 against the float64 oracle.  fp16's
+// range is enough here: hidden states are in [-1, 1], weights O(1), inputs are normalised sensor values; the
+// conversion saturates (no inf can reach the tensor core), so a raw input beyond +-65504 is clipped.  Values below
+// 2^-24 ~ 6e-8 in magnitude flush in the lo part: an ABSOLUTE error of 3e-8 on an O(1) operand.
+__device__ __forceinline__ uint32_t f16x2_sat(float lo_elem, float hi_elem) {
+  uint32_t r;
+  asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(hi_elem), "f"(lo_elem));
+  return r;
+}
+__device__ __forceinline__ void split8(const float (&v)[8], uint4& hi, uint4& lo) {
+  uint32_t h[4], l[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    h[i] = f16x2_sat(v[2 * i], v[2 * i + 1]);
+    const float2 hf = __half22float2(*reinterpret_cast<const __half2*>(&h[i]));
+    float r0, r1;
+    up2(sub2(pk2(v[2 * i], v[2 * i + 1]), pk2(hf.x, hf.y)), r0, r1);
+    l[i] = f16x2_sat(r0, r1);
+  }
+  hi = make_uint4(h[0], h[1], h[2], h[3]);
+  lo = make_uint4(l[0], l[1], l[2], l[3]);
+}
+
+// ---- cell update ------------------------------------------------------------------------------------------------
+// The packed weights and biases of the tensor-core layers carry the factors of the exponentials (-log2 e for the
+// i, f, o columns, -2 log2 e for the candidate column, tc_gate_scale), so the accumulator IS the ex2 argument:
 //   a = e^-zi, f = e^-zf, g = e^-2zg, o = e^-zo,
 //   c' = [c (1+a)(1+g) + (1-g)(1+f)] / [(1+f)(1+a)(1+g)],  h = (1-e^-2c') / [(1+o)(1+e^-2c')].
-// Only large POSITIVE arguments can overflow the products, so one min per exponential is enough
-// (2^36 ~ e^25: sigmoid error < 2e-11); 5 ex2 + 2 rcp on the MUFU pipe, 20 other instructions.
+// Only large POSITIVE arguments can overflow the products, so one min per exponential is enough (2^36 ~ e^25:
+// sigmoid error < 2e-11).  Two units are updated at a time in packed fp32x2 arithmetic.  The step is bound by the
+// transcendental unit (MUFU: 16 lanes per clock and SM) with the FMA pipe mostly idle, so kPolyExps of the five
+// exponentials per unit are evaluated on the FMA pipe instead: round-to-nearest range reduction with the 1.5*2^23
+// constant, a degree-5 minimax polynomial for 2^f on [-0.5, 0.5] (2.3e-7 relative, the same 2 ulp as ex2.approx),
+// exponent inserted with an integer add.
 __host__ __device__ constexpr float tc_gate_scale(int gate) { return gate == 2 ? -2.8853900817779268f : -1.4426950408889634f; }
+#ifndef GNNQC_POLY_EXPS
+#define GNNQC_POLY_EXPS 2
+#endif
+constexpr int kPolyExps = GNNQC_POLY_EXPS;
 
 __device__ __forceinline__ float rcp_approx(float x) {
   float y;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
-__device__ __forceinline__ float lstm_cell_tc(float ei, float ef, float eg, float eo, float& c) {
-  constexpr float kCap = 36.f;
-  const float a = ex2_approx(fminf(ei, kCap));
-  const float f = ex2_approx(fminf(ef, kCap));
-  const float g = ex2_approx(fminf(eg, kCap));
-  const float o = ex2_approx(fminf(eo, kCap));
-  const float g1 = 1.f + g;
-  const float pa = fmaf(a, g1, g1);          // (1+a)(1+g)
-  const float pf = 1.f + f;
-  const float tg = fmaf(-g, pf, pf);         // (1-g)(1+f)
-  const float cn = fmaf(c, pa, tg) * rcp_approx(pf * pa);
-  c = cn;
-  const float e = ex2_approx(fminf(cn * tc_gate_scale(2), kCap));
-  const float e1 = 1.f + e;
-  const float r = rcp_approx(fmaf(o, e1, e1));   // 1 / [(1+o)(1+e)]
-  return fmaf(-e, r, r);
+__device__ __forceinline__ f32x2 ex2_mufu2(f32x2 z) {
+  float z0, z1;
+  up2(z, z0, z1);
+  return pk2(ex2_approx(fminf(z0, 36.f)), ex2_approx(fminf(z1, 36.f)));
 }
+__device__ __forceinline__ f32x2 ex2_poly2(f32x2 z) {
+  float z0, z1;
+  up2(z, z0, z1);
+  const f32x2 x = pk2(fmaxf(fminf(z0, 36.f), -126.f), fmaxf(fminf(z1, 36.f), -126.f));
+  const f32x2 t = add2(x, pk2(12582912.f, 12582912.f));          // low mantissa bits of t = round(x)
+  const f32x2 fr = sub2(x, add2(t, pk2(-12582912.f, -12582912.f)));
+  f32x2 p = fma2(pk2(0.0013276472454890609f, 0.0013276472454890609f), fr, pk2(0.009675540961325169f, 0.009675540961325169f));
+  p = fma2(p, fr, pk2(0.05550713092088699f, 0.05550713092088699f));
+  p = fma2(p, fr, pk2(0.24022120237350464f, 0.24022120237350464f));
+  p = fma2(p, fr, pk2(0.6931469440460205f, 0.6931469440460205f));
+  p = fma2(p, fr, pk2(1.0000001192092896f, 1.0000001192092896f));
+  float p0, p1, t0, t1;
+  up2(p, p0, p1);
+  up2(t, t0, t1);
+  return pk2(__int_as_float(__float_as_int(p0) + (__float_as_int(t0) << 23)), __int_as_float(__float_as_int(p1) + (__float_as_int(t1) << 23)));
+}
+template <int SLOT>   // SLOT = which of the five exponentials (0: forget, 1: output, 2: cell, 3: input, 4: candidate)
+__device__ __forceinline__ f32x2 ex2_sel2(f32x2 z) { return SLOT < kPolyExps ? ex2_poly2(z) : ex2_mufu2(z); }
 
-// Same update, also returning the gates i, f, g, o and the new cell state for the backward pass of
-// integrated gradients (layout of lstm_fwd.cuh's SAVE mode).  The gates come out of the two merged
-// reciprocals by multiplication, so the MUFU count stays at 5 ex2 + 2 rcp.
-__device__ __forceinline__ float lstm_cell_tc_save(float ei, float ef, float eg, float eo, float& c, float (&sv)[5]) {
-  constexpr float kCap = 36.f;
-  const float a = ex2_approx(fminf(ei, kCap));
-  const float f = ex2_approx(fminf(ef, kCap));
-  const float g = ex2_approx(fminf(eg, kCap));
-  const float o = ex2_approx(fminf(eo, kCap));
-  const float g1 = 1.f + g, a1 = 1.f + a, pf = 1.f + f;
-  const float pa = a1 * g1;
-  const float tg = fmaf(-g, pf, pf);         // (1-g)(1+f)
-  const float r1 = rcp_approx(pf * pa);
-  const float cn = fmaf(c, pa, tg) * r1;
+// Two units at once.  SAVE also returns the gates i, f, g, o and the new cell state for the backward pass (layout of
+// lstm_fwd.cuh's SAVE mode); they come out of the two merged reciprocals by multiplication.
+template <bool SAVE>
+__device__ __forceinline__ f32x2 lstm_cell2(f32x2 zi, f32x2 zf, f32x2 zg, f32x2 zo, f32x2& c, f32x2 (&sv)[5]) {
+  const f32x2 one = pk2(1.f, 1.f);
+  const f32x2 a = ex2_sel2<3>(zi);
+  const f32x2 f = ex2_sel2<0>(zf);
+  const f32x2 g = ex2_sel2<4>(zg);
+  const f32x2 o = ex2_sel2<1>(zo);
+  const f32x2 g1 = add2(g, one), pf = add2(f, one);
+  f32x2 pa, a1;
+  if (SAVE) {
+    a1 = add2(a, one);
+    pa = mul2(a1, g1);
+  } else {
+    pa = fma2(a, g1, g1);                       // (1+a)(1+g)
+  }
+  const f32x2 tg = mul2(sub2(one, g), pf);      // (1-g)(1+f)
+  float d0, d1;
+  up2(mul2(pf, pa), d0, d1);
+  const f32x2 r1 = pk2(rcp_approx(d0), rcp_approx(d1));
+  const f32x2 cn = mul2(fma2(c, pa, tg), r1);
   c = cn;
-  sv[0] = r1 * pf * g1;                      // 1/(1+a)
-  sv[1] = r1 * pa;                           // 1/(1+f)
-  sv[2] = r1 * tg * a1;                      // (1-g)/(1+g)
-  const float e = ex2_approx(fminf(cn * tc_gate_scale(2), kCap));
-  const float e1 = 1.f + e;
-  const float r2 = rcp_approx(fmaf(o, e1, e1));   // 1 / [(1+o)(1+e)]
-  sv[3] = r2 * e1;                           // 1/(1+o)
-  sv[4] = cn;
-  return fmaf(-e, r2, r2);
+  if (SAVE) {
+    sv[0] = mul2(r1, mul2(pf, g1));             // 1/(1+a)
+    sv[1] = mul2(r1, pa);                       // 1/(1+f)
+    sv[2] = mul2(r1, mul2(tg, a1));             // (1-g)/(1+g)
+    sv[4] = cn;
+  }
+  const f32x2 e = ex2_sel2<2>(mul2(cn, pk2(tc_gate_scale(2), tc_gate_scale(2))));
+  const f32x2 e1 = add2(e, one);
+  up2(fma2(o, e1, e1), d0, d1);                 // (1+o)(1+e)
+  const f32x2 r2 = pk2(rcp_approx(d0), rcp_approx(d1));
+  if (SAVE) sv[3] = mul2(r2, e1);               // 1/(1+o)
+  return mul2(sub2(one, e), r2);
 }
 
 // Which of the three pooled steps held the maximum (first one on ties, as lstm_fwd.cuh), two bits per unit.
@@ -158,8 +234,12 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
   extern __shared__ __align__(128) unsigned char sm[];
   float* bias = reinterpret_cast<float*>(sm + C::OFF_BIAS);
   __shared__ uint32_t tmem_slot;
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int g = tid >> 7, r = tid & 127, half = r >> 6, b = r & 63;   // group, TMEM lane, tile of the pair, window in tile
+  // The warp index goes through __shfl_sync so that the compiler knows everything derived from it (group, half,
+  // tile, loop bounds, operand addresses) is warp-uniform: uniform branches, and the tcgen05.mma / cp.async.bulk
+  // operands stay in uniform registers instead of being broadcast lane by lane around every instruction.
+  const int tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int g = warp >> 2, quarter = warp & 3, half = quarter >> 1;
+  const int r = quarter * 32 + lane, b = (quarter & 1) * 32 + lane;   // group, TMEM lane, tile of the pair, window in tile
 
   unsigned char* gsm = sm + C::OFF_GROUPS + size_t(g) * C::GROUP_BYTES;
   uint4* Ahi = reinterpret_cast<uint4*>(gsm + C::G_AHI);   // 16-byte chunk index: kb * ROWS + row
@@ -193,8 +273,13 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
     const uint4* src = reinterpret_cast<const uint4*>(wpk);
     uint4* dst = reinterpret_cast<uint4*>(sm);
     for (int i = tid; i < static_cast<int>(2 * C::B_BYTES / 16); i += C::NT) dst[i] = __ldg(src + i);
-    const float* bsrc = reinterpret_cast<const float*>(wpk + 2 * C::B_BYTES);
-    for (int i = tid; i < C::N; i += C::NT) bias[i] = __ldg(bsrc + i);
+    if (C::BIAS_MMA) {
+      for (int i = tid; i < static_cast<int>(C::BT_BYTES / 16); i += C::NT) dst[2 * C::B_BYTES / 16 + i] = __ldg(src + 2 * C::B_BYTES / 16 + i);
+      fill_ones_tile(sm + C::OFF_ONES, tid, C::NT);
+    } else {
+      const __half* bt = reinterpret_cast<const __half*>(wpk + 2 * C::B_BYTES);   // row n of the bias tile: {hi, lo, 0 ...}
+      for (int i = tid; i < C::N; i += C::NT) bias[i] = __half2float(bt[i * 8]) + __half2float(bt[i * 8 + 1]);
+    }
     uint4* gz = reinterpret_cast<uint4*>(gsm);
     for (int i = r; i < static_cast<int>(C::GROUP_BYTES / 16); i += C::ROWS) gz[i] = make_uint4(0u, 0u, 0u, 0u);
   }
@@ -203,6 +288,13 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
   __syncthreads();
   umma::fence_after_sync();
   const uint32_t tbase = tmem_slot + static_cast<uint32_t>(g * C::N);
+  const bool issuer = quarter == 0;
+  const int g_u = g;
+  const uint32_t sm_u = ptx::smem_addr(sm);
+  const uint32_t gsm_u = sm_u + static_cast<uint32_t>(C::OFF_GROUPS + size_t(g_u) * C::GROUP_BYTES);
+  const uint32_t tbase_u = __shfl_sync(0xffffffffu, tmem_slot, 0) + static_cast<uint32_t>(g_u * C::N);
+  const uint64_t d_ones = umma::smem_desc_u(sm_u + C::OFF_ONES, C::ROWS * 16, 128);
+  const uint64_t d_bias = umma::smem_desc_u(sm_u + C::OFF_BIAS, C::N * 16, 128);
 
   // x_q of this group: both halves of one step through one barrier
   auto issue_load = [&](long long q) {
@@ -217,9 +309,9 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
   if (r == 0)
     for (long long q = 0; q < C::NST && q < total; ++q) issue_load(q);
 
-  constexpr uint32_t idesc = umma::instr_desc_bf16(C::ROWS, C::N);
+  constexpr uint32_t idesc = umma::instr_desc_f16(C::ROWS, C::N);
   const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
-  float cst[H];
+  f32x2 cst[H / 2];                                           // cell states, two units per register pair
   float pmax[POOL ? H : 1];
   unsigned long long parg = 0ull;
   int rho = 0, t = 0;
@@ -228,7 +320,7 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
     const bool valid = rho + (2 * g + half) * R < my_tiles;    // uniform over the two warps of a half
     if (t == 0) {
 #pragma unroll
-      for (int j = 0; j < H; ++j) cst[j] = 0.f;
+      for (int j = 0; j < H / 2; ++j) cst[j] = 0ull;
     }
     // x_t -> bf16 hi/lo operand chunks
     const int s = static_cast<int>(q % C::NST);
@@ -249,24 +341,21 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
     }
     umma::fence_before_sync();
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(ptx::smem_addr(a_ready)) : "memory");
-    if ((r >> 5) == 0) {
-      if (r == 0) {
-        // ---- elected thread: MMA chain of this step, then the x load that reuses the freed slot ----
+    if (issuer) {
+      // ---- first warp of the group, one elected lane: MMA chain of this step, then the x load that reuses the freed slot ----
+      if (umma::elect_one()) {
         ptx::mbar_wait(a_ready, static_cast<uint32_t>(q & 1));
         umma::fence_after_sync();
-        const unsigned char* a_hi = gsm + C::G_AHI;
-        const unsigned char* a_lo = gsm + C::G_ALO;
-        const unsigned char* b_hi = sm + C::OFF_BHI;
-        const unsigned char* b_lo = sm + C::OFF_BLO;
+        if (C::BIAS_MMA) umma::mma_bf16(tbase_u, d_ones, d_bias, idesc, false);
 #pragma unroll
         for (int kc = 0; kc < C::KP / 16; ++kc) {
-          const uint64_t dah = umma::smem_desc(a_hi + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
-          const uint64_t dal = umma::smem_desc(a_lo + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
-          const uint64_t dbh = umma::smem_desc(b_hi + kc * 2 * C::N * 16, C::N * 16, 128);
-          const uint64_t dbl = umma::smem_desc(b_lo + kc * 2 * C::N * 16, C::N * 16, 128);
-          umma::mma_bf16(tbase, dah, dbh, idesc, kc > 0);
-          umma::mma_bf16(tbase, dah, dbl, idesc, true);
-          umma::mma_bf16(tbase, dal, dbh, idesc, true);
+          const uint64_t dah = umma::smem_desc_u(gsm_u + C::G_AHI + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
+          const uint64_t dal = umma::smem_desc_u(gsm_u + C::G_ALO + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
+          const uint64_t dbh = umma::smem_desc_u(sm_u + C::OFF_BHI + kc * 2 * C::N * 16, C::N * 16, 128);
+          const uint64_t dbl = umma::smem_desc_u(sm_u + C::OFF_BLO + kc * 2 * C::N * 16, C::N * 16, 128);
+          umma::mma_bf16(tbase_u, dah, dbh, idesc, C::BIAS_MMA || kc > 0);
+          umma::mma_bf16(tbase_u, dah, dbl, idesc, true);
+          umma::mma_bf16(tbase_u, dal, dbh, idesc, true);
         }
         umma::commit(d_full);
         if (q + C::NST < total) issue_load(q + C::NST);
@@ -285,18 +374,24 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
         umma::tmem_ld8x4(col0, col0 + H, col0 + 2 * H, col0 + 3 * H, zi, zf, zg, zo);
         const int j0 = b8 * 8;
 #pragma unroll
-        for (int i = 0; i < 8; ++i) {
+        for (int i = 0; i < 8; i += 2) {
+          f32x2 pi = pk2(zi[i], zi[i + 1]), pf = pk2(zf[i], zf[i + 1]), pg = pk2(zg[i], zg[i + 1]), po = pk2(zo[i], zo[i + 1]);
+          if (!C::BIAS_MMA) {
+            pi = add2(pi, *reinterpret_cast<const f32x2*>(bias + j0 + i));
+            pf = add2(pf, *reinterpret_cast<const f32x2*>(bias + H + j0 + i));
+            pg = add2(pg, *reinterpret_cast<const f32x2*>(bias + 2 * H + j0 + i));
+            po = add2(po, *reinterpret_cast<const f32x2*>(bias + 3 * H + j0 + i));
+          }
+          f32x2 sv[5];
+          up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[(j0 + i) / 2], sv), hv[i], hv[i + 1]);
           if (SAVE) {
-            float sv[5];
-            hv[i] = lstm_cell_tc_save(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
-                                      zo[i] + bias[3 * H + j0 + i], cst[j0 + i], sv);
             float* so = save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b;
 #pragma unroll
-            for (int v = 0; v < 5; ++v) so[v * H * kTile] = sv[v];
-            if (nsave > 5) so[5 * H * kTile] = hv[i];
-          } else {
-            hv[i] = lstm_cell_tc(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
-                                 zo[i] + bias[3 * H + j0 + i], cst[j0 + i]);
+            for (int v = 0; v < 5; ++v) up2(sv[v], so[v * H * kTile], so[(v * H + 1) * kTile]);
+            if (nsave > 5) {
+              so[5 * H * kTile] = hv[i];
+              so[(5 * H + 1) * kTile] = hv[i + 1];
+            }
           }
         }
         if (POOL) {

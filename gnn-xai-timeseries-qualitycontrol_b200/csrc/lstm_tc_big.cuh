@@ -37,16 +37,20 @@ struct TcBigCfg {
   static constexpr int TMEM_COLS = NCH * NC;              // 256 or 512
   static constexpr int PIECE_BYTES = 2 * 16 * NC * 2;     // hi | lo of one (chunk, K slice)
   static constexpr int N_PIECES = NCH * KC;
-  static constexpr int RING = STREAM ? 10 : N_PIECES;
+  static constexpr int RING = STREAM ? 8 : N_PIECES;
   static constexpr int XBYTES = I * kTile * 4;            // one 64-window half of one step
   static constexpr size_t B_BYTES = size_t(RING) * PIECE_BYTES;
   static constexpr size_t A_BYTES = size_t(KP) * ROWS * 2;
   static constexpr size_t OFF_B = 0, OFF_AHI = B_BYTES, OFF_ALO = B_BYTES + A_BYTES, OFF_X = B_BYTES + 2 * A_BYTES;
+  static constexpr size_t BT_BYTES = tc_bias_tile_bytes(NC);       // one bias tile per chunk (resident also when the weights stream)
   static constexpr size_t OFF_BIAS = OFF_X + 2 * size_t(XBYTES);
-  static constexpr size_t OFF_BAR = OFF_BIAS + size_t(4 * H) * 4;
+  // 64 -> 64 units leaves no room for the bias / ones tiles next to the resident weights: fp32 biases in shared memory instead
+  static constexpr bool BIAS_MMA = OFF_BIAS + NCH * BT_BYTES + kOnesTileBytes + 1024 <= 227 * 1024;
+  static constexpr size_t OFF_ONES = OFF_BIAS + (BIAS_MMA ? NCH * BT_BYTES : size_t(4 * H) * 4);
+  static constexpr size_t OFF_BAR = OFF_ONES + (BIAS_MMA ? kOnesTileBytes : 0);
   static constexpr int N_BARS = 2 + NCH + 2 * RING;       // x_full, a_ready, d_full[NCH], b_full[RING], b_empty[RING]
   static constexpr size_t SMEM_BYTES = OFF_BAR + size_t(N_BARS) * 8 + 16;
-  static constexpr size_t PACKED_BYTES = size_t(N_PIECES) * PIECE_BYTES + size_t(4 * H) * 4;
+  static constexpr size_t PACKED_BYTES = size_t(N_PIECES) * PIECE_BYTES + NCH * BT_BYTES;
   static_assert(I % 8 == 0 && H % (UB * G) == 0 && TMEM_COLS <= 512, "shape not covered");
   static_assert(SMEM_BYTES <= 227 * 1024, "operands do not fit in shared memory");
 };
@@ -65,7 +69,6 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
   uint4* Ahi = reinterpret_cast<uint4*>(sm + C::OFF_AHI);   // 16-byte chunk index: kb * ROWS + row
   uint4* Alo = reinterpret_cast<uint4*>(sm + C::OFF_ALO);
   float* xs = reinterpret_cast<float*>(sm + C::OFF_X);      // [2][I][64]
-  float* bias = reinterpret_cast<float*>(sm + C::OFF_BIAS);
   uint64_t* x_full = reinterpret_cast<uint64_t*>(sm + C::OFF_BAR);
   uint64_t* a_ready = x_full + 1;
   uint64_t* d_full = a_ready + 1;
@@ -103,8 +106,21 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
       uint4* dst = reinterpret_cast<uint4*>(sm + C::OFF_B);
       for (int i = tid; i < static_cast<int>(C::B_BYTES / 16); i += C::NT) dst[i] = __ldg(src + i);
     }
-    const float* bsrc = reinterpret_cast<const float*>(wpk + size_t(C::N_PIECES) * C::PIECE_BYTES);
-    for (int i = tid; i < 4 * H; i += C::NT) bias[i] = __ldg(bsrc + i);
+    if (C::BIAS_MMA) {
+      const uint4* bsrc = reinterpret_cast<const uint4*>(wpk + size_t(C::N_PIECES) * C::PIECE_BYTES);
+      uint4* bdst = reinterpret_cast<uint4*>(sm + C::OFF_BIAS);
+      for (int i = tid; i < static_cast<int>(C::NCH * C::BT_BYTES / 16); i += C::NT) bdst[i] = __ldg(bsrc + i);
+      fill_ones_tile(sm + C::OFF_ONES, tid, C::NT);
+    } else {
+      // bias tile of chunk c, row n = gate * 32 + unit-in-chunk: {hi, lo, 0 ...}  ->  bias[gate * H + c * 32 + unit]
+      const __half* bt = reinterpret_cast<const __half*>(wpk + size_t(C::N_PIECES) * C::PIECE_BYTES);
+      float* bias = reinterpret_cast<float*>(sm + C::OFF_BIAS);
+      for (int i = tid; i < 4 * H; i += C::NT) {
+        const int gate = i / H, unit = i % H, c = unit / C::UB, n = gate * C::UB + unit % C::UB;
+        const __half* row = bt + (size_t(c) * C::BT_BYTES / 2) + n * 8;
+        bias[i] = __half2float(row[0]) + __half2float(row[1]);
+      }
+    }
     for (int i = tid; i < static_cast<int>(2 * C::A_BYTES / 16); i += C::NT) Ahi[i] = make_uint4(0u, 0u, 0u, 0u);   // A_hi and A_lo are adjacent
     for (int i = tid; i < 2 * I * kTile; i += C::NT) xs[i] = 0.f;
   }
@@ -114,9 +130,12 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
   umma::fence_after_sync();
   const uint32_t tbase = tmem_slot;
 
-  if (warp == kMmaWarp) {
-    // ---- x loads + MMA issue (one thread) --------------------------------------------------------
-    if (lane == 0) {
+  const int warp_u = __shfl_sync(0xffffffffu, warp, 0);     // warp-uniform (see umma::elect_one)
+  if (warp_u == kMmaWarp) {
+    // ---- x loads + MMA issue (one elected lane, warp-uniform operands) ------------------------------
+    const uint32_t sm_u = ptx::smem_addr(sm);
+    const uint32_t tbase_u = __shfl_sync(0xffffffffu, tmem_slot, 0);
+    if (umma::elect_one()) {
       auto issue_load = [&](long long q) {
         const int n = static_cast<int>(q / T), t = static_cast<int>(q % T);
         const long long tile_a = tile0 + 2 * n;
@@ -126,10 +145,9 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
         if (second) ptx::bulk_load(xs + I * kTile, xin + ((tile_a + 1) * t_in_stride + t) * (I * kTile), C::XBYTES, x_full);
       };
       issue_load(0);
-      constexpr uint32_t idesc = umma::instr_desc_bf16(C::ROWS, C::NC);
-      const unsigned char* a_hi = sm + C::OFF_AHI;
-      const unsigned char* a_lo = sm + C::OFF_ALO;
-      const unsigned char* bsm = sm + C::OFF_B;
+      constexpr uint32_t idesc = umma::instr_desc_f16(C::ROWS, C::NC);
+      const uint64_t d_ones = umma::smem_desc_u(sm_u + C::OFF_ONES, C::ROWS * 16, 128);
+      const uint32_t a_hi = sm_u + C::OFF_AHI, a_lo = sm_u + C::OFF_ALO, bsm = sm_u + C::OFF_B;
       long long pc = 0;   // pieces consumed (STREAM)
       for (long long q = 0; q < total; ++q) {
         ptx::mbar_wait(a_ready, static_cast<uint32_t>(q & 1));
@@ -137,6 +155,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
         if (q + 1 < total) issue_load(q + 1);   // every thread has converted x_q by now
 #pragma unroll 1
         for (int c = 0; c < C::NCH; ++c) {
+          if (C::BIAS_MMA) umma::mma_bf16(tbase_u + c * C::NC, d_ones, umma::smem_desc_u(sm_u + C::OFF_BIAS + c * C::BT_BYTES, C::NC * 16, 128), idesc, false);
 #pragma unroll
           for (int kc = 0; kc < C::KC; ++kc) {
             int slot = c * C::KC + kc;
@@ -145,14 +164,14 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
               ptx::mbar_wait(&b_full[slot], static_cast<uint32_t>((pc / C::RING) & 1));
               umma::fence_after_sync();
             }
-            const unsigned char* bp = bsm + size_t(slot) * C::PIECE_BYTES;
-            const uint64_t dah = umma::smem_desc(a_hi + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
-            const uint64_t dal = umma::smem_desc(a_lo + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
-            const uint64_t dbh = umma::smem_desc(bp, C::NC * 16, 128);
-            const uint64_t dbl = umma::smem_desc(bp + C::PIECE_BYTES / 2, C::NC * 16, 128);
-            umma::mma_bf16(tbase + c * C::NC, dah, dbh, idesc, kc > 0);
-            umma::mma_bf16(tbase + c * C::NC, dah, dbl, idesc, true);
-            umma::mma_bf16(tbase + c * C::NC, dal, dbh, idesc, true);
+            const uint32_t bp = bsm + static_cast<uint32_t>(slot) * C::PIECE_BYTES;
+            const uint64_t dah = umma::smem_desc_u(a_hi + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
+            const uint64_t dal = umma::smem_desc_u(a_lo + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
+            const uint64_t dbh = umma::smem_desc_u(bp, C::NC * 16, 128);
+            const uint64_t dbl = umma::smem_desc_u(bp + C::PIECE_BYTES / 2, C::NC * 16, 128);
+            umma::mma_bf16(tbase_u + c * C::NC, dah, dbh, idesc, C::BIAS_MMA || kc > 0);
+            umma::mma_bf16(tbase_u + c * C::NC, dah, dbl, idesc, true);
+            umma::mma_bf16(tbase_u + c * C::NC, dal, dbh, idesc, true);
             if (STREAM) {
               umma::commit(&b_empty[slot]);
               ++pc;
@@ -162,7 +181,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
         }
       }
     }
-  } else if (warp == kLoadWarp) {
+  } else if (warp_u == kLoadWarp) {
     // ---- weight pieces through the ring (H = 128 only) ---------------------------------------------
     if (STREAM && lane == 0) {
       const long long n_loads = total * C::N_PIECES;
@@ -181,7 +200,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
     const int quarter = warp & 3, g = warp >> 2;
     const int r = quarter * 32 + lane, half = r >> 6, b = r & 63;
     const uint32_t lane_base = static_cast<uint32_t>(quarter * 32) << 16;
-    float cst[C::CPG * C::UB];
+    f32x2 cst[C::CPG * C::UB / 2];                   // cell states, two units per register pair
     float pmax[POOL ? C::CPG * C::UB : 1];
     unsigned long long parg = 0ull;
     uint4 hold_hi[C::CPG][C::UB / 8], hold_lo[C::CPG][C::UB / 8];
@@ -221,7 +240,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
       const uint32_t par = static_cast<uint32_t>(q & 1);
       if (t == 0) {
 #pragma unroll
-        for (int j = 0; j < C::CPG * C::UB; ++j) cst[j] = 0.f;
+        for (int j = 0; j < C::CPG * C::UB / 2; ++j) cst[j] = 0ull;
       }
       const bool last_step = (t == T - 1);
 #pragma unroll
@@ -239,20 +258,25 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
           const int j0 = c * C::UB + b8 * 8;       // first unit of this block
           const int l0 = ci * C::UB + b8 * 8;      // its slot in cst / pmax
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            if (SAVE) {
-              float sv[5];
-              hv[i] = lstm_cell_tc_save(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
-                                        zo[i] + bias[3 * H + j0 + i], cst[l0 + i], sv);
-              if (valid) {
-                float* so = save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b;
+          for (int i = 0; i < 8; i += 2) {
+            f32x2 sv[5];
+            f32x2 pi = pk2(zi[i], zi[i + 1]), pf = pk2(zf[i], zf[i + 1]), pg = pk2(zg[i], zg[i + 1]), po = pk2(zo[i], zo[i + 1]);
+            if (!C::BIAS_MMA) {
+              const float* bias = reinterpret_cast<const float*>(sm + C::OFF_BIAS);
+              pi = add2(pi, *reinterpret_cast<const f32x2*>(bias + j0 + i));
+              pf = add2(pf, *reinterpret_cast<const f32x2*>(bias + H + j0 + i));
+              pg = add2(pg, *reinterpret_cast<const f32x2*>(bias + 2 * H + j0 + i));
+              po = add2(po, *reinterpret_cast<const f32x2*>(bias + 3 * H + j0 + i));
+            }
+            up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[(l0 + i) / 2], sv), hv[i], hv[i + 1]);
+            if (SAVE && valid) {
+              float* so = save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b;
 #pragma unroll
-                for (int v = 0; v < 5; ++v) so[v * H * kTile] = sv[v];
-              if (nsave > 5) so[5 * H * kTile] = hv[i];
+              for (int v = 0; v < 5; ++v) up2(sv[v], so[v * H * kTile], so[(v * H + 1) * kTile]);
+              if (nsave > 5) {
+                so[5 * H * kTile] = hv[i];
+                so[(5 * H + 1) * kTile] = hv[i + 1];
               }
-            } else {
-              hv[i] = lstm_cell_tc(zi[i] + bias[j0 + i], zf[i] + bias[H + j0 + i], zg[i] + bias[2 * H + j0 + i],
-                                   zo[i] + bias[3 * H + j0 + i], cst[l0 + i]);
             }
           }
           if (POOL) {

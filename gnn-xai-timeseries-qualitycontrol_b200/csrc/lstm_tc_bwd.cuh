@@ -267,10 +267,10 @@ lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this lay
         uint4* Ahi = reinterpret_cast<uint4*>(abase + size_t(buf) * C::A_BUF);
         uint4* Alo = reinterpret_cast<uint4*>(abase + size_t(buf) * C::A_BUF + C::A_BUF / 2);
         uint4 hi, lo;
-        split8(zi, hi, lo); Ahi[0 * 128 + r] = hi; Alo[0 * 128 + r] = lo;
-        split8(zf, hi, lo); Ahi[1 * 128 + r] = hi; Alo[1 * 128 + r] = lo;
-        split8(zg, hi, lo); Ahi[2 * 128 + r] = hi; Alo[2 * 128 + r] = lo;
-        split8(zo, hi, lo); Ahi[3 * 128 + r] = hi; Alo[3 * 128 + r] = lo;
+        split8_bf16(zi, hi, lo); Ahi[0 * 128 + r] = hi; Alo[0 * 128 + r] = lo;
+        split8_bf16(zf, hi, lo); Ahi[1 * 128 + r] = hi; Alo[1 * 128 + r] = lo;
+        split8_bf16(zg, hi, lo); Ahi[2 * 128 + r] = hi; Alo[2 * 128 + r] = lo;
+        split8_bf16(zo, hi, lo); Ahi[3 * 128 + r] = hi; Alo[3 * 128 + r] = lo;
         umma::fence_async_smem();
         umma::fence_before_sync();
         asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(ptx::smem_addr(&a_ready[buf])) : "memory");

@@ -21,8 +21,10 @@ struct TcPairCfg {
   static constexpr int XBYTES = I * kTile * 4;            // one 64-window half of one step
   static constexpr size_t B1_BYTES = size_t(KP1) * N * 2, B2_BYTES = size_t(KP2) * N * 2;   // one of hi / lo
   static constexpr size_t A1_BYTES = size_t(KP1) * ROWS * 2, A2_BYTES = size_t(KP2) * ROWS * 2;
-  static constexpr size_t OFF_B1 = 0, OFF_B2 = 2 * B1_BYTES, OFF_BIAS = OFF_B2 + 2 * B2_BYTES;   // bias1[64] | bias2[64]
-  static constexpr size_t OFF_GROUPS = OFF_BIAS + 2 * size_t(N) * 4;
+  static constexpr size_t BT_BYTES = tc_bias_tile_bytes(N);
+  static constexpr size_t OFF_B1 = 0, OFF_B2 = 2 * B1_BYTES, OFF_BIAS = OFF_B2 + 2 * B2_BYTES;   // bias tile 1 | bias tile 2 | ones tile
+  static constexpr size_t OFF_ONES = OFF_BIAS + 2 * BT_BYTES;
+  static constexpr size_t OFF_GROUPS = OFF_ONES + kOnesTileBytes;
   static constexpr size_t G_A1 = 0, G_A2 = 2 * A1_BYTES, G_X = G_A2 + 2 * A2_BYTES;          // hi then lo in each
   static constexpr size_t GROUP_BYTES = (G_X + 2 * size_t(XBYTES) + 127) / 128 * 128;
   static constexpr size_t OFF_BAR = OFF_GROUPS + GROUPS * GROUP_BYTES;
@@ -41,11 +43,13 @@ lstm_tc_pair_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
   using C = TcPairCfg<I>;
   constexpr int H = C::H;
   extern __shared__ __align__(128) unsigned char sm[];
-  float* bias1 = reinterpret_cast<float*>(sm + C::OFF_BIAS);
-  float* bias2 = bias1 + C::N;
   __shared__ uint32_t tmem_slot;
-  const int tid = threadIdx.x, warp = tid >> 5;
-  const int g = tid >> 7, r = tid & 127, half = r >> 6, b = r & 63;
+  // The warp index goes through __shfl_sync so that the compiler knows everything derived from it (group, half,
+  // tile, loop bounds, operand addresses) is warp-uniform: uniform branches, and the tcgen05.mma / cp.async.bulk
+  // operands stay in uniform registers instead of being broadcast lane by lane around every instruction.
+  const int tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+  const int g = warp >> 2, quarter = warp & 3, half = quarter >> 1;
+  const int r = quarter * 32 + lane, b = (quarter & 1) * 32 + lane;
 
   unsigned char* gsm = sm + C::OFF_GROUPS + size_t(g) * C::GROUP_BYTES;
   uint4* A1hi = reinterpret_cast<uint4*>(gsm + C::G_A1);
@@ -83,12 +87,12 @@ lstm_tc_pair_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
     uint4* d2 = reinterpret_cast<uint4*>(sm + C::OFF_B2);
     for (int i = tid; i < static_cast<int>(2 * C::B1_BYTES / 16); i += C::NT) d1[i] = __ldg(s1 + i);
     for (int i = tid; i < static_cast<int>(2 * C::B2_BYTES / 16); i += C::NT) d2[i] = __ldg(s2 + i);
-    const float* b1 = reinterpret_cast<const float*>(wpk1 + 2 * C::B1_BYTES);
-    const float* b2 = reinterpret_cast<const float*>(wpk2 + 2 * C::B2_BYTES);
-    for (int i = tid; i < C::N; i += C::NT) {
-      bias1[i] = __ldg(b1 + i);
-      bias2[i] = __ldg(b2 + i);
+    uint4* bt = reinterpret_cast<uint4*>(sm + C::OFF_BIAS);
+    for (int i = tid; i < static_cast<int>(C::BT_BYTES / 16); i += C::NT) {
+      bt[i] = __ldg(s1 + 2 * C::B1_BYTES / 16 + i);
+      bt[C::BT_BYTES / 16 + i] = __ldg(s2 + 2 * C::B2_BYTES / 16 + i);
     }
+    fill_ones_tile(sm + C::OFF_ONES, tid, C::NT);
     uint4* gz = reinterpret_cast<uint4*>(gsm);
     for (int i = r; i < static_cast<int>(C::GROUP_BYTES / 16); i += C::ROWS) gz[i] = make_uint4(0u, 0u, 0u, 0u);
   }
@@ -97,6 +101,14 @@ lstm_tc_pair_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
   __syncthreads();
   umma::fence_after_sync();
   const uint32_t tb1 = tmem_slot + static_cast<uint32_t>(g * 2 * C::N), tb2 = tb1 + C::N;
+  const bool issuer = quarter == 0;
+  const int g_u = g;
+  const uint32_t sm_u = ptx::smem_addr(sm);
+  const uint32_t gsm_u = sm_u + static_cast<uint32_t>(C::OFF_GROUPS + size_t(g_u) * C::GROUP_BYTES);
+  const uint32_t tb1_u = __shfl_sync(0xffffffffu, tmem_slot, 0) + static_cast<uint32_t>(g_u * 2 * C::N), tb2_u = tb1_u + C::N;
+  const uint64_t d_ones = umma::smem_desc_u(sm_u + C::OFF_ONES, C::ROWS * 16, 128);
+  const uint64_t d_bias1 = umma::smem_desc_u(sm_u + C::OFF_BIAS, C::N * 16, 128);
+  const uint64_t d_bias2 = umma::smem_desc_u(sm_u + C::OFF_BIAS + C::BT_BYTES, C::N * 16, 128);
 
   // x of layer-1 step t of round rho (both halves through one barrier); `n` counts the loads issued
   auto issue_load = [&](int rho, int t) {
@@ -108,9 +120,10 @@ lstm_tc_pair_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
   };
   if (r == 0 && total > 0) issue_load(0, 0);
 
-  constexpr uint32_t idesc = umma::instr_desc_bf16(C::ROWS, C::N);
+  constexpr uint32_t idesc = umma::instr_desc_f16(C::ROWS, C::N);
   const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
-  float c1[H], c2[H], pmax[H];
+  f32x2 c1[H / 2], c2[H / 2];     // cell states, two units per register pair
+  float pmax[H];
   int rho = 0, t = 0;          // t = macro-step inside the sequence: layer 1 runs step t (t < T), layer 2 step t-1 (t >= 1)
   uint32_t x_loads = 0;        // x loads consumed so far (barrier phase)
   for (long long q = 0; q < total; ++q) {
@@ -118,7 +131,7 @@ lstm_tc_pair_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
     const bool valid = rho + (2 * g + half) * R < my_tiles;    // uniform over the two warps of a half
     if (t == 0) {
 #pragma unroll
-      for (int j = 0; j < H; ++j) c1[j] = c2[j] = 0.f;
+      for (int j = 0; j < H / 2; ++j) c1[j] = c2[j] = 0ull;
     }
     // x_t -> bf16 hi/lo operand chunks of layer 1
     if (t < T) {
@@ -141,41 +154,35 @@ lstm_tc_pair_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
     }
     umma::fence_before_sync();
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(ptx::smem_addr(a_ready)) : "memory");
-    if ((r >> 5) == 0) {
-      if (r == 0) {
-        // ---- elected thread: layer 1 step t and layer 2 step t-1 behind one commit ----------------
+    if (issuer) {
+      // ---- first warp of the group, one elected lane: layer 1 step t and layer 2 step t-1 behind one commit ----
+      if (umma::elect_one()) {
         ptx::mbar_wait(a_ready, static_cast<uint32_t>(q & 1));
         umma::fence_after_sync();
         if (t < T) {
-          const unsigned char* a_hi = gsm + C::G_A1;
-          const unsigned char* a_lo = gsm + C::G_A1 + C::A1_BYTES;
-          const unsigned char* b_hi = sm + C::OFF_B1;
-          const unsigned char* b_lo = sm + C::OFF_B1 + C::B1_BYTES;
+          umma::mma_bf16(tb1_u, d_ones, d_bias1, idesc, false);
 #pragma unroll
           for (int kc = 0; kc < C::KP1 / 16; ++kc) {
-            const uint64_t dah = umma::smem_desc(a_hi + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
-            const uint64_t dal = umma::smem_desc(a_lo + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
-            const uint64_t dbh = umma::smem_desc(b_hi + kc * 2 * C::N * 16, C::N * 16, 128);
-            const uint64_t dbl = umma::smem_desc(b_lo + kc * 2 * C::N * 16, C::N * 16, 128);
-            umma::mma_bf16(tb1, dah, dbh, idesc, kc > 0);
-            umma::mma_bf16(tb1, dah, dbl, idesc, true);
-            umma::mma_bf16(tb1, dal, dbh, idesc, true);
+            const uint64_t dah = umma::smem_desc_u(gsm_u + C::G_A1 + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
+            const uint64_t dal = umma::smem_desc_u(gsm_u + C::G_A1 + C::A1_BYTES + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
+            const uint64_t dbh = umma::smem_desc_u(sm_u + C::OFF_B1 + kc * 2 * C::N * 16, C::N * 16, 128);
+            const uint64_t dbl = umma::smem_desc_u(sm_u + C::OFF_B1 + C::B1_BYTES + kc * 2 * C::N * 16, C::N * 16, 128);
+            umma::mma_bf16(tb1_u, dah, dbh, idesc, true);
+            umma::mma_bf16(tb1_u, dah, dbl, idesc, true);
+            umma::mma_bf16(tb1_u, dal, dbh, idesc, true);
           }
         }
         if (t >= 1) {
-          const unsigned char* a_hi = gsm + C::G_A2;
-          const unsigned char* a_lo = gsm + C::G_A2 + C::A2_BYTES;
-          const unsigned char* b_hi = sm + C::OFF_B2;
-          const unsigned char* b_lo = sm + C::OFF_B2 + C::B2_BYTES;
+          umma::mma_bf16(tb2_u, d_ones, d_bias2, idesc, false);
 #pragma unroll
           for (int kc = 0; kc < C::KP2 / 16; ++kc) {
-            const uint64_t dah = umma::smem_desc(a_hi + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
-            const uint64_t dal = umma::smem_desc(a_lo + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
-            const uint64_t dbh = umma::smem_desc(b_hi + kc * 2 * C::N * 16, C::N * 16, 128);
-            const uint64_t dbl = umma::smem_desc(b_lo + kc * 2 * C::N * 16, C::N * 16, 128);
-            umma::mma_bf16(tb2, dah, dbh, idesc, kc > 0);
-            umma::mma_bf16(tb2, dah, dbl, idesc, true);
-            umma::mma_bf16(tb2, dal, dbh, idesc, true);
+            const uint64_t dah = umma::smem_desc_u(gsm_u + C::G_A2 + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
+            const uint64_t dal = umma::smem_desc_u(gsm_u + C::G_A2 + C::A2_BYTES + kc * 2 * C::ROWS * 16, C::ROWS * 16, 128);
+            const uint64_t dbh = umma::smem_desc_u(sm_u + C::OFF_B2 + kc * 2 * C::N * 16, C::N * 16, 128);
+            const uint64_t dbl = umma::smem_desc_u(sm_u + C::OFF_B2 + C::B2_BYTES + kc * 2 * C::N * 16, C::N * 16, 128);
+            umma::mma_bf16(tb2_u, dah, dbh, idesc, true);
+            umma::mma_bf16(tb2_u, dah, dbl, idesc, true);
+            umma::mma_bf16(tb2_u, dal, dbh, idesc, true);
           }
         }
         umma::commit(d_full);
@@ -195,10 +202,11 @@ lstm_tc_pair_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
           float zi[8], zf[8], zg[8], zo[8], hv[8];
           const uint32_t col0 = tb1 + lane_base + b8 * 8;
           umma::tmem_ld8x4(col0, col0 + H, col0 + 2 * H, col0 + 3 * H, zi, zf, zg, zo);
+          f32x2 sv[5];
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            hv[i] = lstm_cell_tc(zi[i] + bias1[j0 + i], zf[i] + bias1[H + j0 + i], zg[i] + bias1[2 * H + j0 + i],
-                                 zo[i] + bias1[3 * H + j0 + i], c1[j0 + i]);
+          for (int i = 0; i < 8; i += 2)
+            up2(lstm_cell2<false>(pk2(zi[i], zi[i + 1]), pk2(zf[i], zf[i + 1]), pk2(zg[i], zg[i + 1]), pk2(zo[i], zo[i + 1]), c1[(j0 + i) / 2], sv),
+                hv[i], hv[i + 1]);
           uint4 hi, lo;
           split8(hv, hi, lo);
           A2hi[b8 * C::ROWS + r] = hi;                       // layer 2's input of step t
@@ -212,10 +220,11 @@ lstm_tc_pair_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
           float zi[8], zf[8], zg[8], zo[8], hv[8];
           const uint32_t col0 = tb2 + lane_base + b8 * 8;
           umma::tmem_ld8x4(col0, col0 + H, col0 + 2 * H, col0 + 3 * H, zi, zf, zg, zo);
+          f32x2 sv[5];
 #pragma unroll
-          for (int i = 0; i < 8; ++i)
-            hv[i] = lstm_cell_tc(zi[i] + bias2[j0 + i], zf[i] + bias2[H + j0 + i], zg[i] + bias2[2 * H + j0 + i],
-                                 zo[i] + bias2[3 * H + j0 + i], c2[j0 + i]);
+          for (int i = 0; i < 8; i += 2)
+            up2(lstm_cell2<false>(pk2(zi[i], zi[i + 1]), pk2(zf[i], zf[i + 1]), pk2(zg[i], zg[i + 1]), pk2(zo[i], zo[i + 1]), c2[(j0 + i) / 2], sv),
+                hv[i], hv[i + 1]);
           const int ph = t2 % 3;
 #pragma unroll
           for (int i = 0; i < 8; ++i) pmax[j0 + i] = (ph == 0) ? hv[i] : fmaxf(pmax[j0 + i], hv[i]);

@@ -27,12 +27,37 @@ __device__ __forceinline__ uint64_t smem_desc(const void* smem_ptr, uint32_t lbo
   return d;                                                      // base offset 0, layout type 0 (none)
 }
 
+// Same from a shared-window address that is already warp-uniform (keeps the descriptor in uniform registers).
+__device__ __forceinline__ uint64_t smem_desc_u(uint32_t addr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  return static_cast<uint64_t>((addr & 0x3FFFF) >> 4) | (static_cast<uint64_t>((lbo_bytes >> 4) & 0x3FFF) << 16) |
+         (static_cast<uint64_t>((sbo_bytes >> 4) & 0x3FFF) << 32) | (static_cast<uint64_t>(1) << 46);
+}
+// One lane of a converged warp.  The MMA-issuing code runs in warp-uniform control flow with warp-uniform operands
+// (group index and TMEM base taken through __shfl_sync) and only the instruction itself is predicated on the elected
+// lane: otherwise the compiler wraps every tcgen05.mma in an elect / broadcast loop (~14 dependent instructions each).
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "elect.sync _|p, 0xffffffff;\n"
+      "selp.u32 %0, 1, 0, p;\n"
+      "}\n"
+      : "=r"(pred));
+  return pred != 0;
+}
+
 // 32-bit instruction descriptor: bf16 x bf16 -> fp32, both operands K-major, dense.
 __host__ __device__ constexpr uint32_t instr_desc_bf16(int m, int n) {
   return (1u << 4)                       // D format: F32
          | (1u << 7)                     // A format: BF16
          | (1u << 10)                    // B format: BF16
          | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
+}
+
+// Same with fp16 operands (kind::f16 covers both 16-bit formats; format code 0 = F16).
+__host__ __device__ constexpr uint32_t instr_desc_f16(int m, int n) {
+  return (1u << 4) | (static_cast<uint32_t>(n >> 3) << 17) | (static_cast<uint32_t>(m >> 4) << 24);
 }
 
 __device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, uint32_t ncols) {   // one full warp
