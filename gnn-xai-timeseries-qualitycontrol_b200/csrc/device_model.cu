@@ -26,13 +26,11 @@ StackPlan::StackPlan(const ModelSpec& s, int T_) : T(T_) {
     t_out[2 * p] = need;          // full sequence to its partner
     t_out[2 * p + 1] = need / 3;  // pooled
   }
-  // Ping/pong: buffer A holds x1 and the outputs of odd layers (1,3,5), buffer B those of even
-  // layers (0,2,4,6).
-  size_t a = size_t(t_run[0]) * s.lstm_in[0], b = 0;
-  for (int l = 0; l < s.n_lstm; ++l) {
-    size_t sz = size_t(t_out[l]) * s.lstm_hid[l];
-    if (l % 2 == 0) b = std::max(b, sz); else a = std::max(a, sz);
-  }
+  // Ping/pong: every launch reads one buffer and writes the other.  Which layers land in which buffer depends on the
+  // schedule (fused layer pairs skip a hand-over), so both are sized for the largest tensor that can land in them.
+  size_t b = 0;
+  for (int l = 0; l < s.n_lstm; ++l) b = std::max(b, size_t(t_out[l]) * s.lstm_hid[l]);
+  const size_t a = std::max(b, size_t(t_run[0]) * s.lstm_in[0]);
   bytes_a = a * kTile * sizeof(float);
   bytes_b = b * kTile * sizeof(float);
 }
@@ -269,7 +267,8 @@ void DeviceModel::configure_kernels() {
     layer_dispatch<true>(s.lstm_in[l], s.lstm_hid[l], pool, last, nullptr, nullptr, nullptr, 0, 0, 0, 0, 0, nullptr);
     if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last)) tc_configure(s.lstm_in[l], s.lstm_hid[l], pool, last);
   }
-  if (s.n_lstm >= 3 && tc_pair_supported(s.lstm_in[0], s.lstm_hid[0], s.lstm_in[1], s.lstm_hid[1])) tc_pair_configure(s.lstm_in[0]);
+  for (int l = 0; l + 2 < s.n_lstm; l += 2)
+    if (tc_pair_supported(s.lstm_in[l], s.lstm_hid[l], s.lstm_in[l + 1], s.lstm_hid[l + 1])) tc_pair_configure(s.lstm_in[l], s.lstm_hid[l]);
   configure_cml_frontend();
   GNNQC_CUDA(cudaGetLastError());
   if (s.lstm_hid[s.n_lstm - 1] != 128 || s.dense_units != 64)
@@ -284,27 +283,25 @@ void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, l
   int cur = 0;                       // `in` lives in bufs[cur]; every layer writes the other buffer
   int t_in = plan.t_run[0];
   static const char* const kNames[kMaxLstmLayers] = {"lstm_l1", "lstm_l2", "lstm_l3", "lstm_l4", "lstm_l5", "lstm_l6", "lstm_l7"};
-  int l = 0;
-  // Layers 1 + 2 as one kernel when the shapes allow it.  It reads buffer A and writes B, which swaps the
-  // roles the two buffers have in the one-kernel-per-layer schedule, so both must hold any later layer.
-  if (s.n_lstm >= 3 && plan.t_run[0] == plan.t_run[1] && tc_pair_supported(s.lstm_in[0], s.lstm_hid[0], s.lstm_in[1], s.lstm_hid[1])) {
-    size_t need = 0;
-    for (int k = 1; k < s.n_lstm; ++k) need = std::max(need, size_t(plan.t_out[k]) * s.lstm_hid[k] * kTile * sizeof(float));
-    if (need <= std::min(plan.bytes_a, plan.bytes_b)) {
-      mark_begin("lstm_l1_l2", st);
-      tc_pair_launch(s.lstm_in[0], in, bufs[1], d_packed_tc + packed_tc_off[0], d_packed_tc + packed_tc_off[1], plan.t_run[0], t_in,
-                     plan.t_out[1], n_tiles, sm_count, st);
-      mark_end(st);
-      in = bufs[1];
-      cur = 1;
-      t_in = plan.t_out[1];
-      l = 2;
-    }
-  }
-  for (; l < s.n_lstm; ++l) {
+  static const char* const kPairNames[kMaxLstmLayers] = {"lstm_l1_l2", "", "lstm_l3_l4", "", "lstm_l5_l6", "", ""};
+  for (int l = 0; l < s.n_lstm;) {
     const bool last = (l == s.n_lstm - 1);
     const bool pool = !last && (l % 2 == 1);
     float* out = bufs[cur ^ 1];
+    // An (un-pooled, pooled) pair of equally wide layers as one software-pipelined kernel when the shapes allow it
+    // (lstm_tc_pair.cuh); the first layer's output then never leaves the SM.
+    if (l % 2 == 0 && l + 2 < s.n_lstm && plan.t_run[l] == plan.t_run[l + 1] &&
+        tc_pair_supported(s.lstm_in[l], s.lstm_hid[l], s.lstm_in[l + 1], s.lstm_hid[l + 1])) {
+      mark_begin(kPairNames[l], st);
+      tc_pair_launch(s.lstm_in[l], s.lstm_hid[l], in, out, d_packed_tc + packed_tc_off[l], d_packed_tc + packed_tc_off[l + 1], plan.t_run[l], t_in,
+                     plan.t_out[l + 1], n_tiles, sm_count, st);
+      mark_end(st);
+      in = out;
+      cur ^= 1;
+      t_in = plan.t_out[l + 1];
+      l += 2;
+      continue;
+    }
     mark_begin(kNames[l], st);
     if (tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last))
       tc_launch(s.lstm_in[l], s.lstm_hid[l], pool, last, in, out, d_packed_tc + packed_tc_off[l], plan.t_run[l], t_in, plan.t_out[l], n_tiles,
@@ -316,6 +313,7 @@ void DeviceModel::run_stack(const StackPlan& plan, float* buf_a, float* buf_b, l
     in = out;
     cur ^= 1;
     t_in = plan.t_out[l];
+    ++l;
   }
   const float* p = d_params;
   mark_begin("head", st);

@@ -62,8 +62,8 @@ void tc_configure(int in, int hid, bool pool, bool last);
 void tc_launch(int in, int hid, bool pool, bool last, const float* x, float* y, const unsigned char* w, int T, int t_in, int t_out, long long n_tiles,
                int sm_count, cudaStream_t st, float* save = nullptr, float* amax = nullptr, int nsave = 5);   // save != nullptr: also store gates (IG / training forward)
 bool tc_pair_supported(int in0, int hid0, int in1, int hid1);
-void tc_pair_configure(int in0);
-void tc_pair_launch(int in0, const float* x, float* y, const unsigned char* w1, const unsigned char* w2, int T, int t_in, int t_out,
+void tc_pair_configure(int in0, int hid0);
+void tc_pair_launch(int in0, int hid0, const float* x, float* y, const unsigned char* w1, const unsigned char* w2, int T, int t_in, int t_out,
                     long long n_tiles, int sm_count, cudaStream_t st);
 void tc_repack_device(const float* W, const float* U, const float* bias, int in, int hid, unsigned char* out, cudaStream_t st);
 // Tensor-core LSTM backward (csrc/lstm_tc_bwd.cu).

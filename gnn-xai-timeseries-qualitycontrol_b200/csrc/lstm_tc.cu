@@ -13,6 +13,7 @@
 #include "lstm_tc.cuh"
 #include "lstm_tc_big.cuh"
 #include "lstm_tc_pair.cuh"
+#include "lstm_tc_wide.cuh"
 
 namespace gnnqc {
 namespace {
@@ -52,6 +53,20 @@ struct TcBigLaunch {
       GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
       std::fprintf(stderr, "[gnnqc] tc-big I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
     }
+    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
+    GNNQC_CUDA(cudaGetLastError());
+  }
+};
+
+// 64-unit layers, second version (lstm_tc_wide.cuh): input projection one step ahead, sixteen cell-update warps.
+template <int I, int H, bool POOL, bool SAVE>
+struct TcWideLaunch {
+  using Cfg = TcWideCfg<I, H>;
+  static auto kernel() { return lstm_tc_wide_kernel<I, H, POOL, SAVE>; }
+  static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
+  static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st,
+                     float* save, float* amax, int nsave) {
+    const long long grid = std::min<long long>((n_tiles + 1) / 2, sm_count);
     kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
     GNNQC_CUDA(cudaGetLastError());
   }
@@ -97,9 +112,34 @@ bool tc_big_case(TcOp op, const TcArgs& a) {
 
 bool tc_is_big(int hid) { return hid >= 64; }
 
+bool tc_wide_enabled() {   // GNNQC_TC_WIDE=0: the first-version kernel for the 64-unit layers (A/B)
+  static const bool on = [] { const char* e = std::getenv("GNNQC_TC_WIDE"); return !(e && std::strcmp(e, "0") == 0); }();
+  return on;
+}
+
+template <int I, int H, bool POOL>
+bool tc_wide_case(TcOp op, const TcArgs& a) {
+  if (op == TcOp::Configure) {
+    TcWideLaunch<I, H, POOL, false>::configure();
+    TcWideLaunch<I, H, POOL, true>::configure();
+  } else if (op == TcOp::Launch) {
+    if (a.save) TcWideLaunch<I, H, POOL, true>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax, a.nsave);
+    else TcWideLaunch<I, H, POOL, false>::launch(a.x, a.y, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, nullptr, nullptr, 5);
+  }
+  return true;
+}
+
 bool tc_dispatch(TcOp op, int in, int hid, bool pool, bool last, const TcArgs& a) {
-  if (in == 32 && hid == 64 && !pool && !last) return tc_big_case<32, 64, false, false>(op, a);
-  if (in == 64 && hid == 64 && pool && !last) return tc_big_case<64, 64, true, false>(op, a);
+  if (in == 32 && hid == 64 && !pool && !last) {
+    if (op == TcOp::Configure) tc_wide_case<32, 64, false>(op, a);
+    if (op != TcOp::Configure && tc_wide_enabled()) return tc_wide_case<32, 64, false>(op, a);
+    return tc_big_case<32, 64, false, false>(op, a);
+  }
+  if (in == 64 && hid == 64 && pool && !last) {
+    if (op == TcOp::Configure) tc_wide_case<64, 64, true>(op, a);
+    if (op != TcOp::Configure && tc_wide_enabled()) return tc_wide_case<64, 64, true>(op, a);
+    return tc_big_case<64, 64, true, false>(op, a);
+  }
   if (in == 64 && hid == 128 && !pool && last) return tc_big_case<64, 128, false, true>(op, a);
   if (last) return false;
 #define GNNQC_TC_CASE(I_, H_, POOL_) \
@@ -128,39 +168,43 @@ int tc_max_hidden() {
 }  // namespace
 
 namespace {
-template <int I>
+template <int I, int H>
 bool pair_case(TcOp op, const TcArgs& a, const unsigned char* w2) {
-  using Cfg = TcPairCfg<I>;
+  using Cfg = TcPairCfg<I, H>;
   if (op == TcOp::Configure) {
-    GNNQC_CUDA(cudaFuncSetAttribute(lstm_tc_pair_kernel<I>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+    GNNQC_CUDA(cudaFuncSetAttribute(lstm_tc_pair_kernel<I, H>, cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
   } else if (op == TcOp::Launch) {
     const long long grid = std::min<long long>(a.n_tiles, a.sm_count);
-    lstm_tc_pair_kernel<I><<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, a.st>>>(a.x, a.y, a.w, w2, a.T, a.t_in, a.t_out,
-                                                                                            static_cast<int>(a.n_tiles));
+    lstm_tc_pair_kernel<I, H><<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, a.st>>>(a.x, a.y, a.w, w2, a.T, a.t_in, a.t_out,
+                                                                                               static_cast<int>(a.n_tiles));
     GNNQC_CUDA(cudaGetLastError());
   }
   return true;
 }
-bool pair_dispatch(TcOp op, int in, const TcArgs& a, const unsigned char* w2) {
-  if (in == 2) return pair_case<2>(op, a, w2);
-  if (in == 3) return pair_case<3>(op, a, w2);
-  if (in == 18) return pair_case<18>(op, a, w2);
-  if (in == 19) return pair_case<19>(op, a, w2);
+bool pair_dispatch(TcOp op, int in, int hid, const TcArgs& a, const unsigned char* w2) {
+  if (hid == 16) {
+    if (in == 2) return pair_case<2, 16>(op, a, w2);
+    if (in == 3) return pair_case<3, 16>(op, a, w2);
+    if (in == 18) return pair_case<18, 16>(op, a, w2);
+    if (in == 19) return pair_case<19, 16>(op, a, w2);
+  }
+  if (hid == 32 && in == 16) return pair_case<16, 32>(op, a, w2);
   return false;
 }
 }  // namespace
 
-// Layers 1 and 2 of the stack (I -> 16, 16 -> 16 + pool) as one kernel (lstm_tc_pair.cuh).  GNNQC_TC_PAIR=0: two launches (A/B).
+// Two consecutive layers in -> hid -> hid (+ pool) as one software-pipelined kernel (lstm_tc_pair.cuh): layers 1+2 and 3+4
+// of the stack.  GNNQC_TC_PAIR=0: one launch per layer (A/B).
 bool tc_pair_supported(int in0, int hid0, int in1, int hid1) {
   static const bool off = [] { const char* e = std::getenv("GNNQC_TC_PAIR"); return e && std::strcmp(e, "0") == 0; }();
-  return !off && tc_max_hidden() >= 16 && hid0 == 16 && in1 == 16 && hid1 == 16 && pair_dispatch(TcOp::Query, in0, TcArgs(), nullptr);
+  return !off && tc_max_hidden() >= hid0 && in1 == hid0 && hid1 == hid0 && pair_dispatch(TcOp::Query, in0, hid0, TcArgs(), nullptr);
 }
-void tc_pair_configure(int in0) { pair_dispatch(TcOp::Configure, in0, TcArgs(), nullptr); }
-void tc_pair_launch(int in0, const float* x, float* y, const unsigned char* w1, const unsigned char* w2, int T, int t_in, int t_out,
+void tc_pair_configure(int in0, int hid0) { pair_dispatch(TcOp::Configure, in0, hid0, TcArgs(), nullptr); }
+void tc_pair_launch(int in0, int hid0, const float* x, float* y, const unsigned char* w1, const unsigned char* w2, int T, int t_in, int t_out,
                     long long n_tiles, int sm_count, cudaStream_t st) {
   TcArgs a;
   a.x = x; a.y = y; a.w = w1; a.T = T; a.t_in = t_in; a.t_out = t_out; a.n_tiles = n_tiles; a.sm_count = sm_count; a.st = st;
-  if (!pair_dispatch(TcOp::Launch, in0, a, w2)) throw std::invalid_argument("no fused tensor-core kernel for this first layer");
+  if (!pair_dispatch(TcOp::Launch, in0, hid0, a, w2)) throw std::invalid_argument("no fused tensor-core kernel for this pair of layers");
 }
 
 bool tc_layer_supported(int in, int hid, bool pool, bool last) {

@@ -144,7 +144,7 @@ __device__ __forceinline__ void split8(const float (&v)[8], uint4& hi, uint4& lo
 // exponent inserted with an integer add.
 __host__ __device__ constexpr float tc_gate_scale(int gate) { return gate == 2 ? -2.8853900817779268f : -1.4426950408889634f; }
 #ifndef GNNQC_POLY_EXPS
-#define GNNQC_POLY_EXPS 2
+#define GNNQC_POLY_EXPS 1
 #endif
 constexpr int kPolyExps = GNNQC_POLY_EXPS;
 
