@@ -64,29 +64,42 @@ def _bce_from_scores(p, y, class_weights):
     return float(np.mean(w * -(y * np.log(p) + (1 - y) * np.log(1 - p))))
 
 
+def _device_of(native):
+    return torch.device("cuda", native.device) if native.device is not None and native.device >= 0 else torch.device("cpu")
+
+
 def train_step(native, inputs, labels, class_weights, lr):
     """One optimisation step on one global batch; returns the (global) loss.  Works for one process
     or for every rank of a torch.distributed group (each rank passes the same global batch and
-    works on its own shard)."""
+    works on its own shard).  A rank whose shard is empty (the last, partial batch of an epoch can hold
+    fewer windows than there are ranks; Keras' fit trains on it too) skips the device calls and
+    contributes zeros to both all-reduces, so the collectives stay matched on every rank."""
     rank, world_size = dp.world()
-    dev = torch.device("cuda", native.device)
+    dev = _device_of(native)
     cw = (class_weights[0], class_weights[1]) if class_weights else (1.0, 1.0)
     labels = torch.as_tensor(labels).to(torch.int64)
     if native.has_gcn:
         B = inputs["anom"].shape[0]
         sub, lab = dp.shard_cml_batch(inputs, labels, rank, world_size)
+        empty = sub["anom"].shape[0] == 0
         sub = {k: (v.to(dev, non_blocking=True) if isinstance(v, torch.Tensor) else v) for k, v in sub.items()}
-        moments = native.train_moments_cml(sub["features"])
+        moments = torch.zeros(6, dtype=torch.float64, device=dev) if empty else native.train_moments_cml(sub["features"])
         dp.all_reduce_sum(moments)
-        rvec = native.train_grads_cml(sub["features"], sub["anom"], sub["edges"], sub["node_off"].to(torch.int32), sub["edge_off"],
-                                      lab.to(dev), moments, cw, global_batch=B, n_nodes_total=sub["n_nodes_total"])
+        if empty:
+            rvec = torch.zeros(native.train_vector_len(), dtype=torch.float32, device=dev)
+        else:
+            rvec = native.train_grads_cml(sub["features"], sub["anom"], sub["edges"], sub["node_off"].to(torch.int32), sub["edge_off"],
+                                          lab.to(dev), moments, cw, global_batch=B, n_nodes_total=sub["n_nodes_total"])
         dp.all_reduce_sum(rvec)
         native.train_apply(rvec, moments, lr)
     else:
         x = torch.as_tensor(inputs)
         B = x.shape[0]
         xs, lab = dp.shard_seq_batch(x, labels, rank, world_size)
-        rvec = native.train_grads_seq(xs.to(dev, dtype=torch.float32), lab.to(dev), cw, global_batch=B)
+        if xs.shape[0] == 0:
+            rvec = torch.zeros(native.train_vector_len(), dtype=torch.float32, device=dev)
+        else:
+            rvec = native.train_grads_seq(xs.to(dev, dtype=torch.float32), lab.to(dev), cw, global_batch=B)
         dp.all_reduce_sum(rvec)
         native.train_apply(rvec, None, lr)
     return float(rvec[-1].item())

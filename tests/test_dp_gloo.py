@@ -102,3 +102,58 @@ def test_schedule_and_class_weights_follow_the_reference_rules():
     assert w == {0: 8 / 6, 1: 2 * 8 / 2}
     mc.weight_classes.use = False
     assert fit_model.calculate_weights(mc, []) is None
+
+
+class _FakeNative:
+    """Stands in for NativeModel on the CPU: 'gradients' are plain sums over the shard, so the data-parallel result
+    is known, and the device entry points refuse empty shards exactly like libgnnqc does (GNNQC_ERR_ARG)."""
+    device = None
+
+    def __init__(self, has_gcn):
+        self.has_gcn = has_gcn
+        self.applied = None
+
+    def train_vector_len(self):
+        return 4
+
+    def train_moments_cml(self, features):
+        assert features.shape[0] > 0, "gnnqc_train_moments_cml rejects n_rows <= 0"
+        return torch.tensor([features.sum().item(), 0, 0, 0, 0, float(features.shape[0])], dtype=torch.float64)
+
+    def train_grads_cml(self, features, anom, edges, node_off, edge_off, labels, moments, cw, global_batch=None, n_nodes_total=None):
+        assert anom.shape[0] > 0, "gnnqc_train_grads_cml rejects B <= 0"
+        return torch.tensor([anom.sum().item(), float(anom.shape[0]), labels.sum().item(), anom.shape[0] / global_batch], dtype=torch.float32)
+
+    def train_grads_seq(self, x, labels, cw, global_batch=None):
+        assert x.shape[0] > 0, "gnnqc_train_grads_seq rejects B <= 0"
+        return torch.tensor([x.sum().item(), float(x.shape[0]), labels.sum().item(), x.shape[0] / global_batch], dtype=torch.float32)
+
+    def train_apply(self, rvec, moments, lr):
+        self.applied = (rvec.clone(), None if moments is None else moments.clone())
+
+
+def _small_batch_worker(rank, world_size, port, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world_size)
+    try:
+        batch = synth.make_cml_batch(1, seed=3)            # one window for two ranks: rank 1's shard is empty
+        gcn, base = _FakeNative(True), _FakeNative(False)
+        loss_g = fit_model.train_step(gcn, batch, torch.tensor([1]), {0: 1, 1: 5}, 1e-4)
+        loss_b = fit_model.train_step(base, batch["anom"], torch.tensor([1]), None, 1e-4)
+        out[rank] = (gcn.applied[0].numpy(), gcn.applied[1].numpy(), base.applied[0].numpy(), loss_g, loss_b)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_a_batch_smaller_than_the_world_does_not_hang():
+    port = _free_port()
+    out = mp.Manager().dict()
+    mp.spawn(_small_batch_worker, args=(2, port, out), nprocs=2, join=True)
+    batch = synth.make_cml_batch(1, seed=3)
+    for rank in (0, 1):                                     # both ranks applied the same, full-batch reduction
+        g, m, b, loss_g, loss_b = out[rank]
+        np.testing.assert_allclose(g, [batch["anom"].sum().item(), 1, 1, 1.0], rtol=1e-6)
+        np.testing.assert_allclose(m[[0, 5]], [batch["features"].sum().item(), batch["features"].shape[0]], rtol=1e-6)
+        np.testing.assert_allclose(b, [batch["anom"].sum().item(), 1, 1, 1.0], rtol=1e-6)
+        assert loss_g == loss_b == 1.0
