@@ -256,10 +256,11 @@ int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_de
   });
 }
 
-int64_t gnnqc_train_vector_len(const gnnqc_model* m) { return m ? m->dm.host.spec.n_params + 81 : 0; }
+int64_t gnnqc_train_vector_len(const gnnqc_model* m) { return m ? m->dm.host.spec.n_params + 97 : 0; }
 
 int gnnqc_train_moments_cml(gnnqc_model* m, const float* features_dev, int64_t n_rows, double* moments_dev, void* stream) {
   if (int rc = need_device(m, "gnnqc_train_moments_cml")) return rc;
+  if (!m->dm.host.spec.has_gcn || m->dm.host.spec.soilnet) return fail(GNNQC_ERR_STATE, "gnnqc_train_moments_cml: model is not a CML GCNClassifier");
   if (!features_dev || !moments_dev || n_rows <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_train_moments_cml: bad argument");
   return guarded([&] { m->dm.train_moments(features_dev, n_rows, moments_dev, static_cast<cudaStream_t>(stream)); });
 }
@@ -280,10 +281,34 @@ int gnnqc_train_grads_cml(gnnqc_model* m, const float* features_dev, const float
   });
 }
 
+int gnnqc_train_moments_soilnet(gnnqc_model* m, const float* features_dev, int64_t n_rows, double* moments_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_train_moments_soilnet")) return rc;
+  if (!m->dm.host.spec.has_gcn || !m->dm.host.spec.soilnet) return fail(GNNQC_ERR_STATE, "gnnqc_train_moments_soilnet: model is not a SoilNet GCNClassifier");
+  if (!features_dev || !moments_dev || n_rows <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_train_moments_soilnet: bad argument");
+  return guarded([&] { m->dm.train_moments(features_dev, n_rows, moments_dev, static_cast<cudaStream_t>(stream)); });
+}
+
+int gnnqc_train_grads_soilnet(gnnqc_model* m, const float* features_dev, const int64_t* edges_dev, const int32_t* node_off_dev,
+                              const int64_t* edge_off_dev, const int64_t* labels_dev, int64_t B, int32_t T, int64_t n_nodes_total,
+                              int64_t n_edges_total, const double* moments_dev, float class_weight_0, float class_weight_1,
+                              int64_t global_batch, float* rvec_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_train_grads_soilnet")) return rc;
+  if (!m->dm.host.spec.has_gcn || !m->dm.host.spec.soilnet) return fail(GNNQC_ERR_STATE, "gnnqc_train_grads_soilnet: model is not a SoilNet GCNClassifier");
+  if (B <= 0 || T <= 0 || n_nodes_total <= 0 || n_edges_total < 0 || global_batch <= 0) return fail(GNNQC_ERR_ARG, "gnnqc_train_grads_soilnet: bad sizes");
+  if (!features_dev || !edges_dev || !node_off_dev || !edge_off_dev || !labels_dev || !moments_dev || !rvec_dev)
+    return fail(GNNQC_ERR_ARG, "gnnqc_train_grads_soilnet: null buffer");
+  return guarded([&] {
+    m->dm.train_grads(features_dev, nullptr, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
+                      reinterpret_cast<const long long*>(edge_off_dev), nullptr, reinterpret_cast<const long long*>(labels_dev), B, T,
+                      n_nodes_total, moments_dev, class_weight_0, class_weight_1, global_batch, rvec_dev, static_cast<cudaStream_t>(stream),
+                      n_edges_total);
+  });
+}
+
 int gnnqc_train_grads_seq(gnnqc_model* m, const float* x_dev, const int64_t* labels_dev, int64_t n_seq, int32_t T, float class_weight_0,
                           float class_weight_1, int64_t global_batch, float* rvec_dev, void* stream) {
   if (int rc = need_device(m, "gnnqc_train_grads_seq")) return rc;
-  if (m->dm.host.spec.has_gcn || m->dm.host.spec.soilnet) return fail(GNNQC_ERR_STATE, "gnnqc_train_grads_seq: model is not a CML BaselineClassifier");
+  if (m->dm.host.spec.has_gcn) return fail(GNNQC_ERR_STATE, "gnnqc_train_grads_seq: model is not a BaselineClassifier");
   if (n_seq <= 0 || T <= 0 || global_batch <= 0 || !x_dev || !labels_dev || !rvec_dev) return fail(GNNQC_ERR_ARG, "gnnqc_train_grads_seq: bad argument");
   return guarded([&] {
     m->dm.train_grads(nullptr, nullptr, nullptr, nullptr, nullptr, x_dev, reinterpret_cast<const long long*>(labels_dev), n_seq, T, 0, nullptr,

@@ -123,7 +123,7 @@ struct DeviceModel {
   void train_moments(const float* feat, long long n_rows, double* moments, cudaStream_t stream);
   void train_grads(const float* feat, const float* anom, const long long* edges, const int* node_off, const long long* edge_off,
                    const float* x_seq, const long long* labels, long long B, int T, long long n_nodes, const double* moments,
-                   float cw0, float cw1, long long global_batch, float* rvec, cudaStream_t stream);
+                   float cw0, float cw1, long long global_batch, float* rvec, cudaStream_t stream, long long n_edges = 0);
   void train_apply(float* rvec, const double* moments, float lr, cudaStream_t stream);
   // SoilNet GCN (csrc/soilnet.cu): scores [n_nodes], one per (window, sensor).
   void score_soilnet(const float* feat, const long long* edges, const int* node_off, const long long* edge_off, long long B,

@@ -8,12 +8,15 @@
 //   gnnqc_train_moments_cml   local feature moments (6 doubles)     -> all-reduce (sum)
 //   gnnqc_train_grads_*       local reduction vector (grads, raw GCN sums, loss) -> all-reduce (sum)
 //   gnnqc_train_apply         BN-backward closure, Adam, BN moving statistics, weight re-packing
+#include <cub/device/device_scan.cuh>
+
 #include <algorithm>
 #include <cmath>
 #include <cstring>
 
 #include "device_model.cuh"
 #include "lstm_bwd.cuh"
+#include "soil_kernels.cuh"
 #include "train_kernels.cuh"
 
 namespace gnnqc {
@@ -90,7 +93,9 @@ void dispatch(Op op, int in, int hid, bool pool, bool last, const LayerArgs& a) 
 #define GNNQC_CASE(I_, H_, POOL_, LAST_) \
   if (in == I_ && hid == H_ && pool == POOL_ && last == LAST_) return layer_op<I_, H_, POOL_, LAST_>(op, a);
   GNNQC_CASE(2, 16, false, false)
+  GNNQC_CASE(3, 16, false, false)
   GNNQC_CASE(18, 16, false, false)
+  GNNQC_CASE(19, 16, false, false)
   GNNQC_CASE(16, 16, true, false)
   GNNQC_CASE(16, 32, false, false)
   GNNQC_CASE(32, 32, true, false)
@@ -98,7 +103,7 @@ void dispatch(Op op, int in, int hid, bool pool, bool last, const LayerArgs& a) 
   GNNQC_CASE(64, 64, true, false)
   GNNQC_CASE(64, 128, false, true)
 #undef GNNQC_CASE
-  throw std::invalid_argument("training: no kernel for this LSTM layer shape (CML models only)");
+  throw std::invalid_argument("training: no kernel for this LSTM layer shape");
 }
 
 constexpr size_t kPartialBytes = size_t(64) << 20;
@@ -115,7 +120,6 @@ struct TrainState {
 
 void DeviceModel::configure_train_kernels() {
   const ModelSpec& s = host.spec;
-  if (s.soilnet) return;
   LayerArgs none;
   for (int l = 0; l < s.n_lstm; ++l) {
     const bool last = (l == s.n_lstm - 1);
@@ -159,13 +163,16 @@ void DeviceModel::sync_host_params() {
 
 void DeviceModel::train_moments(const float* feat, long long n_rows, double* moments, cudaStream_t st) {
   GNNQC_CUDA(cudaSetDevice(device));
-  GNNQC_CUDA(cudaMemsetAsync(moments, 0, 6 * sizeof(double), st));
+  const bool soil = host.spec.soilnet;       // three input channels: ten moments instead of six
+  const int n_mom = soil ? kSoilMoments : 6;
+  GNNQC_CUDA(cudaMemsetAsync(moments, 0, n_mom * sizeof(double), st));
   mark_begin("train_moments", st);
-  feat_moments_kernel<<<sm_count * 4, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), n_rows, moments);
+  if (soil) feat_moments3_kernel<<<sm_count * 4, 256, 0, st>>>(feat, n_rows, moments);
+  else feat_moments_kernel<<<sm_count * 4, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), n_rows, moments);
   GNNQC_CUDA(cudaGetLastError());
   mark_end(st);
   const double n = static_cast<double>(n_rows);
-  GNNQC_CUDA(cudaMemcpyAsync(moments + 5, &n, sizeof(double), cudaMemcpyHostToDevice, st));
+  GNNQC_CUDA(cudaMemcpyAsync(moments + n_mom - 1, &n, sizeof(double), cudaMemcpyHostToDevice, st));
   GNNQC_CUDA(cudaStreamSynchronize(st));  // `n` lives on this stack frame
 }
 
@@ -173,9 +180,12 @@ void DeviceModel::train_moments(const float* feat, long long n_rows, double* mom
 void DeviceModel::train_grads(const float* feat, const float* anom, const long long* edges, const int* node_off,
                               const long long* edge_off, const float* x_seq, const long long* labels, long long B, int T,
                               long long n_nodes, const double* moments, float cw0, float cw1, long long global_batch, float* rvec,
-                              cudaStream_t st) {
+                              cudaStream_t st, long long n_edges) {
   const ModelSpec& s = host.spec;
   const bool gcn = s.has_gcn;
+  const bool soil = gcn && s.soilnet;        // every sensor of every window is a sequence (create_model.py:224-231)
+  const long long n_win = B;
+  if (soil) B = n_nodes;                     // from here on B counts sequences
   GNNQC_CUDA(cudaSetDevice(device));
   refresh_tc();   // no-op inside a training loop: train_apply refreshes the operand tiles on the device
   TrainState* ts = train_state();
@@ -194,6 +204,17 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   size_t off = 0;
   auto take = [&off](size_t bytes) { size_t at = off; off += align_up(bytes, 256); return at; };
   const size_t o_deg = take(size_t(std::max<long long>(n_nodes, 1)) * 4), o_coef = take(size_t(std::max<long long>(n_nodes, 1)) * 4);
+  // SoilNet: CSR by receiving node (forward) and by sending node (backward)
+  const size_t nb = size_t(n_nodes + 1) * sizeof(int);
+  size_t scan_bytes = 0;
+  size_t o_csr[7] = {0}, o_scan = 0, o_nbr = 0, o_nbrT = 0;
+  if (soil) {
+    GNNQC_CUDA(cub::DeviceScan::ExclusiveSum(nullptr, scan_bytes, static_cast<int*>(nullptr), static_cast<int*>(nullptr), static_cast<int>(n_nodes + 1), st));
+    for (int k = 0; k < 7; ++k) o_csr[k] = take(nb);      // deg, cursor, row_ptr, seq_win, degT, cursorT, rowT_ptr
+    o_scan = take(scan_bytes);
+    o_nbr = take(size_t(std::max<long long>(n_edges, 1)) * sizeof(int));
+    o_nbrT = take(size_t(std::max<long long>(n_edges, 1)) * sizeof(int));
+  }
   const size_t o_x1 = take(size_t(nt) * plan.t_run[0] * s.lstm_in[0] * kTile * 4);
   size_t o_y[kMaxLstmLayers], o_save[kMaxLstmLayers], o_amax[kMaxLstmLayers], o_dz[kMaxLstmLayers];
   size_t g_bytes = 0;
@@ -210,16 +231,44 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   const size_t o_lossp = take(size_t(nt) * 4);
   const dim3 grid_fe(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
   const dim3 grid_feb(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + kFeBwdSteps - 1) / kFeBwdSteps));
-  const size_t o_gcnp = take(size_t(grid_feb.x) * grid_feb.y * kGcnSums * 4);
+  const size_t o_gcnp = take(size_t(grid_feb.x) * grid_feb.y * kRvecGcn * 4);
   const size_t o_part = take(kPartialBytes);
   char* base = static_cast<char*>(scratch(off));
   auto F = [base](size_t o) { return reinterpret_cast<float*>(base + o); };
 
-  GNNQC_CUDA(cudaMemsetAsync(rvec, 0, size_t(np + kGcnSums + 1) * sizeof(float), st));
+  GNNQC_CUDA(cudaMemsetAsync(rvec, 0, size_t(np + kRvecGcn + 1) * sizeof(float), st));
+  auto I32 = [base](size_t o) { return reinterpret_cast<int*>(base + o); };
 
   // ---- forward ----------------------------------------------------------------------------------
   const float* prm = d_params;
-  if (gcn) {
+  if (soil) {
+    int *deg = I32(o_csr[0]), *cursor = I32(o_csr[1]), *row_ptr = I32(o_csr[2]), *seq_win = I32(o_csr[3]);
+    int *degT = I32(o_csr[4]), *cursorT = I32(o_csr[5]), *rowT_ptr = I32(o_csr[6]);
+    GNNQC_CUDA(cudaMemsetAsync(deg, 0, nb, st));
+    GNNQC_CUDA(cudaMemsetAsync(cursor, 0, nb, st));
+    GNNQC_CUDA(cudaMemsetAsync(degT, 0, nb, st));
+    GNNQC_CUDA(cudaMemsetAsync(cursorT, 0, nb, st));
+    const unsigned wblocks = static_cast<unsigned>((n_win * 32 + 255) / 256), nblocks = static_cast<unsigned>((n_nodes + 255) / 256);
+    mark_begin("soil_csr", st);
+    soil_count_kernel<<<wblocks, 256, 0, st>>>(edges, node_off, edge_off, deg, seq_win, n_win, 0);
+    soil_count_kernel<<<wblocks, 256, 0, st>>>(edges, node_off, edge_off, degT, seq_win, n_win, 1);
+    GNNQC_CUDA(cub::DeviceScan::ExclusiveSum(base + o_scan, scan_bytes, deg, row_ptr, static_cast<int>(n_nodes + 1), st));
+    GNNQC_CUDA(cub::DeviceScan::ExclusiveSum(base + o_scan, scan_bytes, degT, rowT_ptr, static_cast<int>(n_nodes + 1), st));
+    soil_fill_kernel<<<wblocks, 256, 0, st>>>(edges, node_off, edge_off, row_ptr, cursor, I32(o_nbr), n_win, 0);
+    soil_fill_kernel<<<wblocks, 256, 0, st>>>(edges, node_off, edge_off, rowT_ptr, cursorT, I32(o_nbrT), n_win, 1);
+    soil_sort_kernel<<<nblocks, 256, 0, st>>>(row_ptr, deg, I32(o_nbr), n_nodes);
+    soil_sort_kernel<<<nblocks, 256, 0, st>>>(rowT_ptr, degT, I32(o_nbrT), n_nodes);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
+    bn_prepare3_kernel<<<1, 32, 0, st>>>(prm + s.off_gcn_kernel, prm + s.off_gcn_bias, prm + s.off_prelu, prm + s.off_bn_gamma,
+                                         prm + s.off_bn_beta, moments, s.bn_eps, ts->folded, ts->stats);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_begin("train_frontend", st);
+    soil_frontend_devparam_kernel<<<grid_fe, 256, 0, st>>>(feat, node_off, seq_win, row_ptr, deg, I32(o_nbr), ts->folded, F(o_x1), 0, B, T,
+                                                          plan.t_run[0]);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
+  } else if (gcn) {
     GNNQC_CUDA(cudaMemsetAsync(base + o_deg, 0, size_t(n_nodes) * 4, st));
     mark_begin("cml_node_coef", st);
     cml_node_coef_kernel<<<static_cast<unsigned>((B * 32 + 255) / 256), 256, 0, st>>>(edges, node_off, edge_off, reinterpret_cast<int*>(base + o_deg), F(o_coef), B);
@@ -235,7 +284,8 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     mark_end(st);
   } else {
     mark_begin("seq_to_tiles", st);
-    seq_to_tiles_kernel<2><<<grid_fe, 256, 0, st>>>(x_seq, F(o_x1), B, T, plan.t_run[0]);
+    if (s.lstm_in[0] == 3) seq_to_tiles_kernel<3><<<grid_fe, 256, 0, st>>>(x_seq, F(o_x1), B, T, plan.t_run[0]);
+    else seq_to_tiles_kernel<2><<<grid_fe, 256, 0, st>>>(x_seq, F(o_x1), B, T, plan.t_run[0]);
     GNNQC_CUDA(cudaGetLastError());
     mark_end(st);
   }
@@ -322,7 +372,16 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     wgrad("wgrad_dense", F(o_head), ht, 0, D, F(o_head) + 3LL * D * kTile, ht, 0, D, 1, 1, rvec + s.off_d2_w, rvec + s.off_d2_b);
     wgrad("wgrad_dense", F(o_head) + 1LL * D * kTile, ht, 0, D, F(o_head) + 4LL * D * kTile, ht, 0, 1, 1, 1, rvec + s.off_out_w, rvec + s.off_out_b);
   }
-  if (gcn) {
+  if (soil) {
+    mark_begin("train_frontend_bwd", st);
+    soil_frontend_train_bwd_kernel<<<grid_feb, 256, 0, st>>>(feat, node_off, I32(o_csr[3]), I32(o_csr[6]), I32(o_csr[4]), I32(o_nbrT), I32(o_csr[0]),
+                                                            prm + s.off_gcn_kernel, prm + s.off_gcn_bias, ts->folded, ts->stats, s.bn_eps, dx1,
+                                                            F(o_gcnp), B, T, plan.t_run[0]);
+    GNNQC_CUDA(cudaGetLastError());
+    mark_end(st);
+    sum_partials_kernel<<<1, 128, 0, st>>>(F(o_gcnp), static_cast<long long>(grid_feb.x) * grid_feb.y, kSoilGcnSums, rvec + np);
+    GNNQC_CUDA(cudaGetLastError());
+  } else if (gcn) {
     mark_begin("train_frontend_bwd", st);
     cml_frontend_train_bwd_kernel<<<grid_feb, 256, 0, st>>>(reinterpret_cast<const float2*>(feat), F(o_coef), node_off, prm + s.off_gcn_kernel,
                                                            prm + s.off_gcn_bias, ts->folded, ts->stats, s.bn_eps, dx1, F(o_gcnp), B, T,
@@ -332,7 +391,7 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     sum_partials_kernel<<<1, 128, 0, st>>>(F(o_gcnp), static_cast<long long>(grid_feb.x) * grid_feb.y, kGcnSums, rvec + np);
     GNNQC_CUDA(cudaGetLastError());
   }
-  sum_partials_kernel<<<1, 128, 0, st>>>(F(o_lossp), nt, 1, rvec + np + kGcnSums);
+  sum_partials_kernel<<<1, 128, 0, st>>>(F(o_lossp), nt, 1, rvec + np + kRvecGcn);
   GNNQC_CUDA(cudaGetLastError());
 }
 
@@ -345,7 +404,8 @@ void DeviceModel::train_apply(float* rvec, const double* moments, float lr, cuda
   if (s.has_gcn) {
     if (!moments) throw std::invalid_argument("gnnqc_train_apply: a GCN model needs the (global) feature moments");
     GcnOffsets o{s.off_gcn_kernel, s.off_gcn_bias, s.off_prelu, s.off_bn_gamma, s.off_bn_beta, s.off_bn_mean, s.off_bn_var};
-    gcn_finalize_kernel<<<1, 32, 0, st>>>(rvec, np, d_params, o, moments, ts->stats, s.bn_eps);
+    if (s.soilnet) gcn_finalize3_kernel<<<1, 32, 0, st>>>(rvec, np, d_params, o, moments, ts->stats, s.bn_eps);
+    else gcn_finalize_kernel<<<1, 32, 0, st>>>(rvec, np, d_params, o, moments, ts->stats, s.bn_eps);
     GNNQC_CUDA(cudaGetLastError());
     skip_lo = s.off_bn_mean;
     skip_hi = s.off_bn_var + kGcnChannels;

@@ -371,6 +371,157 @@ static __global__ void __launch_bounds__(256) cml_frontend_train_bwd_kernel(cons
   }
 }
 
+// ---- SoilNet (three input channels) -------------------------------------------------------------------------------
+// The same closure with F = 3: z = x W + b is linear in the three channels, so the batch statistics over all node
+// rows follow from nine moments, moments = {Sx0, Sx1, Sx2, Sx00, Sx11, Sx22, Sx01, Sx02, Sx12, N} (double precision).
+constexpr int kSoilMoments = 10;
+static __global__ void __launch_bounds__(256) feat_moments3_kernel(const float* __restrict__ feat, long long n_rows, double* __restrict__ moments) {
+  double s[9] = {0, 0, 0, 0, 0, 0, 0, 0, 0};
+  for (long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x; i < n_rows; i += static_cast<long long>(gridDim.x) * blockDim.x) {
+    const double a = __ldg(feat + 3 * i), b = __ldg(feat + 3 * i + 1), c = __ldg(feat + 3 * i + 2);
+    s[0] += a; s[1] += b; s[2] += c; s[3] += a * a; s[4] += b * b; s[5] += c * c; s[6] += a * b; s[7] += a * c; s[8] += b * c;
+  }
+  __shared__ double red[9][8];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 9; ++k) {
+    double v = s[k];
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+    if (lane == 0) red[k][w] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < 9) {
+    double v = 0;
+    for (int i = 0; i < 8; ++i) v += red[threadIdx.x][i];
+    atomicAdd(&moments[threadIdx.x], v);
+  }
+}
+
+// S_x[f] and S_xx[f][g] out of the ten moments
+struct Moments3 {
+  double n, sx[3], sxx[3][3];
+  __device__ explicit Moments3(const double* m) {
+    n = m[9];
+    sx[0] = m[0]; sx[1] = m[1]; sx[2] = m[2];
+    sxx[0][0] = m[3]; sxx[1][1] = m[4]; sxx[2][2] = m[5];
+    sxx[0][1] = sxx[1][0] = m[6]; sxx[0][2] = sxx[2][0] = m[7]; sxx[1][2] = sxx[2][1] = m[8];
+  }
+};
+static __global__ void bn_prepare3_kernel(const float* __restrict__ w, const float* __restrict__ bias, const float* __restrict__ prelu,
+                                          const float* __restrict__ gamma, const float* __restrict__ beta, const double* __restrict__ m,
+                                          float eps, GcnFolded* __restrict__ folded, BnBatch* __restrict__ stats) {
+  const int c = threadIdx.x;
+  if (c >= kGcnChannelsDev) return;
+  const Moments3 mo(m);
+  const double b = bias[c];
+  double wf[3], lin = 0, quad = 0;
+  for (int f = 0; f < 3; ++f) wf[f] = w[f * kGcnChannelsDev + c];
+  for (int f = 0; f < 3; ++f) {
+    lin += wf[f] * mo.sx[f] / mo.n;
+    for (int g = 0; g < 3; ++g) quad += wf[f] * wf[g] * mo.sxx[f][g] / mo.n;
+  }
+  const double mu = lin + b;
+  double var = quad + 2.0 * b * lin + b * b - mu * mu;
+  if (var < 0) var = 0;
+  const double scale = gamma[c] / sqrt(var + eps);
+  for (int f = 0; f < 3; ++f) folded->a[f][c] = static_cast<float>(wf[f] * scale);
+  folded->c[c] = static_cast<float>((b - mu) * scale + beta[c]);
+  folded->alpha[c] = prelu[c];
+  stats->mu[c] = static_cast<float>(mu);
+  stats->var[c] = static_cast<float>(var);
+}
+
+// Raw sums of the SoilNet GeneralConv backward.  The front-end computes h_i = mean_{j in N(i)} prelu(y_j) for every
+// sensor i (y = BN output), so the gradient that reaches sensor j's activation is up_j = sum_{i : j in N(i)} dh_i / deg_i:
+// a gather over the TRANSPOSED adjacency (rows = sending node).  With dy = up * prelu'(y) the kernel accumulates over
+// all (sensor, t < t_run):
+//   sums[0..15] S_dy   [16..31] S_dy_zhat   [32..47] S_x0dy   [48..63] S_x1dy   [64..79] S_x2dy   [80..95] d prelu alpha
+// One thread per (sequence, step group); one partial row per CTA, summed afterwards in double in a fixed order.
+constexpr int kSoilGcnSums = 6 * kGcnChannelsDev;
+constexpr int kRvecGcn = kSoilGcnSums;            // reduction-vector slots reserved for the raw GCN sums (CML uses the first 80)
+static __global__ void __launch_bounds__(256) soil_frontend_train_bwd_kernel(const float* __restrict__ feat, const int* __restrict__ node_off,
+                                                                             const int* __restrict__ seq_win, const int* __restrict__ rowT_ptr,
+                                                                             const int* __restrict__ degT, const int* __restrict__ nbrT,
+                                                                             const int* __restrict__ deg, const float* __restrict__ w,
+                                                                             const float* __restrict__ bias, const GcnFolded* __restrict__ pp,
+                                                                             const BnBatch* __restrict__ stats, float eps,
+                                                                             const float* __restrict__ dx1, float* __restrict__ partial,
+                                                                             long long n_seq, int T, int t_run) {
+  __shared__ float red[kSoilGcnSums][8];
+  __shared__ float cst_s[9][kGcnChannelsDev];   // y = sum_f x_f ya_f + yc; z_hat = sum_f x_f za_f + zc; prelu slope
+  if (threadIdx.x < kGcnChannelsDev) {
+    const int c = threadIdx.x;
+    const float rstd = rsqrtf(stats->var[c] + eps);
+    for (int f = 0; f < 3; ++f) {
+      cst_s[f][c] = pp->a[f][c];
+      cst_s[4 + f][c] = w[f * kGcnChannelsDev + c] * rstd;
+    }
+    cst_s[3][c] = pp->c[c];
+    cst_s[7][c] = (bias[c] - stats->mu[c]) * rstd;
+    cst_s[8][c] = pp->alpha[c];
+  }
+  __syncthreads();
+  const int b = threadIdx.x & 63, tq = threadIdx.x >> 6;
+  const long long tile = blockIdx.x;
+  const long long s = tile * kTile + b;
+  const int t0 = blockIdx.y * kFeBwdSteps + tq * (kFeBwdSteps / 4);
+  constexpr int CH = kGcnChannelsDev + 3;
+  float acc[6][kGcnChannelsDev];
+#pragma unroll
+  for (int k = 0; k < 6; ++k)
+#pragma unroll
+    for (int c = 0; c < kGcnChannelsDev; ++c) acc[k][c] = 0.f;
+  if (s < n_seq) {
+    const int wdw = seq_win[s];
+    const int n0 = node_off[wdw], nn = node_off[wdw + 1] - n0;
+    const int me = static_cast<int>(s - n0), dT = degT[s], rp = rowT_ptr[s];
+#pragma unroll 1
+    for (int dt = 0; dt < kFeBwdSteps / 4; ++dt) {
+      const int t = t0 + dt;
+      if (t >= t_run) break;
+      float up[kGcnChannelsDev];
+#pragma unroll
+      for (int c = 0; c < kGcnChannelsDev; ++c) up[c] = 0.f;
+      for (int e = 0; e < dT; ++e) {                       // receivers of this sensor's activation (ascending order: deterministic)
+        const long long si = n0 + __ldg(nbrT + rp + e);
+        const float inv = 1.f / static_cast<float>(__ldg(deg + si));
+        const float* g = dx1 + (((si / kTile) * t_run + t) * CH) * kTile + (si % kTile);
+#pragma unroll
+        for (int c = 0; c < kGcnChannelsDev; ++c) up[c] = fmaf(__ldg(g + c * kTile), inv, up[c]);
+      }
+      const float* x = feat + (static_cast<long long>(n0) * T + static_cast<long long>(t) * nn + me) * 3;
+      const float x0 = __ldg(x), x1 = __ldg(x + 1), x2 = __ldg(x + 2);
+#pragma unroll
+      for (int c = 0; c < kGcnChannelsDev; ++c) {
+        const float y = fmaf(x0, cst_s[0][c], fmaf(x1, cst_s[1][c], fmaf(x2, cst_s[2][c], cst_s[3][c])));
+        const float zh = fmaf(x0, cst_s[4][c], fmaf(x1, cst_s[5][c], fmaf(x2, cst_s[6][c], cst_s[7][c])));
+        const float dy = up[c] * (y > 0.f ? 1.f : cst_s[8][c]);
+        acc[0][c] += dy;
+        acc[1][c] = fmaf(dy, zh, acc[1][c]);
+        acc[2][c] = fmaf(dy, x0, acc[2][c]);
+        acc[3][c] = fmaf(dy, x1, acc[3][c]);
+        acc[4][c] = fmaf(dy, x2, acc[4][c]);
+        acc[5][c] = fmaf(up[c], fminf(y, 0.f), acc[5][c]);
+      }
+    }
+  }
+  const int lane = threadIdx.x & 31, wp = threadIdx.x >> 5;
+#pragma unroll
+  for (int k = 0; k < 6; ++k)
+#pragma unroll
+    for (int c = 0; c < kGcnChannelsDev; ++c) {
+      float v = acc[k][c];
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_down_sync(0xffffffffu, v, o);
+      if (lane == 0) red[k * kGcnChannelsDev + c][wp] = v;
+    }
+  __syncthreads();
+  if (threadIdx.x < kSoilGcnSums) {
+    float v = 0.f;
+    for (int i = 0; i < 8; ++i) v += red[threadIdx.x][i];
+    partial[(static_cast<long long>(blockIdx.y) * gridDim.x + blockIdx.x) * kSoilGcnSums + threadIdx.x] = v;
+  }
+}
+
 static __global__ void __launch_bounds__(128) sum_partials_kernel(const float* __restrict__ partial, long long n_rows, int width,
                                                                   float* __restrict__ out) {
   const int c = blockIdx.x * blockDim.x + threadIdx.x;
@@ -409,6 +560,32 @@ static __global__ void gcn_finalize_kernel(float* __restrict__ rvec, long long n
   }
   rvec[o.bias + c] = 0.f;
   rvec[o.prelu + c] = raw[4 * kGcnChannelsDev + c];
+  rvec[o.gamma + c] = static_cast<float>(dgamma);
+  rvec[o.beta + c] = static_cast<float>(dbeta);
+}
+
+// The same closure for three input channels (raw sums laid out as in soil_frontend_train_bwd_kernel).
+static __global__ void gcn_finalize3_kernel(float* __restrict__ rvec, long long n_params, const float* __restrict__ params, GcnOffsets o,
+                                            const double* __restrict__ m, const BnBatch* __restrict__ stats, float eps) {
+  const int c = threadIdx.x;
+  if (c >= kGcnChannelsDev) return;
+  const float* raw = rvec + n_params;
+  const Moments3 mo(m);
+  double wf[3];
+  for (int f = 0; f < 3; ++f) wf[f] = params[o.kernel + f * kGcnChannelsDev + c];
+  const double b = params[o.bias + c];
+  const double mu = stats->mu[c], sigma = sqrt(static_cast<double>(stats->var[c]) + eps);
+  const double dbeta = raw[c], dgamma = raw[kGcnChannelsDev + c];
+  const double gos = params[o.gamma + c] / sigma;
+  for (int f = 0; f < 3; ++f) {
+    double sxz = b * mo.sx[f];
+    for (int g = 0; g < 3; ++g) sxz += wf[g] * mo.sxx[f][g];
+    const double sxzh = (sxz - mu * mo.sx[f]) / sigma;
+    const double sxdy = raw[(2 + f) * kGcnChannelsDev + c];
+    rvec[o.kernel + f * kGcnChannelsDev + c] = static_cast<float>(gos * (sxdy - dbeta / mo.n * mo.sx[f] - dgamma / mo.n * sxzh));
+  }
+  rvec[o.bias + c] = 0.f;
+  rvec[o.prelu + c] = raw[5 * kGcnChannelsDev + c];
   rvec[o.gamma + c] = static_cast<float>(dgamma);
   rvec[o.beta + c] = static_cast<float>(dbeta);
 }

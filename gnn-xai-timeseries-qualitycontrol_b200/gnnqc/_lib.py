@@ -88,6 +88,8 @@ def _load():
         "gnnqc_train_vector_len": (i64, [vp]),
         "gnnqc_train_moments_cml": (C.c_int, [vp, vp, i64, vp, vp]),
         "gnnqc_train_grads_cml": (C.c_int, [vp, vp, vp, vp, vp, vp, vp, i64, i32, i64, vp, C.c_float, C.c_float, i64, vp, vp]),
+        "gnnqc_train_moments_soilnet": (C.c_int, [vp, vp, i64, vp, vp]),
+        "gnnqc_train_grads_soilnet": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, i64, vp, C.c_float, C.c_float, i64, vp, vp]),
         "gnnqc_train_grads_seq": (C.c_int, [vp, vp, vp, i64, i32, C.c_float, C.c_float, i64, vp, vp]),
         "gnnqc_train_apply": (C.c_int, [vp, vp, vp, C.c_float, vp]),
         "gnnqc_score_scratch_bytes": (i64, [vp, i64, i32]),

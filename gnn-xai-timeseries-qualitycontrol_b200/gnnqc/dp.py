@@ -40,6 +40,26 @@ def shard_cml_batch(batch, labels, rank, world_size):
     return sub, labels[lo:hi]
 
 
+def shard_soil_batch(batch, labels, rank, world_size):
+    """Slice an offsets-layout SoilNet batch to this rank's WINDOWS (a window's sensors share one graph, so windows
+    stay whole); labels are per (window, sensor)."""
+    no, eo = batch["node_off"], batch["edge_off"]
+    B = no.numel() - 1
+    T = int(batch["T"])
+    lo, hi = shard_range(B, rank, world_size)
+    n0, n1 = int(no[lo]), int(no[hi])
+    e0, e1 = int(eo[lo]), int(eo[hi])
+    sub = {
+        "features": batch["features"][n0 * T: n1 * T],
+        "edges": batch["edges"][e0:e1],
+        "node_off": (no[lo: hi + 1] - no[lo]).contiguous(),
+        "edge_off": (eo[lo: hi + 1] - eo[lo]).contiguous(),
+        "n_nodes_total": n1 - n0,
+        "T": T,
+    }
+    return sub, labels[n0:n1]
+
+
 def shard_seq_batch(x, labels, rank, world_size):
     lo, hi = shard_range(x.shape[0], rank, world_size)
     return x[lo:hi], labels[lo:hi]

@@ -281,6 +281,36 @@ class NativeModel:
                                         self._stream()))
         return rvec
 
+    def train_moments_soilnet(self, features):
+        """Local feature moments of a SoilNet batch (cuda f64 [10]); all-reduce(sum) them across ranks before use."""
+        torch = _torch()
+        features = self._dev_tensor(features, torch.float32, "features")
+        out = torch.empty(10, dtype=torch.float64, device=features.device)
+        check(lib.gnnqc_train_moments_soilnet(self._h, features.data_ptr(), features.shape[0], out.data_ptr(), self._stream()))
+        return out
+
+    def train_grads_soilnet(self, features, edges, node_off, edge_off, labels, T, moments, class_weights=(1.0, 5.0), global_batch=None,
+                            n_nodes_total=None):
+        """This rank's reduction vector for a SoilNet GCN batch; labels: cuda i64 [sum N_b], one per (window, sensor)."""
+        torch = _torch()
+        features = self._dev_tensor(features, torch.float32, "features")
+        edges = self._dev_tensor(edges, torch.int64, "edges")
+        node_off = self._dev_tensor(node_off, torch.int32, "node_off")
+        edge_off = self._dev_tensor(edge_off, torch.int64, "edge_off")
+        labels = self._dev_tensor(labels, torch.int64, "labels")
+        moments = self._dev_tensor(moments, torch.float64, "moments")
+        B = node_off.numel() - 1
+        if n_nodes_total is None:
+            n_nodes_total = int(node_off[-1].item())
+        if labels.numel() != n_nodes_total or features.shape[0] != n_nodes_total * int(T):
+            raise ValueError("expected features [sum(N_b)*T, 3] and one label per (window, sensor)")
+        rvec = torch.empty(self.train_vector_len(), dtype=torch.float32, device=features.device)
+        check(lib.gnnqc_train_grads_soilnet(self._h, features.data_ptr(), edges.data_ptr(), node_off.data_ptr(), edge_off.data_ptr(),
+                                            labels.data_ptr(), B, int(T), n_nodes_total, edges.shape[0], moments.data_ptr(),
+                                            float(class_weights[0]), float(class_weights[1]), int(global_batch or n_nodes_total),
+                                            rvec.data_ptr(), self._stream()))
+        return rvec
+
     def train_grads_seq(self, x, labels, class_weights=(1.0, 5.0), global_batch=None):
         torch = _torch()
         x = self._dev_tensor(x, torch.float32, "x")

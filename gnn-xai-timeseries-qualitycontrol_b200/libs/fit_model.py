@@ -78,7 +78,21 @@ def train_step(native, inputs, labels, class_weights, lr):
     dev = _device_of(native)
     cw = (class_weights[0], class_weights[1]) if class_weights else (1.0, 1.0)
     labels = torch.as_tensor(labels).to(torch.int64)
-    if native.has_gcn:
+    if native.has_gcn and native.soilnet:
+        n_seq = int(inputs["node_off"][-1])                      # the loss is the mean over all sensor-sequences of the batch
+        sub, lab = dp.shard_soil_batch(inputs, labels, rank, world_size)
+        empty = sub["n_nodes_total"] == 0
+        sub = {k: (v.to(dev, non_blocking=True) if isinstance(v, torch.Tensor) else v) for k, v in sub.items()}
+        moments = torch.zeros(10, dtype=torch.float64, device=dev) if empty else native.train_moments_soilnet(sub["features"])
+        dp.all_reduce_sum(moments)
+        if empty:
+            rvec = torch.zeros(native.train_vector_len(), dtype=torch.float32, device=dev)
+        else:
+            rvec = native.train_grads_soilnet(sub["features"], sub["edges"], sub["node_off"].to(torch.int32), sub["edge_off"], lab.to(dev),
+                                              sub["T"], moments, cw, global_batch=n_seq, n_nodes_total=sub["n_nodes_total"])
+        dp.all_reduce_sum(rvec)
+        native.train_apply(rvec, moments, lr)
+    elif native.has_gcn:
         B = inputs["anom"].shape[0]
         sub, lab = dp.shard_cml_batch(inputs, labels, rank, world_size)
         empty = sub["anom"].shape[0] == 0

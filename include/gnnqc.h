@@ -257,13 +257,17 @@ int gnnqc_roc_auc(int device, const float* scores_dev, const int64_t* labels_dev
  * (libs/fit_model.py:61-112): loss 'binary_crossentropy' on the sigmoid output (Keras evaluates it
  * from the logits), class_weight {0: w0, 1: w1} as per-sample weights, mean over the batch, Adam
  * (lr; beta 0.9/0.999, epsilon 1e-7), BatchNormalization of the GeneralConv in training mode
- * (batch statistics over all node rows, moving statistics with momentum 0.99).  CML models only.
+ * (batch statistics over all node rows, moving statistics with momentum 0.99).  All four models:
+ * the SoilNet GCN trains through the 'soilnet' branch of GCNClassifier.call (libs/create_model.py:224-231:
+ * per-sensor neighbour mean, concat, graph_reshape) with one label per (window, sensor)
+ * (libs/preprocessing_functions.py:861-897); the baselines through gnnqc_train_grads_seq.
  *
  * The step is split where data-parallel ranks must sum across GPUs - the only exchange steps:
  *   1. gnnqc_train_moments_cml: moments_dev f64[6] = {sum x0, sum x1, sum x0^2, sum x1^2,
  *      sum x0 x1, row count} of this rank's features          -> all-reduce(sum) over ranks
+ *      (gnnqc_train_moments_soilnet: f64[10] = {sum x0, x1, x2, x0^2, x1^2, x2^2, x0x1, x0x2, x1x2, row count})
  *   2. gnnqc_train_grads_*: rvec_dev f32[gnnqc_train_vector_len()] = this rank's gradients in
- *      flat-parameter order, 80 raw GeneralConv/BatchNorm sums, and the loss in the last slot;
+ *      flat-parameter order, 96 slots of raw GeneralConv/BatchNorm sums (CML uses 80), and the loss in the last slot;
  *      everything is already divided by global_batch            -> all-reduce(sum) over ranks
  *   3. gnnqc_train_apply: closes the BatchNorm backward with the global sums, applies Adam to the
  *      device copy of the parameters, moves the BN statistics, refreshes the packed weights.
@@ -276,6 +280,17 @@ int gnnqc_train_grads_cml(gnnqc_model* m, const float* features_dev, const float
                           const int64_t* edge_off_dev, const int64_t* labels_dev, int64_t B, int32_t T,
                           int64_t n_nodes_total, const double* moments_dev, float class_weight_0,
                           float class_weight_1, int64_t global_batch, float* rvec_dev, void* stream);
+/* SoilNet GCNClassifier: features_dev f32 [sum N_b * T, 3] rows (window, t, sensor), edges / offsets as for
+ * gnnqc_score_soilnet, labels_dev i64 [sum N_b] in (window, sensor) order; global_batch counts SEQUENCES
+ * (the reference's loss is the mean over all sensor-sequences of the batch). */
+int gnnqc_train_moments_soilnet(gnnqc_model* m, const float* features_dev, int64_t n_rows,
+                                double* moments_dev, void* stream);
+int gnnqc_train_grads_soilnet(gnnqc_model* m, const float* features_dev, const int64_t* edges_dev,
+                              const int32_t* node_off_dev, const int64_t* edge_off_dev,
+                              const int64_t* labels_dev, int64_t B, int32_t T, int64_t n_nodes_total,
+                              int64_t n_edges_total, const double* moments_dev, float class_weight_0,
+                              float class_weight_1, int64_t global_batch, float* rvec_dev, void* stream);
+/* BaselineClassifier of either dataset: x_dev f32 [n_seq, T, 2 or 3] (SoilNet: the graph_reshape'd sensor series). */
 int gnnqc_train_grads_seq(gnnqc_model* m, const float* x_dev, const int64_t* labels_dev, int64_t n_seq,
                           int32_t T, float class_weight_0, float class_weight_1, int64_t global_batch,
                           float* rvec_dev, void* stream);

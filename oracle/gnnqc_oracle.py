@@ -329,6 +329,24 @@ def train_grads_cml(features, anom, edge_index, sample_indices, labels, named, c
     return loss, grads, stats["mean"], stats["var"]
 
 
+def train_grads_soilnet(features, edge_index, sample_indices, batch_size, seq_len, labels, named, class_weights=(1.0, 5.0), dtype=torch.float64):
+    """One training-mode forward/backward of the SoilNet GCN model (create_model.py:224-231): one label and one loss
+    term per (window, sensor), BatchNorm statistics over all node rows.  Returns (loss, grads, batch mean, batch variance)."""
+    w = {k: torch.as_tensor(np.asarray(v)).to(dtype).clone().requires_grad_(k not in TRAINABLE_EXCLUDE) for k, v in named.items()}
+    stats = {}
+
+    def fwd(w):
+        f = features.to(dtype)
+        x, mu, var = _general_conv_train(f, edge_index, w)
+        stats["mean"], stats["var"] = mu, var
+        x = torch.cat([x, f], dim=-1)
+        x = graph_reshape(x, sample_indices, batch_size, seq_len)
+        return _logits_head(time_layer(x, w, "time_layer/"), w, "dense")
+
+    loss, grads = loss_and_grads(w, labels, class_weights, fwd)
+    return loss, grads, stats["mean"], stats["var"]
+
+
 def train_grads_baseline(x, labels, named, class_weights=(1.0, 5.0), dtype=torch.float64):
     w = {k: torch.as_tensor(np.asarray(v)).to(dtype).clone().requires_grad_(True) for k, v in named.items()}
     return loss_and_grads(w, labels, class_weights, lambda w: _logits_head(time_layer(x.to(dtype), w, ""), w, "dense1"))

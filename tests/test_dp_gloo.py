@@ -108,6 +108,7 @@ class _FakeNative:
     """Stands in for NativeModel on the CPU: 'gradients' are plain sums over the shard, so the data-parallel result
     is known, and the device entry points refuse empty shards exactly like libgnnqc does (GNNQC_ERR_ARG)."""
     device = None
+    soilnet = False
 
     def __init__(self, has_gcn):
         self.has_gcn = has_gcn

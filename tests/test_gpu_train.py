@@ -189,3 +189,83 @@ def test_device_refresh_of_tensor_core_operands_equals_host_packing():
         assert torch.equal(after_step, from_host)
     finally:
         m.close()
+
+
+# ---- SoilNet (create_model.py:224-231; one label per (window, sensor), preprocessing_functions.py:861-897) -------------
+@pytest.mark.parametrize("n_win,nodes,ragged", [(2, 9, False), (3, 14, True)])
+def test_soilnet_gcn_gradients_match_oracle(n_win, nodes, ragged):
+    m = NativeModel.load(os.path.join(MODELS, "model_soilnet"), device=0)
+    try:
+        batch = synth.make_soilnet_batch(n_win, seed=70 + n_win, n_nodes=nodes, ragged=ragged, min_nodes=5)
+        n_seq = int(batch["node_off"][-1])
+        labels = make_labels(n_seq, n_win)
+        b = cuda(batch)
+        mom = m.train_moments_soilnet(b["features"])
+        rvec = m.train_grads_soilnet(b["features"], b["edges"], b["node_off"], b["edge_off"], labels.cuda(), batch["T"], mom)
+        fin = rvec.clone()
+        m.train_apply(fin, mom, 1e-4)      # closes the BN backward: `fin` now holds the GeneralConv gradients too
+        got, loss = split_rvec(m, fin)
+        feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 3)
+        named = O.load_named(os.path.join(MODELS, "model_soilnet"))
+        oloss, ograds, mu, var = O.train_grads_soilnet(torch.tensor(feat), torch.tensor(idx), torch.tensor(samp), n_win, batch["T"], labels, named)
+        assert abs(loss - oloss.item()) <= 1e-5 * abs(oloss.item()) + 1e-7
+        check_grads(got, ograds, skip=("gcn_layer/bias",))
+        assert np.abs(got["gcn_layer/bias"]).max() == 0.0
+        new = m.named_params()
+        np.testing.assert_allclose(new["gcn_layer/batch_norm/moving_mean"], 0.99 * named["gcn_layer/batch_norm/moving_mean"] + 0.01 * mu.numpy(), rtol=1e-5, atol=1e-7)
+        np.testing.assert_allclose(new["gcn_layer/batch_norm/moving_variance"], 0.99 * named["gcn_layer/batch_norm/moving_variance"] + 0.01 * var.numpy(), rtol=1e-4, atol=1e-7)
+    finally:
+        m.close()
+
+
+def test_soilnet_baseline_gradients_match_oracle():
+    m = NativeModel.load(os.path.join(MODELS, "model_soilnet_baseline"), device=0)
+    try:
+        n = 40
+        x = synth.make_seq_batch(n, 3, 337, seed=9)
+        labels = make_labels(n, 4)
+        rvec = m.train_grads_seq(x.cuda(), labels.cuda())
+        got, loss = split_rvec(m, rvec)
+        oloss, ograds = O.train_grads_baseline(x, labels, O.load_named(os.path.join(MODELS, "model_soilnet_baseline")))
+        assert abs(loss - oloss.item()) <= 1e-5 * abs(oloss.item()) + 1e-7
+        check_grads(got, ograds)
+    finally:
+        m.close()
+
+
+def test_soilnet_loss_goes_down_and_windows_shard():
+    """A few optimiser steps on a fixed SoilNet batch, and the data-parallel decomposition by whole windows."""
+    from gnnqc import dp
+    m = NativeModel.load(os.path.join(MODELS, "model_soilnet"), device=0)
+    try:
+        batch = synth.make_soilnet_batch(4, seed=13, n_nodes=12)
+        n_seq = int(batch["node_off"][-1])
+        labels = make_labels(n_seq, 6)
+        b = cuda(batch)
+        mom = m.train_moments_soilnet(b["features"])
+        ref = m.train_grads_soilnet(b["features"], b["edges"], b["node_off"], b["edge_off"], labels.cuda(), batch["T"], mom)
+        total, gmom = None, None
+        for rank in range(2):
+            sub, lab = dp.shard_soil_batch(batch, labels, rank, 2)
+            sub = cuda(sub)
+            mm = m.train_moments_soilnet(sub["features"])
+            gmom = mm if gmom is None else gmom + mm
+        torch.testing.assert_close(gmom, mom, rtol=1e-12, atol=1e-9)
+        for rank in range(2):
+            sub, lab = dp.shard_soil_batch(batch, labels, rank, 2)
+            sub = cuda(sub)
+            r = m.train_grads_soilnet(sub["features"], sub["edges"], sub["node_off"], sub["edge_off"], lab.cuda(), batch["T"], gmom,
+                                      global_batch=n_seq, n_nodes_total=sub["n_nodes_total"])
+            total = r if total is None else total + r
+        assert (total - ref).abs().max().item() <= 2e-5 * ref.abs().max().item()
+        losses = []
+        for _ in range(8):
+            mom = m.train_moments_soilnet(b["features"])
+            rvec = m.train_grads_soilnet(b["features"], b["edges"], b["node_off"], b["edge_off"], labels.cuda(), batch["T"], mom)
+            losses.append(float(rvec[-1].item()))
+            m.train_apply(rvec, mom, 5e-4)
+        assert losses[-1] < losses[0]
+        s = m.score_soilnet(b["features"], b["edges"], b["node_off"], b["edge_off"], batch["T"])
+        assert torch.isfinite(s).all()
+    finally:
+        m.close()
