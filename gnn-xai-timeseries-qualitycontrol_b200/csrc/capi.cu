@@ -161,6 +161,7 @@ int gnnqc_model_set_params(gnnqc_model* m, const float* in_host, int64_t n) {
   if (n != m->dm.host.spec.n_params) return fail(GNNQC_ERR_ARG, "gnnqc_model_set_params: wrong length");
   return guarded([&] {
     std::memcpy(m->dm.host.params.data(), in_host, sizeof(float) * n);
+    m->dm.params_dirty = false;      // the host copy is authoritative again
     m->dm.upload();
   });
 }
@@ -203,6 +204,18 @@ int gnnqc_score_seq(gnnqc_model* m, const float* x_dev, int64_t n_seq, int32_t T
   });
 }
 
+int gnnqc_score_rows(gnnqc_model* m, const float* features_dev, const int32_t* node_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
+                     float* scores_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_score_rows")) return rc;
+  if (m->dm.host.spec.has_gcn) return fail(GNNQC_ERR_STATE, "gnnqc_score_rows: model is not a BaselineClassifier");
+  if (B < 0 || T <= 0 || n_nodes_total < 0 || B >= (int64_t(1) << 31)) return fail(GNNQC_ERR_ARG, "gnnqc_score_rows: bad B / T / n_nodes_total");
+  if (n_nodes_total > 0 && (!features_dev || !node_off_dev || !scores_dev)) return fail(GNNQC_ERR_ARG, "gnnqc_score_rows: null buffer");
+  return guarded([&] {
+    m->dm.refresh_tc();
+    m->dm.score_seq(features_dev, n_nodes_total, T, scores_dev, static_cast<cudaStream_t>(stream), node_off_dev, static_cast<int>(B));
+  });
+}
+
 int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom_dev, const int64_t* edges_dev,
                     const int32_t* node_off_dev, const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
                     float* scores_dev, void* stream) {
@@ -214,7 +227,6 @@ int gnnqc_score_cml(gnnqc_model* m, const float* features_dev, const float* anom
     return fail(GNNQC_ERR_ARG, "gnnqc_score_cml: null buffer");
   return guarded([&] {
     m->dm.refresh_tc();
-    m->dm.sync_host_params();
     m->dm.score_cml(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
                     reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, scores_dev,
                     static_cast<cudaStream_t>(stream));
@@ -233,7 +245,6 @@ int gnnqc_score_soilnet(gnnqc_model* m, const float* features_dev, const int64_t
     return fail(GNNQC_ERR_ARG, "gnnqc_score_soilnet: null buffer");
   return guarded([&] {
     m->dm.refresh_tc();
-    m->dm.sync_host_params();
     m->dm.score_soilnet(features_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
                         reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, n_edges_total, scores_dev,
                         static_cast<cudaStream_t>(stream));
@@ -249,7 +260,7 @@ int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_de
   if (B > 0 && (!features_dev || !anom_dev || !edges_dev || !node_off_dev || !edge_off_dev || !attr_features_dev || !attr_anom_dev || !scores_dev))
     return fail(GNNQC_ERR_ARG, "gnnqc_ig_cml: null buffer");
   return guarded([&] {
-    m->dm.sync_host_params();
+    m->dm.refresh_tc();
     m->dm.ig_cml(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
                  reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, m_steps, attr_features_dev, attr_anom_dev,
                  scores_dev, static_cast<cudaStream_t>(stream));

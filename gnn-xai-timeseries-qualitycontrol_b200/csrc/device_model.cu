@@ -72,6 +72,7 @@ DeviceModel::~DeviceModel() {
     cudaFree(d_packed_t);
     cudaFree(d_packed_tc);
     cudaFree(d_packed_tcb);
+    cudaFree(d_folded);
     cudaFree(d_scratch);
   }
 }
@@ -152,6 +153,7 @@ void DeviceModel::upload() {
   if (!d_packed_tcb) GNNQC_CUDA(cudaMalloc(&d_packed_tcb, total_tcb));
   GNNQC_CUDA(cudaMemcpy(d_packed_tcb, packed_tcb.data(), total_tcb, cudaMemcpyHostToDevice));
   tc_stale = false;
+  folded_valid = false;
 }
 
 void DeviceModel::refresh_tc() {
@@ -332,7 +334,7 @@ static size_t scratch_budget_bytes() {
 
 static inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-void DeviceModel::score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t st) {
+void DeviceModel::score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t st, const int* node_off, int n_windows) {
   if (n_seq <= 0) return;
   const ModelSpec& s = host.spec;
   GNNQC_CUDA(cudaSetDevice(device));
@@ -350,7 +352,11 @@ void DeviceModel::score_seq(const float* x, long long n_seq, int T, float* score
     dim3 grid(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
     const float* xs = x + seq0 * T * c_in;
     mark_begin("seq_to_tiles", st);
-    if (c_in == 2) seq_to_tiles_kernel<2><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
+    if (node_off) {   // rows in (window, t, node) order: graph_reshape happens in the tile builder
+      if (c_in == 3) rows_to_tiles_kernel<3><<<grid, 256, 0, st>>>(x, node_off, n_windows, buf_a, seq0, n_seq, T, plan.t_run[0]);
+      else if (c_in == 2) rows_to_tiles_kernel<2><<<grid, 256, 0, st>>>(x, node_off, n_windows, buf_a, seq0, n_seq, T, plan.t_run[0]);
+      else throw std::invalid_argument("row-layout scoring is for the baseline models (2 or 3 input channels)");
+    } else if (c_in == 2) seq_to_tiles_kernel<2><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
     else if (c_in == 3) seq_to_tiles_kernel<3><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
     else if (c_in == 18) seq_to_tiles_kernel<18><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
     else if (c_in == 19) seq_to_tiles_kernel<19><<<grid, 256, 0, st>>>(xs, buf_a, ns, T, plan.t_run[0]);
@@ -361,18 +367,34 @@ void DeviceModel::score_seq(const float* x, long long n_seq, int T, float* score
   }
 }
 
-static GcnFolded fold_gcn(const HostModel& m) {
-  const ModelSpec& s = m.spec;
-  const float* p = m.params.data();
-  GcnFolded f;
-  std::memset(&f, 0, sizeof(f));
-  for (int c = 0; c < kGcnChannels; ++c) {
-    const float scale = p[s.off_bn_gamma + c] / std::sqrt(p[s.off_bn_var + c] + s.bn_eps);
-    for (int k = 0; k < s.n_features; ++k) f.a[k][c] = p[s.off_gcn_kernel + k * kGcnChannels + c] * scale;
-    f.c[c] = (p[s.off_gcn_bias + c] - p[s.off_bn_mean + c]) * scale + p[s.off_bn_beta + c];
-    f.alpha[c] = p[s.off_prelu + c];
+// Same arithmetic on the host (parameters loaded or set from the host) and on the device (after an optimizer step).
+struct FoldOffsets { long long kernel, bias, prelu, gamma, beta, mean, var; int n_features; float eps; };
+__host__ __device__ inline void fold_channel(const float* p, const FoldOffsets& o, int c, GcnFolded* f) {
+  const float scale = p[o.gamma + c] / sqrtf(p[o.var + c] + o.eps);
+  for (int k = 0; k < 3; ++k) f->a[k][c] = k < o.n_features ? p[o.kernel + k * kGcnChannels + c] * scale : 0.f;
+  f->c[c] = fmaf(p[o.bias + c] - p[o.mean + c], scale, p[o.beta + c]);   // explicit fma: the same bits on the host and on the device
+  f->alpha[c] = p[o.prelu + c];
+}
+static __global__ void gcn_fold_kernel(const float* __restrict__ params, FoldOffsets o, GcnFolded* __restrict__ out) {
+  if (threadIdx.x < kGcnChannels) fold_channel(params, o, threadIdx.x, out);
+}
+
+const GcnFolded& DeviceModel::folded(cudaStream_t st) {
+  if (folded_valid) return folded_cache;
+  const ModelSpec& s = host.spec;
+  const FoldOffsets o{s.off_gcn_kernel, s.off_gcn_bias, s.off_prelu, s.off_bn_gamma, s.off_bn_beta, s.off_bn_mean, s.off_bn_var, s.n_features, s.bn_eps};
+  if (params_dirty && device >= 0) {
+    // the device copy is authoritative (train_apply): fold there, 320 bytes back, once per training -> scoring transition
+    if (!d_folded) GNNQC_CUDA(cudaMalloc(&d_folded, sizeof(GcnFolded)));
+    gcn_fold_kernel<<<1, 32, 0, st>>>(d_params, o, d_folded);
+    GNNQC_CUDA(cudaGetLastError());
+    GNNQC_CUDA(cudaMemcpyAsync(&folded_cache, d_folded, sizeof(GcnFolded), cudaMemcpyDeviceToHost, st));
+    GNNQC_CUDA(cudaStreamSynchronize(st));
+  } else {
+    for (int c = 0; c < kGcnChannels; ++c) fold_channel(host.params.data(), o, c, &folded_cache);
   }
-  return f;
+  folded_valid = true;
+  return folded_cache;
 }
 
 void DeviceModel::score_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
@@ -400,7 +422,7 @@ void DeviceModel::score_cml(const float* feat, const float* anom, const long lon
     GNNQC_CUDA(cudaGetLastError());
     mark_end(st);
   }
-  const GcnFolded folded = fold_gcn(host);
+  const GcnFolded folded = this->folded(st);
   for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
     const long long nt = std::min(chunk, n_tiles - t0);
     const long long win0 = t0 * kTile, nw = std::min<long long>(B - win0, nt * kTile);

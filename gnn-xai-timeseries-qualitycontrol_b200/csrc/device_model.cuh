@@ -110,12 +110,19 @@ struct DeviceModel {
   // x1: sequence tiles [n_tiles][plan.t_run[0]][lstm_in[0]][64] already in `buf_a`.
   void run_stack(const StackPlan& plan, float* buf_a, float* buf_b, long long n_tiles, long long n_seq,
                  float* scores, cudaStream_t stream);
-  void score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t stream);
+  void score_seq(const float* x, long long n_seq, int T, float* scores, cudaStream_t stream, const int* node_off = nullptr, int n_windows = 0);
   // Training (csrc/train.cu).  After train_apply the device copy of the parameters is the
   // authoritative one; sync_host_params() brings host.params up to date on demand.
   HostStage* host_stage = nullptr;
   TrainState* train = nullptr;
   bool params_dirty = false;
+  // BatchNorm (inference) folded into the GeneralConv projection, as the front-end kernels take it by value.  After a
+  // training step the device copy of the parameters is authoritative: the fold then runs on the device and 320 bytes
+  // come back once (not the whole parameter vector, and not on every scoring call).
+  GcnFolded folded_cache;
+  bool folded_valid = false;
+  GcnFolded* d_folded = nullptr;
+  const GcnFolded& folded(cudaStream_t stream);
   void configure_train_kernels();
   TrainState* train_state();
   void free_train_state();

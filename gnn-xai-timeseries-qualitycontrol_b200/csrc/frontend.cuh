@@ -4,6 +4,7 @@
 #include <cstdint>
 
 #include "lstm_fwd.cuh"
+#include "model_spec.h"
 
 namespace gnnqc {
 
@@ -97,12 +98,41 @@ static __global__ void __launch_bounds__(256) cml_node_coef_kernel(const long lo
   }
 }
 
-// BatchNorm (inference) folded into the GeneralConv projection: z = prelu(x0*a0 + x1*a1 (+ x2*a2) + c).
-struct GcnFolded {
-  float a[3][kGcnChannelsDev];
-  float c[kGcnChannelsDev];
-  float alpha[kGcnChannelsDev];
-};
+// ---- graph_reshape (libs/create_model.py:242-258) for the SoilNet baseline ---------------------
+// feat [sum_b N_b * T, C] rows in (window, t, node) order  ->  sequence tiles of the (window, node) sequences.
+// The window of a sequence is found by bisection of node_off (B is a few hundred at most).
+template <int C>
+__global__ void __launch_bounds__(256) rows_to_tiles_kernel(const float* __restrict__ feat, const int* __restrict__ node_off, int n_windows,
+                                                            float* __restrict__ out, long long seq_base, long long n_seq_total, int T, int t_run) {
+  const int b = threadIdx.x & 63, tq = threadIdx.x >> 6;
+  const long long tile = blockIdx.x;
+  const long long s = seq_base + tile * kTile + b;
+  const int t0 = blockIdx.y * 32 + tq * 8;
+  int n0 = 0, nn = 0;
+  const bool live = s < n_seq_total;
+  if (live) {
+    int lo = 0, hi = n_windows;                       // node_off[lo] <= s < node_off[hi]
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (__ldg(node_off + mid) <= s) lo = mid; else hi = mid;
+    }
+    n0 = __ldg(node_off + lo);
+    nn = __ldg(node_off + lo + 1) - n0;
+  }
+  const int me = static_cast<int>(s - n0);
+#pragma unroll 1
+  for (int dt = 0; dt < 8; ++dt) {
+    const int t = t0 + dt;
+    if (t >= t_run) break;
+    const float* x = feat + (static_cast<long long>(n0) * T + static_cast<long long>(t) * nn + me) * C;
+    float* o = out + ((tile * t_run + t) * C) * kTile + b;
+#pragma unroll
+    for (int c = 0; c < C; ++c) o[c * kTile] = live ? __ldg(x + c) : 0.f;
+  }
+}
+
+// GcnFolded (BatchNorm folded into the GeneralConv projection) is declared in model_spec.h.
+static_assert(kGcnChannelsDev == kGcnChannels, "GeneralConv width");
 
 // PReLU pooled over nodes without a branch per element: prelu(z) = k1*z + k2*|z| with
 // k1 = (1+alpha)/2, k2 = (1-alpha)/2, and z is affine in the two input channels, so

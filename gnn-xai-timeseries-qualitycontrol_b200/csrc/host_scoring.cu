@@ -138,7 +138,6 @@ extern "C" int gnnqc_score_cml_host(gnnqc_model* m, const float* features_host, 
     return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_score_cml_host: null buffer");
   try {
     m->dm.refresh_tc();
-    m->dm.sync_host_params();
     gnnqc::score_cml_host(m->dm, features_host, anom_host, reinterpret_cast<const long long*>(edges_host), node_off_host,
                           reinterpret_cast<const long long*>(edge_off_host), B, T, chunk_windows > 0 ? chunk_windows : 8192, scores_host,
                           reinterpret_cast<long long*>(h2d_bytes_out));

@@ -119,19 +119,6 @@ void dispatch(Op op, int in, int hid, bool pool, bool last, const LayerArgs& a) 
   throw std::invalid_argument("integrated gradients: no kernel for this LSTM layer shape");
 }
 
-GcnFolded fold_gcn_params(const HostModel& m) {
-  const ModelSpec& s = m.spec;
-  const float* p = m.params.data();
-  GcnFolded f;
-  std::memset(&f, 0, sizeof(f));
-  for (int c = 0; c < kGcnChannels; ++c) {
-    const float scale = p[s.off_bn_gamma + c] / std::sqrt(p[s.off_bn_var + c] + s.bn_eps);
-    for (int k = 0; k < s.n_features; ++k) f.a[k][c] = p[s.off_gcn_kernel + k * kGcnChannels + c] * scale;
-    f.c[c] = (p[s.off_gcn_bias + c] - p[s.off_bn_mean + c]) * scale + p[s.off_bn_beta + c];
-    f.alpha[c] = p[s.off_prelu + c];
-  }
-  return f;
-}
 
 }  // namespace
 
@@ -194,7 +181,7 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
   GNNQC_CUDA(cudaGetLastError());
   mark_end(st);
 
-  const GcnFolded folded = fold_gcn_params(host);
+  const GcnFolded folded = this->folded(st);
   const float* prm = d_params;
   static const char* const kFwd[kMaxLstmLayers] = {"ig_fwd_l1", "ig_fwd_l2", "ig_fwd_l3", "ig_fwd_l4", "ig_fwd_l5", "ig_fwd_l6", "ig_fwd_l7"};
   static const char* const kBwd[kMaxLstmLayers] = {"ig_bwd_l1", "ig_bwd_l2", "ig_bwd_l3", "ig_bwd_l4", "ig_bwd_l5", "ig_bwd_l6", "ig_bwd_l7"};

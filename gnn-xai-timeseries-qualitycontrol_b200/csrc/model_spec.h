@@ -17,6 +17,13 @@ constexpr int kGcnChannels = 16;   // graph_convolution.units in every shipped m
 constexpr int kMaxLstmLayers = 7;  // 2 + 2*n_stacks + 1 with n_stacks = 2
 constexpr int kTile = 64;          // sequences per device-side tile (see lstm_fwd.cuh)
 
+// BatchNorm (inference) folded into the GeneralConv projection: z = prelu(x0*a0 + x1*a1 (+ x2*a2) + c).
+struct GcnFolded {
+  float a[3][kGcnChannels];
+  float c[kGcnChannels];
+  float alpha[kGcnChannels];
+};
+
 struct ModelSpec {
   bool has_gcn = false;     // GCNClassifier vs BaselineClassifier
   bool soilnet = false;     // ds_type: 'soilnet' (F=3, every node is a sequence) or 'cml' (F=2)

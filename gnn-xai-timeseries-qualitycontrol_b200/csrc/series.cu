@@ -34,6 +34,8 @@ struct gnnqc_series {
   int* nbr_idx = nullptr;      // [n_nbr] global sensor ids of each target's neighbourhood (target included)
   long long* edge_off = nullptr;  // [S+1]
   long long* edges = nullptr;     // [n_edges][2] indices into the target's neighbour list
+  void* scan_tmp = nullptr;       // cub scratch of the prefix rebuild, kept so that updates allocate nothing
+  size_t scan_tmp_bytes = 0;
 };
 
 namespace gnnqc {
@@ -196,40 +198,30 @@ __global__ void __launch_bounds__(256) series_mask_scores_kernel(float* __restri
   if (n_nodes_out) n_nodes_out[i] = c;
 }
 
-GcnFolded fold(const HostModel& m) {
-  const ModelSpec& s = m.spec;
-  const float* p = m.params.data();
-  GcnFolded f;
-  std::memset(&f, 0, sizeof(f));
-  for (int c = 0; c < kGcnChannels; ++c) {
-    const float scale = p[s.off_bn_gamma + c] / std::sqrt(p[s.off_bn_var + c] + s.bn_eps);
-    for (int k = 0; k < s.n_features; ++k) f.a[k][c] = p[s.off_gcn_kernel + k * kGcnChannels + c] * scale;
-    f.c[c] = (p[s.off_gcn_bias + c] - p[s.off_bn_mean + c]) * scale + p[s.off_bn_beta + c];
-    f.alpha[c] = p[s.off_prelu + c];
-  }
-  return f;
-}
 
 void free_series(gnnqc_series* s) {
   if (!s) return;
   cudaSetDevice(s->device);
   cudaFree(s->raw); cudaFree(s->rmed); cudaFree(s->nan_prefix); cudaFree(s->nbr_off); cudaFree(s->nbr_idx);
-  cudaFree(s->edge_off); cudaFree(s->edges);
+  cudaFree(s->edge_off); cudaFree(s->edges); cudaFree(s->scan_tmp);
   delete s;
 }
 
-void rebuild_nan_prefix(gnnqc_series* s) {
+// Stream-ordered; the cub scratch is allocated once (at creation) and reused by every update.
+void rebuild_nan_prefix(gnnqc_series* s, cudaStream_t st) {
   const long long n = s->S * (s->Tt + 1);
-  nan_flag_kernel<<<static_cast<unsigned>((n + 255) / 256), 256>>>(s->raw, s->nan_prefix, s->S, s->Tt);
+  nan_flag_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, st>>>(s->raw, s->nan_prefix, s->S, s->Tt);
   GNNQC_CUDA(cudaGetLastError());
   size_t tmp_bytes = 0;
-  GNNQC_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, s->nan_prefix, s->nan_prefix, static_cast<int>(n)));
-  void* tmp = nullptr;
-  GNNQC_CUDA(cudaMalloc(&tmp, tmp_bytes));
-  cudaError_t err = cub::DeviceScan::InclusiveSum(tmp, tmp_bytes, s->nan_prefix, s->nan_prefix, static_cast<int>(n));
-  cudaFree(tmp);
-  GNNQC_CUDA(err);
-  GNNQC_CUDA(cudaDeviceSynchronize());
+  GNNQC_CUDA(cub::DeviceScan::InclusiveSum(nullptr, tmp_bytes, s->nan_prefix, s->nan_prefix, static_cast<int>(n), st));
+  if (tmp_bytes > s->scan_tmp_bytes) {
+    GNNQC_CUDA(cudaStreamSynchronize(st));
+    cudaFree(s->scan_tmp);
+    s->scan_tmp = nullptr;
+    GNNQC_CUDA(cudaMalloc(&s->scan_tmp, tmp_bytes));
+    s->scan_tmp_bytes = tmp_bytes;
+  }
+  GNNQC_CUDA(cub::DeviceScan::InclusiveSum(s->scan_tmp, tmp_bytes, s->nan_prefix, s->nan_prefix, static_cast<int>(n), st));
 }
 
 }  // namespace
@@ -272,7 +264,8 @@ int gnnqc_series_create(int device, const float* raw_host, const float* rmed_hos
     GNNQC_CUDA(cudaMemcpy(s->nbr_idx, nbr_idx_host, size_t(s->n_nbr) * sizeof(int), cudaMemcpyHostToDevice));
     GNNQC_CUDA(cudaMemcpy(s->edge_off, edge_off_host, size_t(n_sensors + 1) * sizeof(long long), cudaMemcpyHostToDevice));
     GNNQC_CUDA(cudaMemcpy(s->edges, edges_host, size_t(s->n_edges) * 2 * sizeof(long long), cudaMemcpyHostToDevice));
-    gnnqc::rebuild_nan_prefix(s);
+    gnnqc::rebuild_nan_prefix(s, nullptr);
+    GNNQC_CUDA(cudaDeviceSynchronize());
   } catch (const gnnqc::CudaError& e) {
     gnnqc::free_series(s);
     return gnnqc_internal_fail(GNNQC_ERR_CUDA, e.what());
@@ -284,20 +277,27 @@ int gnnqc_series_create(int device, const float* raw_host, const float* rmed_hos
   return GNNQC_OK;
 }
 
-int gnnqc_series_update(gnnqc_series* s, int64_t t0, int64_t n_t, const float* raw_host, const float* rmed_host) {
+int gnnqc_series_update_async(gnnqc_series* s, int64_t t0, int64_t n_t, const float* raw_host, const float* rmed_host, void* stream) {
   if (!s || !raw_host || !rmed_host || t0 < 0 || n_t <= 0 || t0 + n_t > s->Tt) return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_series_update: bad range");
   try {
     GNNQC_CUDA(cudaSetDevice(s->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
     // host slab is [S][n_t][2]; device rows have pitch Tt
-    GNNQC_CUDA(cudaMemcpy2D(s->raw + t0, size_t(s->Tt) * sizeof(float2), raw_host, size_t(n_t) * sizeof(float2), size_t(n_t) * sizeof(float2),
-                            size_t(s->S), cudaMemcpyHostToDevice));
-    GNNQC_CUDA(cudaMemcpy2D(s->rmed + t0, size_t(s->Tt) * sizeof(float2), rmed_host, size_t(n_t) * sizeof(float2), size_t(n_t) * sizeof(float2),
-                            size_t(s->S), cudaMemcpyHostToDevice));
-    gnnqc::rebuild_nan_prefix(s);
+    GNNQC_CUDA(cudaMemcpy2DAsync(s->raw + t0, size_t(s->Tt) * sizeof(float2), raw_host, size_t(n_t) * sizeof(float2), size_t(n_t) * sizeof(float2),
+                                 size_t(s->S), cudaMemcpyHostToDevice, st));
+    GNNQC_CUDA(cudaMemcpy2DAsync(s->rmed + t0, size_t(s->Tt) * sizeof(float2), rmed_host, size_t(n_t) * sizeof(float2), size_t(n_t) * sizeof(float2),
+                                 size_t(s->S), cudaMemcpyHostToDevice, st));
+    gnnqc::rebuild_nan_prefix(s, st);
   } catch (const std::exception& e) {
     return gnnqc_internal_fail(GNNQC_ERR_CUDA, e.what());
   }
   return GNNQC_OK;
+}
+
+int gnnqc_series_update(gnnqc_series* s, int64_t t0, int64_t n_t, const float* raw_host, const float* rmed_host) {
+  const int rc = gnnqc_series_update_async(s, t0, n_t, raw_host, rmed_host, nullptr);
+  if (rc != GNNQC_OK) return rc;
+  return cudaStreamSynchronize(nullptr) == cudaSuccess ? GNNQC_OK : gnnqc_internal_fail(GNNQC_ERR_CUDA, "gnnqc_series_update: copy failed");
 }
 
 void gnnqc_series_free(gnnqc_series* s) { gnnqc::free_series(s); }
@@ -315,7 +315,6 @@ int gnnqc_score_cml_series(gnnqc_model* m, const gnnqc_series* series, const int
   try {
     using namespace gnnqc;
     dm.refresh_tc();
-    dm.sync_host_params();
     GNNQC_CUDA(cudaSetDevice(dm.device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int T = timestep_before + timestep_after + 1;
@@ -343,7 +342,7 @@ int gnnqc_score_cml_series(gnnqc_model* m, const gnnqc_series* series, const int
                                                                                        w_sensor, w_coef, w_med, w_count, w_tgt);
     GNNQC_CUDA(cudaGetLastError());
     dm.mark_end(st);
-    const GcnFolded folded = fold(dm.host);
+    const GcnFolded folded = dm.folded(st);
     for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
       const long long nt = std::min(chunk, n_tiles - t0);
       const long long win0 = t0 * kTile, nw = std::min<long long>(B - win0, nt * kTile);

@@ -147,19 +147,6 @@ __global__ void __launch_bounds__(256) soil_mask_kernel(float* __restrict__ scor
   if (i < n && !valid[i]) scores[i] = nanf("");
 }
 
-GcnFolded fold_soil(const HostModel& m) {
-  const ModelSpec& s = m.spec;
-  const float* p = m.params.data();
-  GcnFolded f;
-  std::memset(&f, 0, sizeof(f));
-  for (int c = 0; c < kGcnChannels; ++c) {
-    const float scale = p[s.off_bn_gamma + c] / std::sqrt(p[s.off_bn_var + c] + s.bn_eps);
-    for (int k = 0; k < s.n_features; ++k) f.a[k][c] = p[s.off_gcn_kernel + k * kGcnChannels + c] * scale;
-    f.c[c] = (p[s.off_gcn_bias + c] - p[s.off_bn_mean + c]) * scale + p[s.off_bn_beta + c];
-    f.alpha[c] = p[s.off_prelu + c];
-  }
-  return f;
-}
 
 }  // namespace
 }  // namespace gnnqc
@@ -225,7 +212,6 @@ int gnnqc_score_soilnet_series(gnnqc_model* m, const gnnqc_soil_series* series, 
   try {
     DeviceModel& dm = m->dm;
     dm.refresh_tc();
-    dm.sync_host_params();
     GNNQC_CUDA(cudaSetDevice(dm.device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const ModelSpec& s = dm.host.spec;
@@ -248,7 +234,7 @@ int gnnqc_score_soilnet_series(gnnqc_model* m, const gnnqc_soil_series* series, 
     soil_valid_kernel<<<static_cast<unsigned>((n_seq + 255) / 256), 256, 0, st>>>(*series, t_anom_dev, steps_before, steps_after, n_seq, valid);
     GNNQC_CUDA(cudaGetLastError());
     dm.mark_end(st);
-    const GcnFolded folded = fold_soil(dm.host);
+    const GcnFolded folded = dm.folded(st);
     for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
       const long long nt = std::min(chunk, n_tiles - t0);
       const long long seq0 = t0 * kTile, ns = std::min<long long>(n_seq - seq0, nt * kTile);

@@ -25,19 +25,6 @@ namespace {
 
 inline size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 
-GcnFolded fold(const HostModel& m) {
-  const ModelSpec& s = m.spec;
-  const float* p = m.params.data();
-  GcnFolded f;
-  std::memset(&f, 0, sizeof(f));
-  for (int c = 0; c < kGcnChannels; ++c) {
-    const float scale = p[s.off_bn_gamma + c] / std::sqrt(p[s.off_bn_var + c] + s.bn_eps);
-    for (int k = 0; k < s.n_features; ++k) f.a[k][c] = p[s.off_gcn_kernel + k * kGcnChannels + c] * scale;
-    f.c[c] = (p[s.off_gcn_bias + c] - p[s.off_bn_mean + c]) * scale + p[s.off_bn_beta + c];
-    f.alpha[c] = p[s.off_prelu + c];
-  }
-  return f;
-}
 
 size_t budget_bytes() {
   const char* env = std::getenv("GNNQC_SCRATCH_MB");
@@ -88,7 +75,7 @@ void DeviceModel::score_soilnet(const float* feat, const long long* edges, const
   GNNQC_CUDA(cudaGetLastError());
   mark_end(st);
 
-  const GcnFolded folded = fold(host);
+  const GcnFolded folded = this->folded(st);
   for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
     const long long nt = std::min(chunk, n_tiles - t0);
     const long long seq0 = t0 * kTile, ns = std::min<long long>(n_nodes - seq0, nt * kTile);

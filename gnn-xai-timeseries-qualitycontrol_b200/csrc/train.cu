@@ -431,6 +431,7 @@ void DeviceModel::train_apply(float* rvec, const double* moments, float lr, cuda
   }
   params_dirty = true;
   tc_stale = false;
+  folded_valid = false;
 }
 
 }  // namespace gnnqc

@@ -68,6 +68,8 @@ def _load():
         "gnnqc_score_soilnet": (C.c_int, [vp, vp, vp, vp, vp, i64, i32, i64, i64, vp, vp]),
         "gnnqc_series_create": (C.c_int, [C.c_int, vp, vp, i64, i64, vp, vp, vp, vp, C.POINTER(vp)]),
         "gnnqc_series_update": (C.c_int, [vp, i64, i64, vp, vp]),
+        "gnnqc_series_update_async": (C.c_int, [vp, i64, i64, vp, vp, vp]),
+        "gnnqc_score_rows": (C.c_int, [vp, vp, vp, i64, i32, i64, vp, vp]),
         "gnnqc_series_free": (None, [vp]),
         "gnnqc_score_cml_series": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, vp, vp, vp]),
         "gnnqc_soil_series_create": (C.c_int, [C.c_int, vp, vp, i64, i64, vp, C.POINTER(vp)]),

@@ -23,13 +23,31 @@ def adjacency_indices(adjacency):
     return idx.to(torch.int64)
 
 
-def disjoint_to_offsets(indices, sample_indices, n_windows, T):
-    """indices int64 [E_tiled,2], sample_indices [rows] -> (edges [E,2] local, node_off i32
-    [B+1], edge_off i64 [B+1], n_nodes_total)."""
+def _rows_per_window(sample_indices, n_windows):
+    """Counts without torch.bincount (which reads the maximum back to the host to size its output)."""
     sample_indices = sample_indices.to(torch.int64)
-    rows_per_window = torch.bincount(sample_indices, minlength=n_windows)
-    if int((rows_per_window % T).abs().sum()) != 0:
+    return torch.zeros(n_windows, dtype=torch.int64, device=sample_indices.device).scatter_add_(0, sample_indices, torch.ones_like(sample_indices))
+
+
+def node_offsets(sample_indices, n_windows, T):
+    """sample_indices [rows] -> node_off i32 [n_windows + 1]; windows past the last one present stay empty."""
+    nodes = _rows_per_window(sample_indices, n_windows) // T
+    node_off = torch.zeros(n_windows + 1, dtype=torch.int64, device=sample_indices.device)
+    node_off[1:] = torch.cumsum(nodes, 0)
+    return node_off.to(torch.int32)
+
+
+def disjoint_to_offsets(indices, sample_indices, n_windows, T, validate=False):
+    """indices int64 [E_tiled,2], sample_indices [rows] -> (edges [E,2] local, node_off i32
+    [B+1], edge_off i64 [B+1], n_nodes_total).  Runs on the tensors' device without reading anything back
+    (sizes follow from the shapes: rows / T nodes, E_tiled / T edges); validate=True adds the one check that needs a
+    host read (rows per window divisible by T)."""
+    sample_indices = sample_indices.to(torch.int64)
+    rows_per_window = _rows_per_window(sample_indices, n_windows)
+    if validate and int((rows_per_window % T).abs().sum()) != 0:
         raise ValueError("rows per window are not a multiple of the sequence length %d" % T)
+    if sample_indices.numel() % T or indices.shape[0] % T:
+        raise ValueError("rows / tiled edges are not a multiple of the sequence length %d" % T)
     nodes = rows_per_window // T
     node_off = torch.zeros(n_windows + 1, dtype=torch.int64, device=indices.device)
     node_off[1:] = torch.cumsum(nodes, 0)
@@ -37,13 +55,15 @@ def disjoint_to_offsets(indices, sample_indices, n_windows, T):
     win = sample_indices[indices[:, 0]]                        # window of every tiled edge
     local_row = indices[:, 0] - base[win]
     first_step = local_row < nodes[win]                        # the t == 0 copy of the edge list
-    win0 = win[first_step]
-    edges = torch.stack([local_row[first_step], indices[first_step, 1] - base[win0]], dim=1)
-    order = torch.argsort(win0, stable=True)
-    edges = edges[order].contiguous()
+    n_edges = indices.shape[0] // T
+    # compaction without a dynamic-size op: stable sort by (not first step, window), keep the first E entries
+    key = (~first_step).to(torch.int64) * (n_windows + 1) + win
+    order = torch.argsort(key, stable=True)[:n_edges]
+    win0 = win[order]
+    edges = torch.stack([local_row[order], indices[order, 1] - base[win0]], dim=1).contiguous()
     edge_off = torch.zeros(n_windows + 1, dtype=torch.int64, device=indices.device)
-    edge_off[1:] = torch.cumsum(torch.bincount(win0, minlength=n_windows), 0)
-    return edges, node_off.to(torch.int32), edge_off, int(node_off[-1])
+    edge_off[1:] = torch.cumsum(_rows_per_window(win0, n_windows), 0)
+    return edges, node_off.to(torch.int32), edge_off, sample_indices.numel() // T
 
 
 def offsets_to_disjoint(edges, node_off, edge_off, T):

@@ -135,6 +135,19 @@ class NativeModel:
         check(lib.gnnqc_score_seq(self._h, x.data_ptr(), x.shape[0], x.shape[1], out.data_ptr(), self._stream()))
         return out
 
+    def score_rows(self, features, node_off, T, n_nodes_total=None):
+        """gnnqc_score_rows: baseline scoring from the reference's (window, t, sensor) row layout; features cuda f32
+        [sum N_b * T, C], node_off cuda i32 [B+1] -> cuda f32 [sum N_b]."""
+        torch = _torch()
+        features = self._dev_tensor(features, torch.float32, "features")
+        node_off = self._dev_tensor(node_off, torch.int32, "node_off")
+        if n_nodes_total is None:
+            n_nodes_total = features.shape[0] // int(T)
+        out = torch.empty(n_nodes_total, dtype=torch.float32, device=features.device)
+        check(lib.gnnqc_score_rows(self._h, features.data_ptr(), node_off.data_ptr(), node_off.numel() - 1, int(T), n_nodes_total,
+                                   out.data_ptr(), self._stream()))
+        return out
+
     def score_seq_noalloc(self, x, out):
         """gnnqc_score_seq_noalloc: like score_seq, but the library allocates nothing, so the
         caller also supplies `out` (cuda f32 [n_seq]).  For callers that must not allocate on

@@ -44,10 +44,23 @@ class CmlSeries:
                                       nbr_idx.ctypes.data, edge_off.ctypes.data, edges.ctypes.data, C.byref(h)))
         self._h = h
 
-    def update(self, t0, raw_slab, rmed_slab):
-        raw_slab = np.ascontiguousarray(raw_slab, dtype=np.float32)
-        rmed_slab = np.ascontiguousarray(rmed_slab, dtype=np.float32)
-        check(lib.gnnqc_series_update(self._h, int(t0), raw_slab.shape[1], raw_slab.ctypes.data, rmed_slab.ctypes.data))
+    def update(self, t0, raw_slab, rmed_slab, stream=None):
+        """Overwrites [t0, t0 + n_t) from host slabs [n_sensors, n_t, 2] (numpy arrays, or pinned torch tensors for
+        copies that do not block the host).  stream: a raw CUDA stream handle; the update is ordered on it."""
+        def host(a):
+            if hasattr(a, "data_ptr"):          # torch CPU tensor (pinned memory keeps the copy asynchronous)
+                if a.dtype.is_floating_point and a.element_size() == 4 and a.is_contiguous():
+                    return a, a.data_ptr(), a.shape[1]
+                a = a.numpy()
+            a = np.ascontiguousarray(a, dtype=np.float32)
+            return a, a.ctypes.data, a.shape[1]
+        raw_keep, raw_ptr, n_t = host(raw_slab)
+        med_keep, med_ptr, _ = host(rmed_slab)
+        if stream is None:
+            check(lib.gnnqc_series_update(self._h, int(t0), n_t, raw_ptr, med_ptr))
+        else:
+            check(lib.gnnqc_series_update_async(self._h, int(t0), n_t, raw_ptr, med_ptr, C.c_void_p(int(stream))))
+            self._keep = (raw_keep, med_keep)    # the host slabs must outlive the asynchronous copies
 
     def close(self):
         if self._h:

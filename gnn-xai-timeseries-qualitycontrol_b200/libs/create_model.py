@@ -150,7 +150,7 @@ class GCNClassifier(_Classifier):
             features = _as_device(inputs[0], dev, torch.float32)
             idx = _as_device(_layout.adjacency_indices(inputs[1]), dev, torch.int64)
             samp = _as_device(inputs[2], dev)
-            n_windows = int(samp.max().item()) + 1 if samp.numel() else 0
+            n_windows = max(int(self.model_info[2]), 1)     # the reference's partition count; no device read for it
             edges, node_off, edge_off, n_nodes = _layout.disjoint_to_offsets(idx, samp, n_windows, T)
             return self.native.score_soilnet(features, edges, node_off, edge_off, T, n_nodes)
         if isinstance(inputs, dict):     # offsets layout, see include/gnnqc.h
@@ -200,15 +200,12 @@ class BaselineClassifier(_Classifier):
         features = _as_device(features, dev, torch.float32)
         samp = _as_device(sample_indices, dev, torch.int64)
         T = self.sequence_length
-        # graph_reshape (reference :242-258): rows (window, t, node) -> sequences (window, node, t)
-        rows = torch.bincount(samp)
-        nodes = rows // T
-        seqs = []
-        start = 0
-        for n in nodes.tolist():
-            seqs.append(features[start: start + n * T].reshape(T, n, -1).permute(1, 0, 2))
-            start += n * T
-        return self.native.score_seq(torch.cat(seqs).contiguous())
+        # graph_reshape (reference :242-258) happens inside gnnqc_score_rows; only the per-window node counts are formed
+        # here, on the device and without a host read: the reference partitions into `batch_size` windows (model_info[2]),
+        # short last batches leave the trailing ones empty
+        n_windows = max(int(self.model_info[2]), 1)
+        node_off = _layout.node_offsets(samp, n_windows, T)
+        return self.native.score_rows(features, node_off, T, features.shape[0] // T)
 
 
 def load_model(model_path, device=0, compile=False):

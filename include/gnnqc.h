@@ -104,6 +104,12 @@ void gnnqc_model_free(gnnqc_model* m);
  * model.  x_dev: f32 [n_seq, T, C] row-major, C = the model's first LSTM input width
  * (2 for model_cml_baseline, 3 for model_soilnet_baseline after graph_reshape).
  * scores_dev: f32 [n_seq]. */
+/* The SoilNet baseline straight from the reference's batch layout (BaselineClassifier.call with graph_reshape,
+ * libs/create_model.py:242-258,343-347; wrapper_batch_mapping_baseline_soilnet, libs/preprocessing_functions.py:905-916):
+ * features_dev f32 [sum N_b * T, C] rows in (window, t, sensor) order, node_off_dev i32 [B+1]; the reshape to
+ * (window, sensor) sequences happens inside the tile builder.  scores_dev: f32 [sum N_b]. */
+int gnnqc_score_rows(gnnqc_model* m, const float* features_dev, const int32_t* node_off_dev, int64_t B,
+                     int32_t T, int64_t n_nodes_total, float* scores_dev, void* stream);
 int gnnqc_score_seq(gnnqc_model* m, const float* x_dev, int64_t n_seq, int32_t T,
                     float* scores_dev, void* stream);
 
@@ -152,6 +158,10 @@ int gnnqc_series_create(int device, const float* raw_host, const float* rmed_hos
                         const int64_t* edge_off_host, const int64_t* edges_host, gnnqc_series** out);
 int gnnqc_series_update(gnnqc_series* s, int64_t t0, int64_t n_t, const float* raw_host,
                         const float* rmed_host);
+/* The same, enqueued on `stream` (pinned host slabs make the copies asynchronous); the validity prefix counts are
+ * rebuilt on that stream too, so a scoring call on the same stream sees the update. */
+int gnnqc_series_update_async(gnnqc_series* s, int64_t t0, int64_t n_t, const float* raw_host,
+                              const float* rmed_host, void* stream);
 void gnnqc_series_free(gnnqc_series* s);
 int gnnqc_score_cml_series(gnnqc_model* m, const gnnqc_series* series, const int32_t* target_dev,
                            const int32_t* t_anom_dev, int64_t B, int32_t timestep_before,

@@ -64,3 +64,36 @@ def test_reference_layout_inputs_give_the_same_scores(models_dir):
     c = model(b).cpu().numpy()
     np.testing.assert_array_equal(a, c)
     assert a.shape == (20, 1)
+
+
+def test_soilnet_reference_layouts_and_training(models_dir):
+    """SoilNet GCN with the reference's (features, adjacency, sample_indices) tuple == the offsets-layout dict; the
+    SoilNet baseline from (features, sample_indicator) rows == scoring the graph_reshape'd sequences; and a few
+    training epochs of a freshly initialised SoilNet GCN (one label per (window, sensor))."""
+    import os
+
+    from gnnqc import layout
+    b = synth.make_soilnet_batch(5, seed=8, n_nodes=17, ragged=True, min_nodes=6)
+    labels = b.pop("labels")
+    idx, samp = layout.offsets_to_disjoint(b["edges"], b["node_off"], b["edge_off"], b["T"])
+    model = load_model(os.path.join(models_dir, "model_soilnet"), device=0)
+    a = model((b["features"], (idx, torch.ones(idx.shape[0]), None), samp)).cpu().numpy()
+    c = model(b).cpu().numpy()
+    np.testing.assert_array_equal(a, c)
+    assert a.shape == (int(b["node_off"][-1]), 1)
+
+    base = load_model(os.path.join(models_dir, "model_soilnet_baseline"), device=0)
+    rows = base((b["features"], samp)).cpu().numpy()
+    T, seqs, no = b["T"], [], b["node_off"].tolist()
+    for w in range(5):
+        n = no[w + 1] - no[w]
+        seqs.append(b["features"][no[w] * T: no[w + 1] * T].reshape(T, n, 3).permute(1, 0, 2))
+    direct = base.native.score_seq(torch.cat(seqs).contiguous().cuda()).cpu().numpy().reshape(-1, 1)
+    np.testing.assert_array_equal(rows, direct)
+
+    mc, pc = default_model_config(), default_preproc_config("soilnet")
+    mc.epochs, mc.learning_rate, mc.es_patience = 3, 2e-3, 10
+    fresh = GCNClassifier(mc, pc, device=0, seed=3)
+    labels[0] = 1
+    history, fresh = fit_model.train_model(fresh, mc, pc, [(b, labels)], [(b, labels)])
+    assert len(history["loss"]) == 3 and np.isfinite(history["loss"]).all() and history["loss"][-1] < history["loss"][0]

@@ -1,0 +1,24 @@
+"""gnnqc/layout.py on CPU tensors: the reference's disjoint-graph batch (tiled COO + sample_indices,
+libs/preprocessing_functions.py:638-666) <-> the offsets layout of include/gnnqc.h, without any host read-back."""
+import torch
+
+from gnnqc import layout, synth
+
+
+def test_disjoint_round_trip_with_trailing_empty_windows():
+    for make, T in ((lambda: synth.make_cml_batch(7, seed=2, ragged=True), 181), (lambda: synth.make_soilnet_batch(3, seed=2, n_nodes=11, ragged=True, min_nodes=4), 337)):
+        b = make()
+        idx, samp = layout.offsets_to_disjoint(b["edges"], b["node_off"], b["edge_off"], T)
+        B = b["node_off"].numel() - 1
+        # shuffle the tiled edge list: the conversion must not depend on its order
+        perm = torch.randperm(idx.shape[0], generator=torch.Generator().manual_seed(0))
+        for n_windows in (B, B + 5):            # the reference partitions into batch_size windows; short batches leave empty ones
+            edges, node_off, edge_off, n_nodes = layout.disjoint_to_offsets(idx[perm], samp, n_windows, T, validate=True)
+            assert n_nodes == int(b["node_off"][-1])
+            assert torch.equal(node_off[: B + 1], b["node_off"]) and (node_off[B:] == node_off[B]).all()
+            assert torch.equal(edge_off[: B + 1], b["edge_off"]) and (edge_off[B:] == edge_off[B]).all()
+            for w in range(B):
+                got = edges[edge_off[w]: edge_off[w + 1]]
+                want = b["edges"][b["edge_off"][w]: b["edge_off"][w + 1]]
+                assert sorted(map(tuple, got.tolist())) == sorted(map(tuple, want.tolist()))
+            assert torch.equal(layout.node_offsets(samp, n_windows, T), node_off)
