@@ -3,6 +3,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <functional>
 #include <stdexcept>
 #include <string>
 #include <vector>
@@ -137,6 +138,10 @@ struct DeviceModel {
                      int T, long long n_nodes, long long n_edges, float* scores, cudaStream_t stream);
   // Integrated gradients for the CML GCN model (csrc/ig.cu).
   void configure_ig_kernels();
+  void ig_core(long long B, int T, int m_steps, float* scores, cudaStream_t stream, size_t extra_bytes,
+               const std::function<void(char*)>& prepare,
+               const std::function<void(float, long long, long long, long long, float*)>& fwd,
+               const std::function<void(float, float, int, long long, long long, const float*)>& bwd);
   void ig_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
               const long long* edge_off, long long B, int T, long long n_nodes, int m_steps, float* attr_feat,
               float* attr_anom, float* scores, cudaStream_t stream);

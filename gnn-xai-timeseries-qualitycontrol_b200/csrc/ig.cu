@@ -17,6 +17,8 @@
 #include <cstring>
 #include <cmath>
 
+#include <functional>
+
 #include "device_model.cuh"
 #include "frontend.cuh"
 #include "lstm_bwd.cuh"
@@ -134,9 +136,14 @@ void DeviceModel::configure_ig_kernels() {
   }
 }
 
-void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
-                         const long long* edge_off, long long B, int T, long long n_nodes, int m_steps, float* attr_feat,
-                         float* attr_anom, float* scores, cudaStream_t st) {
+// Integrated gradients over windows whatever their source: `fwd(alpha, win0, nw, nt, x1)` builds the x1 tiles of a chunk
+// at the interpolation point alpha * x, `bwd(alpha, wk, first, win0, nw, dx1)` turns d(sum p)/d(x1) into attributions
+// (trapezoid weight wk; `first` assigns instead of accumulating).  `extra_bytes` of scratch come first and are handed
+// to `prepare` (node coefficients / per-window node lists).
+void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaStream_t st, size_t extra_bytes,
+                          const std::function<void(char*)>& prepare,
+                          const std::function<void(float, long long, long long, long long, float*)>& fwd,
+                          const std::function<void(float, float, int, long long, long long, const float*)>& bwd) {
   if (B <= 0) return;
   const ModelSpec& s = host.spec;
   GNNQC_CUDA(cudaSetDevice(device));
@@ -162,12 +169,10 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
   }
   const size_t s7 = size_t(s.lstm_hid[L - 1]) * kTile * sizeof(float);
   const size_t per_tile = sa + sb + 2 * sg + s7 + per_tile_save;
-  const size_t coef_bytes = align_up(size_t(n_nodes) * sizeof(float), 256);
+  extra_bytes = align_up(extra_bytes, 256);
   const long long chunk = balanced_chunk(n_tiles, static_cast<long long>(ig_scratch_budget_bytes() / per_tile));
-  char* base = static_cast<char*>(scratch(2 * coef_bytes + size_t(chunk) * per_tile));
-  int* deg = reinterpret_cast<int*>(base);
-  float* coef = reinterpret_cast<float*>(base + coef_bytes);
-  char* p = base + 2 * coef_bytes;
+  char* base = static_cast<char*>(scratch(extra_bytes + size_t(chunk) * per_tile));
+  char* p = base + extra_bytes;
   float* buf_a = reinterpret_cast<float*>(p); p += size_t(chunk) * sa;
   float* buf_b = reinterpret_cast<float*>(p); p += size_t(chunk) * sb;
   float* g0 = reinterpret_cast<float*>(p); p += size_t(chunk) * sg;
@@ -175,13 +180,7 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
   float* dy7 = reinterpret_cast<float*>(p); p += size_t(chunk) * s7;
   char* saves = p;   // layer l of the chunk: saves + chunk*save_off[l] (layer-major, then tile)
 
-  GNNQC_CUDA(cudaMemsetAsync(deg, 0, size_t(n_nodes) * sizeof(int), st));
-  mark_begin("cml_node_coef", st);
-  cml_node_coef_kernel<<<static_cast<unsigned>((B * 32 + 255) / 256), 256, 0, st>>>(edges, node_off, edge_off, deg, coef, B);
-  GNNQC_CUDA(cudaGetLastError());
-  mark_end(st);
-
-  const GcnFolded folded = this->folded(st);
+  prepare(base);
   const float* prm = d_params;
   static const char* const kFwd[kMaxLstmLayers] = {"ig_fwd_l1", "ig_fwd_l2", "ig_fwd_l3", "ig_fwd_l4", "ig_fwd_l5", "ig_fwd_l6", "ig_fwd_l7"};
   static const char* const kBwd[kMaxLstmLayers] = {"ig_bwd_l1", "ig_bwd_l2", "ig_bwd_l3", "ig_bwd_l4", "ig_bwd_l5", "ig_bwd_l6", "ig_bwd_l7"};
@@ -189,13 +188,11 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
   for (long long t0 = 0; t0 < n_tiles; t0 += chunk) {
     const long long nt = std::min(chunk, n_tiles - t0);
     const long long win0 = t0 * kTile, nw = std::min<long long>(B - win0, nt * kTile);
-    const float2* feat2 = reinterpret_cast<const float2*>(feat);
-    const float2* anom2 = reinterpret_cast<const float2*>(anom) + win0 * T;
     for (int k = 0; k <= m_steps; ++k) {
       const float alpha = static_cast<float>(k) / static_cast<float>(m_steps);
       const float wk = ((k == 0 || k == m_steps) ? 0.5f : 1.0f) / static_cast<float>(m_steps);
       mark_begin("ig_frontend", st);
-      launch_cml_frontend(feat2, n_nodes * T, anom2, coef, node_off + win0, folded, buf_a, nw, T, plan.t_run[0], nt, alpha, sm_count, st);
+      fwd(alpha, win0, nw, nt, buf_a);
       GNNQC_CUDA(cudaGetLastError());
       mark_end(st);
       // forward, saving gates
@@ -237,13 +234,43 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
         dy = a.out;
       }
       mark_begin("ig_frontend_bwd", st);
-      cml_frontend_bwd_kernel<<<static_cast<unsigned>(nw), 256, 0, st>>>(feat2, anom2, coef, node_off + win0, folded, dy,
-                                                       reinterpret_cast<float2*>(attr_feat), reinterpret_cast<float2*>(attr_anom) + win0 * T,
-                                                       nw, T, plan.t_run[0], alpha, wk, k == 0 ? 1 : 0);
+      bwd(alpha, wk, k == 0 ? 1 : 0, win0, nw, dy);
       GNNQC_CUDA(cudaGetLastError());
       mark_end(st);
     }
   }
+}
+
+void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
+                         const long long* edge_off, long long B, int T, long long n_nodes, int m_steps, float* attr_feat,
+                         float* attr_anom, float* scores, cudaStream_t st) {
+  if (B <= 0) return;
+  GNNQC_CUDA(cudaSetDevice(device));
+  const StackPlan plan(host.spec, T);
+  const size_t coef_bytes = align_up(size_t(n_nodes) * sizeof(float), 256);
+  const GcnFolded folded = this->folded(st);
+  const float2* feat2 = reinterpret_cast<const float2*>(feat);
+  float* coef = nullptr;
+  ig_core(B, T, m_steps, scores, st, 2 * coef_bytes,
+          [&](char* extra) {
+            int* deg = reinterpret_cast<int*>(extra);
+            coef = reinterpret_cast<float*>(extra + coef_bytes);
+            GNNQC_CUDA(cudaMemsetAsync(deg, 0, size_t(n_nodes) * sizeof(int), st));
+            mark_begin("cml_node_coef", st);
+            cml_node_coef_kernel<<<static_cast<unsigned>((B * 32 + 255) / 256), 256, 0, st>>>(edges, node_off, edge_off, deg, coef, B);
+            GNNQC_CUDA(cudaGetLastError());
+            mark_end(st);
+          },
+          [&](float alpha, long long win0, long long nw, long long nt, float* x1) {
+            launch_cml_frontend(feat2, n_nodes * T, reinterpret_cast<const float2*>(anom) + win0 * T, coef, node_off + win0, folded, x1, nw, T,
+                                plan.t_run[0], nt, alpha, sm_count, st);
+          },
+          [&](float alpha, float wk, int first, long long win0, long long nw, const float* dx1) {
+            cml_frontend_bwd_kernel<<<static_cast<unsigned>(nw), 256, 0, st>>>(feat2, reinterpret_cast<const float2*>(anom) + win0 * T, coef,
+                                                                             node_off + win0, folded, dx1, reinterpret_cast<float2*>(attr_feat),
+                                                                             reinterpret_cast<float2*>(attr_anom) + win0 * T, nw, T, plan.t_run[0],
+                                                                             alpha, wk, first);
+          });
 }
 
 }  // namespace gnnqc

@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(256) series_frontend_kernel(const gnnqc_series
                                                               const int* __restrict__ w_sensor, const float* __restrict__ w_coef,
                                                               const float2* __restrict__ w_med, const int* __restrict__ w_count,
                                                               const int* __restrict__ w_tgt_slot, const GcnFolded p, float* __restrict__ out,
-                                                              long long n_windows, int t_run) {
+                                                              long long n_windows, int t_run, float alpha = 1.f) {
   // The window's node list (sensor row, coefficient, rolling median) is the same for all its steps:
   // staged once per CTA, one padded row per window so lanes hit distinct banks.
   constexpr int STR = kMaxNbr + 1;
@@ -177,7 +177,8 @@ __global__ void __launch_bounds__(256) series_frontend_kernel(const gnnqc_series
     for (int n = 0; n < nn; ++n) {
       const float2 raw = __ldg(sr.raw + static_cast<long long>(sens_s[b * STR + n]) * sr.Tt + base_t + t);
       const float2 m = med_s[b * STR + n];
-      const float2 v = make_float2(raw.x - m.x, raw.y - m.y);
+      float2 v = make_float2(raw.x - m.x, raw.y - m.y);
+      v.x *= alpha; v.y *= alpha;   // integrated-gradients path scaling (as cml_frontend_body); exact no-op for alpha == 1
       if (n == tslot) tv = v;
       acc.add_packed(p, v, coef_s[b * STR + n]);
     }
@@ -186,6 +187,74 @@ __global__ void __launch_bounds__(256) series_frontend_kernel(const gnnqc_series
     o[kTile] = tv.y;
 #pragma unroll
     for (int c = 0; c < kGcnChannelsDev; ++c) o[(2 + c) * kTile] = acc.pooled(p, c);
+  }
+}
+
+// Integrated gradients, backward through the front-end for windows that live in the resident series: the arithmetic of
+// cml_frontend_bwd_kernel (frontend.cuh) with x = raw - median read from the network.  Attributions go to dense,
+// zero-padded per-window blocks: attr_nodes [window][t][kMaxNbr][2] (node = position in the window's node list, which
+// node_sensor names), attr_anom [window][t][2].  One CTA per window.
+__global__ void __launch_bounds__(256) series_frontend_bwd_kernel(const gnnqc_series sr, const int* __restrict__ t_anom, int before,
+                                                                  const int* __restrict__ w_sensor, const float* __restrict__ w_coef,
+                                                                  const float2* __restrict__ w_med, const int* __restrict__ w_count,
+                                                                  const int* __restrict__ w_tgt_slot, const GcnFolded p, const float* __restrict__ dx1,
+                                                                  float2* __restrict__ attr_nodes, float2* __restrict__ attr_anom,
+                                                                  long long n_windows, int T, int t_run, float alpha, float wk, int first) {
+  const long long win = blockIdx.x;
+  if (win >= n_windows) return;
+  __shared__ int sens_s[kMaxNbr];
+  __shared__ float coef_s[kMaxNbr];
+  __shared__ float2 med_s[kMaxNbr];
+  const int nn = w_count[win];
+  if (threadIdx.x < kMaxNbr) {
+    sens_s[threadIdx.x] = w_sensor[win * kMaxNbr + threadIdx.x];
+    coef_s[threadIdx.x] = w_coef[win * kMaxNbr + threadIdx.x];
+    med_s[threadIdx.x] = w_med[win * kMaxNbr + threadIdx.x];
+  }
+  __syncthreads();
+  const long long tile = win / kTile;
+  const int b = static_cast<int>(win % kTile);
+  constexpr int CH = 2 + kGcnChannelsDev;
+  const long long base_t = static_cast<long long>(t_anom[win]) - before;
+  const float* gbase = dx1 + (tile * t_run) * CH * kTile + b;
+  float2* an = attr_nodes + win * T * kMaxNbr;
+  const int live_rows = t_run * kMaxNbr, all_rows = first ? T * kMaxNbr : live_rows;
+  for (int r = threadIdx.x; r < all_rows; r += 256) {
+    const int t = r / kMaxNbr, n = r - t * kMaxNbr;
+    if (r >= live_rows || n >= nn) {              // padding, skipped windows and steps that cannot reach the score: 0
+      if (first) an[r] = make_float2(0.f, 0.f);
+      continue;
+    }
+    const float2 raw = __ldg(sr.raw + static_cast<long long>(sens_s[n]) * sr.Tt + base_t + t);
+    const float2 v = make_float2(raw.x - med_s[n].x, raw.y - med_s[n].y);
+    const float cf = coef_s[n];
+    const float* g = gbase + static_cast<long long>(t) * CH * kTile;
+    float gx = 0.f, gy = 0.f;
+#pragma unroll
+    for (int c = 0; c < kGcnChannelsDev; ++c) {
+      const float z = fmaf(alpha * v.x, p.a[0][c], fmaf(alpha * v.y, p.a[1][c], p.c[c]));
+      const float s = __ldg(g + (2 + c) * kTile) * (z > 0.f ? 1.f : p.alpha[c]);
+      gx = fmaf(s, p.a[0][c], gx);
+      gy = fmaf(s, p.a[1][c], gy);
+    }
+    float2 a = first ? make_float2(0.f, 0.f) : an[r];
+    a.x = fmaf(wk * v.x * cf, gx, a.x);
+    a.y = fmaf(wk * v.y * cf, gy, a.y);
+    an[r] = a;
+  }
+  const int tslot = w_tgt_slot[win];
+  for (int t = threadIdx.x; t < (first ? T : t_run); t += 256) {
+    if (t >= t_run || nn == 0) {
+      if (first) attr_anom[win * T + t] = make_float2(0.f, 0.f);
+      continue;
+    }
+    const float* g = gbase + static_cast<long long>(t) * CH * kTile;
+    const float2 raw = __ldg(sr.raw + static_cast<long long>(sens_s[tslot]) * sr.Tt + base_t + t);
+    const float2 av = make_float2(raw.x - med_s[tslot].x, raw.y - med_s[tslot].y);
+    float2 a = first ? make_float2(0.f, 0.f) : attr_anom[win * T + t];
+    a.x = fmaf(wk * av.x, __ldg(g), a.x);
+    a.y = fmaf(wk * av.y, __ldg(g + kTile), a.y);
+    attr_anom[win * T + t] = a;
   }
 }
 
@@ -356,6 +425,63 @@ int gnnqc_score_cml_series(gnnqc_model* m, const gnnqc_series* series, const int
     }
     series_mask_scores_kernel<<<static_cast<unsigned>((B + 255) / 256), 256, 0, st>>>(scores_dev, w_count, n_nodes_dev, B);
     GNNQC_CUDA(cudaGetLastError());
+    return GNNQC_OK;
+  } catch (const gnnqc::CudaError& e) {
+    return gnnqc_internal_fail(GNNQC_ERR_CUDA, e.what());
+  } catch (const std::exception& e) {
+    return gnnqc_internal_fail(GNNQC_ERR_ARG, e.what());
+  }
+}
+
+int gnnqc_ig_cml_series(gnnqc_model* m, const gnnqc_series* series, const int32_t* target_dev, const int32_t* t_anom_dev, int64_t B,
+                        int32_t timestep_before, int32_t timestep_after, int32_t m_steps, float* attr_nodes_dev, float* attr_anom_dev,
+                        float* scores_dev, int32_t* node_sensor_dev, int32_t* n_nodes_dev, void* stream) {
+  if (!m || !series) return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_ig_cml_series: null handle");
+  gnnqc::DeviceModel& dm = m->dm;
+  if (dm.device < 0) return gnnqc_internal_fail(GNNQC_ERR_STATE, "gnnqc_ig_cml_series: host-only model handle - there is no CPU path");
+  if (!dm.host.spec.has_gcn || dm.host.spec.soilnet) return gnnqc_internal_fail(GNNQC_ERR_STATE, "gnnqc_ig_cml_series: model is not a CML GCNClassifier");
+  if (dm.device != series->device) return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_ig_cml_series: model and series live on different devices");
+  if (B < 0 || timestep_before < 0 || timestep_after < 0 || m_steps < 1) return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_ig_cml_series: bad sizes");
+  if (B == 0) return GNNQC_OK;
+  if (!target_dev || !t_anom_dev || !attr_nodes_dev || !attr_anom_dev || !scores_dev) return gnnqc_internal_fail(GNNQC_ERR_ARG, "gnnqc_ig_cml_series: null buffer");
+  try {
+    using namespace gnnqc;
+    GNNQC_CUDA(cudaSetDevice(dm.device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int T = timestep_before + timestep_after + 1;
+    const StackPlan plan(dm.host.spec, T);
+    const size_t b_sens = align_up(size_t(B) * kMaxNbr * 4, 256), b_med = align_up(size_t(B) * kMaxNbr * 8, 256), b_one = align_up(size_t(B) * 4, 256);
+    const GcnFolded folded = dm.folded(st);
+    int *w_sensor = nullptr, *w_count = nullptr, *w_tgt = nullptr;
+    float* w_coef = nullptr;
+    float2* w_med = nullptr;
+    dm.ig_core(B, T, m_steps, scores_dev, st, 2 * b_sens + b_med + 2 * b_one,
+               [&](char* p) {
+                 w_sensor = reinterpret_cast<int*>(p); p += b_sens;
+                 w_coef = reinterpret_cast<float*>(p); p += b_sens;
+                 w_med = reinterpret_cast<float2*>(p); p += b_med;
+                 w_count = reinterpret_cast<int*>(p); p += b_one;
+                 w_tgt = reinterpret_cast<int*>(p);
+                 dm.mark_begin("series_prepare", st);
+                 series_prepare_kernel<<<static_cast<unsigned>((B * 32 + 255) / 256), 256, 0, st>>>(*series, target_dev, t_anom_dev, timestep_before,
+                                                                                                    timestep_after, B, w_sensor, w_coef, w_med, w_count, w_tgt);
+                 GNNQC_CUDA(cudaGetLastError());
+                 dm.mark_end(st);
+               },
+               [&](float alpha, long long win0, long long nw, long long nt, float* x1) {
+                 dim3 grid(static_cast<unsigned>(nt), static_cast<unsigned>((plan.t_run[0] + 31) / 32));
+                 series_frontend_kernel<<<grid, 256, 0, st>>>(*series, t_anom_dev + win0, timestep_before, w_sensor + win0 * kMaxNbr, w_coef + win0 * kMaxNbr,
+                                                              w_med + win0 * kMaxNbr, w_count + win0, w_tgt + win0, folded, x1, nw, plan.t_run[0], alpha);
+               },
+               [&](float alpha, float wk, int first, long long win0, long long nw, const float* dx1) {
+                 series_frontend_bwd_kernel<<<static_cast<unsigned>(nw), 256, 0, st>>>(
+                     *series, t_anom_dev + win0, timestep_before, w_sensor + win0 * kMaxNbr, w_coef + win0 * kMaxNbr, w_med + win0 * kMaxNbr, w_count + win0,
+                     w_tgt + win0, folded, dx1, reinterpret_cast<float2*>(attr_nodes_dev) + win0 * T * kMaxNbr, reinterpret_cast<float2*>(attr_anom_dev) + win0 * T,
+                     nw, T, plan.t_run[0], alpha, wk, first);
+               });
+    series_mask_scores_kernel<<<static_cast<unsigned>((B + 255) / 256), 256, 0, st>>>(scores_dev, w_count, n_nodes_dev, B);
+    GNNQC_CUDA(cudaGetLastError());
+    if (node_sensor_dev) GNNQC_CUDA(cudaMemcpyAsync(node_sensor_dev, w_sensor, size_t(B) * kMaxNbr * sizeof(int), cudaMemcpyDeviceToDevice, st));
     return GNNQC_OK;
   } catch (const gnnqc::CudaError& e) {
     return gnnqc_internal_fail(GNNQC_ERR_CUDA, e.what());

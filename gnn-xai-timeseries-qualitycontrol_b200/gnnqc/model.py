@@ -239,6 +239,24 @@ class NativeModel:
                                          out.data_ptr(), counts.data_ptr() if return_counts else None, self._stream()))
         return (out, counts) if return_counts else out
 
+    def ig_cml_series(self, series, target, t_anom, timestep_before=120, timestep_after=60, m_steps=50):
+        """Integrated gradients for windows named by (target sensor, time index) on a resident CmlSeries.  Returns
+        (attr_nodes [B,T,32,2], attr_anom [B,T,2], scores [B], node_sensor [B,32], n_nodes [B]) as CUDA tensors."""
+        torch = _torch()
+        target = self._dev_tensor(target, torch.int32, "target")
+        t_anom = self._dev_tensor(t_anom, torch.int32, "t_anom")
+        B, T = target.numel(), int(timestep_before) + int(timestep_after) + 1
+        dev = target.device
+        attr_nodes = torch.empty((B, T, 32, 2), dtype=torch.float32, device=dev)
+        attr_anom = torch.empty((B, T, 2), dtype=torch.float32, device=dev)
+        scores = torch.empty(B, dtype=torch.float32, device=dev)
+        node_sensor = torch.empty((B, 32), dtype=torch.int32, device=dev)
+        n_nodes = torch.empty(B, dtype=torch.int32, device=dev)
+        check(lib.gnnqc_ig_cml_series(self._h, series._h, target.data_ptr(), t_anom.data_ptr(), B, int(timestep_before), int(timestep_after),
+                                      int(m_steps), attr_nodes.data_ptr(), attr_anom.data_ptr(), scores.data_ptr(), node_sensor.data_ptr(),
+                                      n_nodes.data_ptr(), self._stream()))
+        return attr_nodes, attr_anom, scores, node_sensor, n_nodes
+
     def ig_cml(self, features, anom, edges, node_off, edge_off, m_steps=50, n_nodes_total=None):
         """Integrated gradients (zero baseline, trapezoid, scaled by the input) for the CML GCN
         model.  Returns (attr_features [Ntot,2], attr_anom [B,T,2], scores [B]) as CUDA tensors."""

@@ -261,6 +261,23 @@ int gnnqc_select_threshold(int device, const float* scores_dev, const int64_t* l
 int gnnqc_roc_auc(int device, const float* scores_dev, const int64_t* labels_dev, int64_t n,
                   double* auc_out, void* stream);
 
+/* Integrated gradients for windows named by (target sensor, time index) on a resident network (BASELINE.json config 4:
+ * the IG sweep over a network that stays in HBM; reference loop prepare_data -> get_gradients ->
+ * _get_gradients_single_batch, xai/libs/integrated_gradients.py:590-703,1093-1246, with the window extraction of
+ * libs/preprocessing_functions.py:388-412).  Same arithmetic as gnnqc_ig_cml on the materialised windows.
+ *   attr_nodes_dev f32 [B, T, 32, 2]  attribution of node n (position in the window's node list) at step t; zero padding
+ *                                     beyond the window's node count, for skipped windows and for steps past the last live one
+ *   attr_anom_dev  f32 [B, T, 2]      attribution of the target series input
+ *   scores_dev     f32 [B]            NaN for windows the reference would skip
+ *   node_sensor_dev i32 [B, 32] (optional)  global sensor id of every node slot (-1 = unused)
+ *   n_nodes_dev    i32 [B] (optional) nodes per window (0 = skipped)
+ * Shards by target sensor over GPUs with no collective: each rank holds its sensors' series plus their neighbours'. */
+int gnnqc_ig_cml_series(gnnqc_model* m, const gnnqc_series* series, const int32_t* target_dev,
+                        const int32_t* t_anom_dev, int64_t B, int32_t timestep_before,
+                        int32_t timestep_after, int32_t m_steps, float* attr_nodes_dev,
+                        float* attr_anom_dev, float* scores_dev, int32_t* node_sensor_dev,
+                        int32_t* n_nodes_dev, void* stream);
+
 /* ---- training ------------------------------------------------------------------------- */
 
 /* Together these replace one train_step of model.fit as train_model sets it up

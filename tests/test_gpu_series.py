@@ -109,3 +109,37 @@ def test_soilnet_series_scoring_matches_materialised_windows():
     finally:
         series.close()
         m.close()
+
+
+def test_series_integrated_gradients_equal_materialised_windows():
+    """gnnqc_ig_cml_series (windows named by (sensor, time) on the resident network) == materialise the windows on the
+    host, then gnnqc_ig_cml: same arithmetic, bit for bit; skipped windows get NaN and zero attributions."""
+    raw, rmed, dist = make_network()
+    nbr_off, nbr_idx, edge_off, edges = neighbourhoods_from_distances(dist, 20.0)
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    series = CmlSeries(raw, rmed, nbr_off, nbr_idx, edge_off, edges, device=0)
+    try:
+        rng = np.random.default_rng(2)
+        n, m_steps, T = 150, 4, 181
+        targets = rng.integers(0, raw.shape[0], size=n).astype(np.int32)
+        t_anom = rng.integers(100, raw.shape[1] - 30, size=n).astype(np.int32)
+        an, aa, p, sens, cnt = m.ig_cml_series(series, torch.tensor(targets).cuda(), torch.tensor(t_anom).cuda(), 120, 60, m_steps=m_steps)
+        an, aa, p, sens, cnt = an.cpu().numpy(), aa.cpu().numpy(), p.cpu().numpy(), sens.cpu().numpy(), cnt.cpu().numpy()
+        batch, kept, want_counts = WB.materialise_windows(raw, rmed, nbr_off, nbr_idx, edge_off, edges, targets, t_anom, 120, 60)
+        assert kept.sum() > 50 and (~kept).sum() > 3
+        assert np.array_equal(cnt, want_counts) and np.array_equal(np.isnan(p), ~kept)
+        assert not an[~kept].any() and not aa[~kept].any()
+        b = {k: torch.as_tensor(v).cuda() for k, v in batch.items() if k != "T"}
+        rf, ra, rp = m.ig_cml(b["features"], b["anom"], b["edges"], b["node_off"], b["edge_off"], m_steps=m_steps)
+        rf, ra, rp = rf.cpu().numpy(), ra.cpu().numpy(), rp.cpu().numpy()
+        assert np.array_equal(p[kept], rp) and np.array_equal(aa[kept], ra)
+        no = batch["node_off"]
+        for i, w in enumerate(np.nonzero(kept)[0]):
+            nn = int(no[i + 1] - no[i])
+            want = rf[no[i] * T: no[i + 1] * T].reshape(T, nn, 2)
+            assert np.array_equal(an[w, :, :nn], want), "window %d" % w
+            assert not an[w, :, nn:].any() and (sens[w, nn:] == -1).all() and (sens[w, :nn] >= 0).all()
+        assert np.abs(an).max() > 0
+    finally:
+        series.close()
+        m.close()
