@@ -49,9 +49,10 @@ WORKLOADS = {
     "soilnet_gcn": ("soilnet_sensor_sequences_scored_per_sec", "sequences/s", "model_soilnet", 256 * N_SOIL),
     "cml_series": ("cml_windows_scored_per_sec_from_resident_series", "windows/s", "model_cml", 65536),
     "ig": ("cml_ig_attributions_per_sec", "attributions/s", "model_cml", 65536),
+    "ig_series": ("cml_ig_attributions_per_sec_from_resident_series", "attributions/s", "model_cml", 64000),
     "train": ("cml_gcn_training_windows_per_sec", "windows/s", "model_cml", 4096),
 }
-NESTED = ["cml_baseline", "soilnet_gcn", "cml_series", "ig", "train_b128", "train_b4096"]
+NESTED = ["cml_baseline", "soilnet_gcn", "cml_series", "ig", "ig_series", "train_b128", "train_b4096"]
 
 # ---- algorithmic work per unit ----------------------------------------------------
 LSTM = {  # (T, in, H) per layer at the full sequence length
@@ -79,14 +80,14 @@ def base_name(wl):
 def alg_flops_per_unit(wl, m_steps=50):
     """LSTM stack + head forward; IG = (m+1) x (forward + input gradient); training = 3 x forward."""
     fwd = sum(lstm_flops(shapes_of(wl))) + HEAD_FLOPS
-    return {"ig": (m_steps + 1) * 2 * fwd, "train": 3 * fwd}.get(base_name(wl), fwd)
+    return {"ig": (m_steps + 1) * 2 * fwd, "ig_series": (m_steps + 1) * 2 * fwd, "train": 3 * fwd}.get(base_name(wl), fwd)
 
 
 def alg_bytes_per_unit(wl):
     """compulsory HBM traffic with materialised windows."""
     cml = 4 * 2 * T_CML * (N_NODES + 1) + 4 * N_NODES + 4                      # 34,848 B
     return {"cml_gcn": cml, "cml_baseline": 4 * 2 * T_CML + 4, "soilnet_gcn": 4 * 3 * T_SOIL + 4, "cml_series": 16 + 8 + 4,
-            "ig": 2 * cml, "train": cml + 4}[base_name(wl)]
+            "ig": 2 * cml, "ig_series": 16 + 8 + 4 + 4 * 2 * T_CML * (32 + 1), "train": cml + 4}[base_name(wl)]
 
 
 def make_config(wl, units, world=1, m_steps=50):
@@ -97,7 +98,7 @@ def make_config(wl, units, world=1, m_steps=50):
            "l2_policy": "no flush: inputs plus inter-layer tiles of one pass exceed the 126 MB L2 many times over",
            "parallelism": "data parallel: NCCL all-reduce of 6 f64 moments + the flat gradient vector per step" if b == "train"
            else "windows sharded over ranks, no collective"}
-    if b == "ig":
+    if b in ("ig", "ig_series"):
         cfg["m_steps"] = m_steps
     if b == "train":
         cfg.update({"class_weights": [1, 5], "optimizer": "adam", "learning_rate": 1e-4, "positives": "1/6"})
@@ -192,7 +193,7 @@ class CpuOracle:
         self.cores = os.cpu_count() or 1
         torch.set_num_threads(self.cores)
         b = base_name(wl)
-        self.no_grad = b not in ("ig", "train")
+        self.no_grad = b not in ("ig", "ig_series", "train")
         w = O.load_weights(os.path.join(MODELS, WORKLOADS[b][2]), torch.float32)
         named = O.load_named(os.path.join(MODELS, WORKLOADS[b][2]))
         self.calls, self.units = [], 0
@@ -205,7 +206,7 @@ class CpuOracle:
                 self.units += N_SOIL
             self.sample = "%d windows of %d sensors, one window per call" % (n_win, N_SOIL)
             return
-        per_call = {"ig": 2, "train": 128}.get(b, self.BATCH)
+        per_call = {"ig": 2, "ig_series": 2, "train": 128}.get(b, self.BATCH)
         for i, lo in enumerate(range(0, sample_units, per_call)):
             n = min(per_call, sample_units - lo)
             self.units += n
@@ -215,7 +216,7 @@ class CpuOracle:
             batch = synth.make_cml_batch(n, seed=44 + i, n_nodes=N_NODES)
             feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 2)
             args = (torch.tensor(feat), batch["anom"], torch.tensor(idx), torch.tensor(samp))
-            if b == "ig":
+            if b in ("ig", "ig_series"):
                 self.calls.append((O.integrated_gradients_cml, args + (w, m_steps)))
             elif b == "train":
                 labels = (torch.rand(n, generator=torch.Generator().manual_seed(i)) < 1.0 / 6.0).long()
@@ -223,7 +224,7 @@ class CpuOracle:
             else:
                 self.calls.append((O.gcn_forward_cml, args + (w,)))
         self.sample = "%d %s in batches of %d" % (self.units, "windows", per_call)
-        if b == "cml_series":
+        if b in ("cml_series", "ig_series"):
             self.sample += " (materialised windows: the oracle has no resident-series path)"
 
     def step(self):
@@ -238,14 +239,14 @@ class CpuOracle:
         return time.perf_counter() - t0
 
 
-CPU_SAMPLE = {"cml_gcn": 1024, "cml_baseline": 8192, "soilnet_gcn": 2 * N_SOIL, "cml_series": 512, "ig": 4, "train": 256}
-REF_SAMPLE = {"cml_gcn": 2048, "cml_baseline": 16384, "soilnet_gcn": 4 * N_SOIL, "cml_series": 2048, "ig": 8, "train": 512}
+CPU_SAMPLE = {"cml_gcn": 1024, "cml_baseline": 8192, "soilnet_gcn": 2 * N_SOIL, "cml_series": 512, "ig": 4, "ig_series": 4, "train": 256}
+REF_SAMPLE = {"cml_gcn": 2048, "cml_baseline": 16384, "soilnet_gcn": 4 * N_SOIL, "cml_series": 2048, "ig": 8, "ig_series": 8, "train": 512}
 
 
 def cpu_baseline(wl, unit, m_steps):
     o = CpuOracle(wl, CPU_SAMPLE[base_name(wl)], m_steps)
     o.step()                                   # warm-up (thread pool, allocator)
-    secs = min(o.step() for _ in range(2 if base_name(wl) != "ig" else 1))
+    secs = min(o.step() for _ in range(1 if base_name(wl) in ("ig", "ig_series") else 2))
     return {"value": o.units / secs, "unit": unit, "cores": o.cores, "kind": "port",
             "sample": "%s, best pass after warm-up (%.1f s); reference TF CPU path unavailable on this box" % (o.sample, secs)}
 
@@ -424,6 +425,49 @@ class Workload:
             self.e2e_path = "gnnqc_series_update (new samples) + window list H2D -> gnnqc_score_cml_series -> D2H"
             self.extra.update({"sensors": S, "consecutive_windows_per_sensor": per, "resident_series_bytes": int(net["raw"].nbytes * 2),
                                "mean_neighbourhood": float(np.diff(net["nbr_off"]).mean())})
+        elif b == "ig_series":
+            # BASELINE.json config 4: the IG sweep over a 4,000-link network that stays resident in HBM, sharded by target
+            # link over the ranks (each rank holds its links plus their neighbour halo; no collective).  The time extent is
+            # cut from one year (525,600 samples) to 16,384 samples per link so that the host can synthesise it in seconds:
+            # the resident arrays scale linearly with it (full year: 16.8 GB raw + 16.8 GB medians + 8.4 GB validity
+            # prefix, inside one B200's 180 GB) and a window only ever touches 181 consecutive samples.
+            from gnnqc.series import CmlSeries, shard_network_by_link
+            np = ctx.np
+            S, Tt = 4000, 16384
+            net = synth.make_cml_network(S, Tt, seed=42)
+            sh = shard_network_by_link(net, rank, world)
+            del net
+            series = self.series = CmlSeries(sh["raw"], sh["rmed"], sh["nbr_off"], sh["nbr_idx"], sh["edge_off"], sh["edges"], device=ctx.local_rank)
+            owned = torch.tensor(sh["owned_local"], dtype=torch.int32)
+            per = max(1, B // owned.numel())
+            units = B = owned.numel() * per
+            tgt_h = owned.repeat_interleave(per).pin_memory()
+            tau_h = (8000 + torch.arange(per, dtype=torch.int32)).repeat(owned.numel()).pin_memory()
+            tgt_d, tau_d = tgt_h.to(dev), tau_h.to(dev)
+            self.step = lambda: model.ig_cml_series(series, tgt_d, tau_d, 120, 60, self.m_steps)[2]
+            self.in_bytes = B * 8
+            pinned = {}
+
+            def to_host(name, t):
+                if name not in pinned:
+                    pinned[name] = torch.empty(t.shape, dtype=t.dtype).pin_memory()
+                pinned[name].copy_(t, non_blocking=True)
+                return pinned[name]
+
+            def e2e():   # window list up, both attribution arrays, the node lists and the scores down
+                an, aa, p, sens, cnt = model.ig_cml_series(series, tgt_h.to(dev, non_blocking=True), tau_h.to(dev, non_blocking=True), 120, 60, self.m_steps)
+                res = to_host("an", an), to_host("aa", aa), to_host("p", p), to_host("sens", sens), to_host("cnt", cnt)
+                torch.cuda.synchronize()
+                return res[2]
+            self.e2e_step = e2e
+            self.h2d = B * 8
+            self.d2h = B * (T_CML * 33 * 8 + 4 + 32 * 4 + 4)
+            self.e2e_path = "window list H2D -> gnnqc_ig_cml_series on the resident network -> D2H of attributions [B,T,32,2] + [B,T,2], node lists, scores"
+            self.extra.update({"links_total": S, "links_owned_by_rank0": int(owned.numel()), "links_resident_on_rank0_incl_halo": int(sh["global_ids"].size),
+                               "samples_per_link": Tt, "consecutive_windows_per_link": per,
+                               "resident_bytes": int(sh["raw"].nbytes * 2 + sh["raw"].shape[0] * (Tt + 1) * 4),
+                               "mean_neighbourhood": float(np.diff(sh["nbr_off"])[sh["owned_local"]].mean()),
+                               "note": "time extent cut from 525,600 to 16,384 samples per link (host synthesis time); throughput does not depend on it"})
         elif b == "cml_baseline":
             from gnnqc.host_pipeline import SeqHostScorer
             x = self.x = synth.make_seq_batch(B, 2, T_CML, seed=44 + rank, device=str(dev))
@@ -466,6 +510,8 @@ class Workload:
         w = O.load_weights(os.path.join(MODELS, self.model_name), torch.float64)
         torch.set_num_threads(os.cpu_count() or 1)
         t0 = time.perf_counter()
+        if b == "ig_series":
+            return None      # bit-identical to gnnqc_ig_cml on the materialised windows (tests/test_gpu_series.py), which the "ig" workload checks
         if b in ("cml_gcn", "ig", "train"):
             n = {"cml_gcn": 1024, "ig": 1, "train": min(128, self.units)}[b]
             eo, no = self.batch["edge_off"][: n + 1].cpu(), self.batch["node_off"][: n + 1].cpu()
@@ -585,7 +631,7 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
     value = world * units * passes / (ms_step * 1e-3)
 
     # ---- per-kernel times (CUDA events around every launch, on the launching stream) ---------------------
-    prof_passes = 1 if W.base == "ig" else max(1, min(passes * steps, 10))
+    prof_passes = 1 if W.base in ("ig", "ig_series") else max(1, min(passes * steps, 10))
     model.profile(True)
     for _ in range(prof_passes):
         W.step()
@@ -627,7 +673,7 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
     pk = ctx.peaks
     shapes = shapes_of(wl)
     fl_alg, fl_live = lstm_flops(shapes), lstm_flops(shapes, live=True)
-    n_pass = (W.m_steps + 1) if W.base == "ig" else 1
+    n_pass = (W.m_steps + 1) if W.base in ("ig", "ig_series") else 1
     kernels, lstm = [], []
     for name, (ms, cnt) in sorted(prof.items(), key=lambda kv: -kv[1][0]):
         k = {"name": name, "ms_per_pass": ms / prof_passes, "launches_per_pass": cnt / prof_passes}
@@ -647,7 +693,7 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
     fp32 = ctypes.c_double()
     ctx.lib.gnnqc_probe_fp32_peak(ctx.local_rank, 1, ctypes.byref(fp32))
     traffic = ctx.traffic.get(wl)
-    if W.base in ("ig", "train"):
+    if W.base in ("ig", "ig_series", "train"):
         # forward + backward (+ weight gradients): the unit's whole algorithmic FLOPs against the whole pass
         sec = ms_step / passes * 1e-3
         ach = alg_flops_per_unit(wl, W.m_steps) * units / sec / 1e12
@@ -658,7 +704,7 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
                     "frac_of_fp32_cuda_core_peak": ach / fp32.value if fp32.value else None,
                     "note": "SURVEY 8(d) FLOPs per unit x units / pass time; the contractions run on tcgen05 with split-bf16 operands "
                             "(3 MMA passes per product), the weight gradients on the CUDA cores"}
-        if W.base == "ig":
+        if W.base in ("ig", "ig_series"):
             saved = 234e3 * (W.m_steps + 1) * 2   # bytes of saved gates written + read per attribution
             roofline["saved_gate_stream"] = {"bound": "hbm", "achieved": saved * units / sec / 1e9, "peak": pk["hbm"], "unit": "GB/s",
                                              "frac": saved * units / sec / 1e9 / pk["hbm"]}
@@ -726,6 +772,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="gnnqc", choices=["gnnqc", "reference"])
     ap.add_argument("--workload", default=None, choices=sorted(WORKLOADS) + ["train_b128", "train_b4096"])
+    ap.add_argument("--skip", default="", help="comma-separated nested workloads to leave out of the default run")
     ap.add_argument("--windows", type=int, default=0, help="units per GPU per pass (0 = workload default)")
     ap.add_argument("--m-steps", type=int, default=50, help="IG interpolation steps")
     ap.add_argument("--chunk-windows", type=int, default=8192, help="chunk size of the host-buffer scoring call")
@@ -768,7 +815,7 @@ def main():
     if args.workload is None and not args.only_primary:
         ctx.nested = True
         nested = {}
-        for wl in NESTED:
+        for wl in [w for w in NESTED if w not in args.skip.split(",")]:
             sub = measure(wl, ctx, args, max(2, min(args.steps, 5)), 3)
             if sub is not None:
                 nested[wl] = sub

@@ -188,6 +188,7 @@ int gnnqc_model_save(const gnnqc_model* m, const char* dir) {
   if (!m || !dir) return fail(GNNQC_ERR_ARG, "gnnqc_model_save: null argument");
   return guarded([&] {
     const_cast<gnnqc_model*>(m)->dm.sync_host_params();
+    const_cast<gnnqc_model*>(m)->dm.sync_host_optimizer();
     gnnqc::save_saved_model(m->dm.host, dir);
   });
 }
@@ -325,6 +326,20 @@ int gnnqc_train_grads_seq(gnnqc_model* m, const float* x_dev, const int64_t* lab
     m->dm.train_grads(nullptr, nullptr, nullptr, nullptr, nullptr, x_dev, reinterpret_cast<const long long*>(labels_dev), n_seq, T, 0, nullptr,
                       class_weight_0, class_weight_1, global_batch, rvec_dev, static_cast<cudaStream_t>(stream));
   });
+}
+
+int gnnqc_train_set_optimizer(gnnqc_model* m, int kind) {
+  if (int rc = need_device(m, "gnnqc_train_set_optimizer")) return rc;
+  if (kind < 0 || kind > 2) return fail(GNNQC_ERR_ARG, "gnnqc_train_set_optimizer: kind must be 0 (adam), 1 (sgd) or 2 (rmsprop)");
+  return guarded([&] {
+    GNNQC_CUDA(cudaSetDevice(m->dm.device));
+    m->dm.set_optimizer(kind);
+  });
+}
+
+int64_t gnnqc_train_iterations(const gnnqc_model* m) {
+  if (!m) return 0;
+  return m->dm.train_iterations();
 }
 
 int gnnqc_train_apply(gnnqc_model* m, float* rvec_dev, const double* moments_dev, float learning_rate, void* stream) {

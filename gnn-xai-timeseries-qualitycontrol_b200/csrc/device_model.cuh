@@ -128,6 +128,9 @@ struct DeviceModel {
   TrainState* train_state();
   void free_train_state();
   void sync_host_params();
+  void sync_host_optimizer();
+  long long train_iterations() const;
+  void set_optimizer(int kind);      // 0 adam | 1 sgd | 2 rmsprop
   void train_moments(const float* feat, long long n_rows, double* moments, cudaStream_t stream);
   void train_grads(const float* feat, const float* anom, const long long* edges, const int* node_off, const long long* edge_off,
                    const float* x_seq, const long long* labels, long long B, int T, long long n_nodes, const double* moments,

@@ -165,21 +165,49 @@ HostModel load_saved_model(const std::string& dir) {
     std::vector<float> v = r.read_f32(key);
     std::copy(v.begin(), v.end(), m.params.begin() + seg.offset);
   }
+  // Optimizer slots (absent from checkpoints written without them, e.g. tests/golden/models): the k-th trainable variable
+  // in checkpoint order owns optimizer/_variables/(2k+1) (m) and (2k+2) (v) for Adam, or /(k+1) for RMSprop.
+  const std::string it_key = std::string("optimizer/_iterations") + kVarSuffix;
+  if (r.has(it_key)) {
+    std::vector<int64_t> it = r.read_i64(it_key);
+    m.opt_iterations = it.empty() ? 0 : it[0];
+    const std::string lr_key = std::string("optimizer/_learning_rate") + kVarSuffix;
+    if (r.has(lr_key)) { std::vector<float> lr = r.read_f32(lr_key); m.opt_learning_rate = lr.empty() ? 0.f : lr[0]; }
+    std::vector<ParamSegment> trainable;
+    for (const ParamSegment& seg : checkpoint_order(m.spec))
+      if (seg.trainable) trainable.push_back(seg);
+    const int n_tr = static_cast<int>(trainable.size());
+    auto slot_key = [](int n) { return "optimizer/_variables/" + std::to_string(n) + kVarSuffix; };
+    const bool adam = r.has(slot_key(2 * n_tr)) && !r.has(slot_key(2 * n_tr + 1));
+    const bool rms = !adam && r.has(slot_key(n_tr)) && !r.has(slot_key(n_tr + 1));
+    if (adam || rms) {
+      m.optimizer = adam ? 0 : 2;
+      m.opt_v.assign(static_cast<size_t>(m.spec.n_params), 0.f);
+      if (adam) m.opt_m.assign(static_cast<size_t>(m.spec.n_params), 0.f);
+      for (int k = 0; k < n_tr; ++k) {
+        const ParamSegment& seg = trainable[k];
+        for (int which = 0; which < (adam ? 2 : 1); ++which) {
+          const std::string key = slot_key(adam ? 2 * k + 1 + which : k + 1);
+          if (r.entry(key).shape != seg.shape) throw std::runtime_error("load_saved_model: optimizer slot '" + key + "' does not match '" + seg.path + "'");
+          std::vector<float> v = r.read_f32(key);
+          std::vector<float>& dst = (adam && which == 0) ? m.opt_m : m.opt_v;
+          std::copy(v.begin(), v.end(), dst.begin() + seg.offset);
+        }
+      }
+    } else {
+      m.optimizer = 1;   // iteration counter without slots: plain SGD
+    }
+  }
   return m;
 }
 
-void save_saved_model(const HostModel& m, const std::string& dir) {
-  std::error_code ec;
-  std::filesystem::create_directories(dir + "/variables", ec);
-  if (ec) throw std::runtime_error("save_saved_model: cannot create " + dir + "/variables: " + ec.message());
-  const ModelSpec& s = m.spec;
-  std::vector<ParamSegment> segs = param_segments(s);
-  // The reference checkpoints number `variables/N` as Keras lists them: GCN block, then the
-  // stacked layers (time_layers), then time1, time2, time4, then the head.
-  std::vector<int> order;
+// The reference checkpoints number `variables/N` as Keras lists them: GCN block, then the stacked layers (time_layers),
+// then time1, time2, time4, then the head.
+std::vector<ParamSegment> checkpoint_order(const ModelSpec& s) {
+  std::vector<ParamSegment> segs = param_segments(s), out;
   auto add_if = [&](const std::string& needle) {
-    for (int i = 0; i < static_cast<int>(segs.size()); ++i)
-      if (segs[i].path.find(needle) != std::string::npos) order.push_back(i);
+    for (const ParamSegment& seg : segs)
+      if (seg.path.find(needle) != std::string::npos) out.push_back(seg);
   };
   add_if("gcn_layer/");
   add_if("time_layers/");
@@ -187,13 +215,44 @@ void save_saved_model(const HostModel& m, const std::string& dir) {
   add_if("time2/");
   add_if("time4/");
   add_if("dense");
+  return out;
+}
+
+void save_saved_model(const HostModel& m, const std::string& dir) {
+  std::error_code ec;
+  std::filesystem::create_directories(dir + "/variables", ec);
+  if (ec) throw std::runtime_error("save_saved_model: cannot create " + dir + "/variables: " + ec.message());
+  const ModelSpec& s = m.spec;
+  const std::vector<ParamSegment> order = checkpoint_order(s);
   BundleWriter w;
   const std::string cls = s.has_gcn ? "gcn_classifier/" : "baseline_classifier/";
   for (int n = 0; n < static_cast<int>(order.size()); ++n) {
-    const ParamSegment& seg = segs[order[n]];
+    const ParamSegment& seg = order[n];
     std::string key = "variables/" + std::to_string(n) + kVarSuffix;
     w.add_f32(key, seg.shape, m.params.data() + seg.offset);
     w.track(seg.path, key, cls + seg.path);
+  }
+  // Optimizer state, when a training run produced some (model.save keeps it: SURVEY.md section 5, checkpoint row).
+  if (m.opt_iterations > 0) {
+    const std::string it_key = std::string("optimizer/_iterations") + kVarSuffix, lr_key = std::string("optimizer/_learning_rate") + kVarSuffix;
+    const int64_t it = m.opt_iterations;
+    w.add_i64(it_key, {}, &it);
+    w.track("optimizer/_iterations", it_key, "iteration");
+    w.add_f32(lr_key, {}, &m.opt_learning_rate);
+    w.track("optimizer/_learning_rate", lr_key, "learning_rate");
+    const char* const kind = m.optimizer == 0 ? "Adam" : "RMSprop";
+    int n = 0;
+    for (const ParamSegment& seg : order) {
+      if (!seg.trainable || m.optimizer == 1) continue;
+      for (int which = 0; which < (m.optimizer == 0 ? 2 : 1); ++which) {
+        const std::vector<float>& src = (m.optimizer == 0 && which == 0) ? m.opt_m : m.opt_v;
+        if (src.size() != m.params.size()) continue;
+        const std::string path = "optimizer/_variables/" + std::to_string(++n);
+        const std::string key = path + kVarSuffix;
+        w.add_f32(key, seg.shape, src.data() + seg.offset);
+        w.track(path, key, std::string(kind) + (m.optimizer == 0 ? (which == 0 ? "/m/" : "/v/") : "/velocity/") + cls + seg.path);
+      }
+    }
   }
   if (!m.model_info.empty()) {
     std::string key = std::string("model_info") + kVarSuffix;

@@ -55,6 +55,13 @@ struct HostModel {
   std::vector<int32_t> model_info;  // [timestep_before, timestep_after, batch_size(, freq)]
   std::string ds_type;              // "cml" | "soilnet"
   std::string normalization;        // "rolling_median" | "scale_range" | ...
+  // Optimizer state as model.save keeps it (Keras 2.11 optimizer: optimizer/_iterations, optimizer/_learning_rate,
+  // optimizer/_variables/1.. = the slots of every trainable variable in order: Adam m, v interleaved; RMSprop one
+  // velocity each; plain SGD none).  Flat, in parameter-vector layout (moving statistics unused); empty = none saved.
+  int optimizer = 0;                // 0 adam | 1 sgd | 2 rmsprop  (libs/fit_model.py:71-74)
+  long long opt_iterations = 0;
+  float opt_learning_rate = 0.f;
+  std::vector<float> opt_m, opt_v;
 };
 
 // `dir` is a SavedModel directory (containing variables/variables.index) or the
@@ -74,5 +81,6 @@ struct ParamSegment {
   bool trainable;
 };
 std::vector<ParamSegment> param_segments(const ModelSpec& s);
+std::vector<ParamSegment> checkpoint_order(const ModelSpec& s);   // the order of `variables/N` in the reference's checkpoints
 
 }  // namespace gnnqc

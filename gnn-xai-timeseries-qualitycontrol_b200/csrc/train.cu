@@ -116,6 +116,8 @@ struct TrainState {
   GcnFolded* folded = nullptr;
   BnBatch* stats = nullptr;
   long long step = 0;
+  int kind = 0;            // 0 adam | 1 sgd | 2 rmsprop
+  float last_lr = 0.f;
 };
 
 void DeviceModel::configure_train_kernels() {
@@ -137,6 +139,12 @@ TrainState* DeviceModel::train_state() {
     GNNQC_CUDA(cudaMalloc(&train->vel, n * sizeof(float)));
     GNNQC_CUDA(cudaMemset(train->mom, 0, n * sizeof(float)));
     GNNQC_CUDA(cudaMemset(train->vel, 0, n * sizeof(float)));
+    // a checkpoint written by model.save carries the optimizer state: resume where it stopped
+    train->kind = host.optimizer;
+    train->step = host.opt_iterations;
+    train->last_lr = host.opt_learning_rate;
+    if (host.opt_m.size() == n) GNNQC_CUDA(cudaMemcpy(train->mom, host.opt_m.data(), n * sizeof(float), cudaMemcpyHostToDevice));
+    if (host.opt_v.size() == n) GNNQC_CUDA(cudaMemcpy(train->vel, host.opt_v.data(), n * sizeof(float), cudaMemcpyHostToDevice));
     GNNQC_CUDA(cudaMalloc(&train->folded, sizeof(GcnFolded)));
     GNNQC_CUDA(cudaMalloc(&train->stats, sizeof(BnBatch)));
   }
@@ -151,6 +159,36 @@ void DeviceModel::free_train_state() {
   cudaFree(train->stats);
   delete train;
   train = nullptr;
+}
+
+void DeviceModel::set_optimizer(int kind) {
+  if (kind < 0 || kind > 2) throw std::invalid_argument("optimizer must be 0 (adam), 1 (sgd) or 2 (rmsprop)");
+  TrainState* ts = train_state();
+  if (ts->kind != kind) {   // slots of another rule mean nothing to this one
+    const size_t n = size_t(host.spec.n_params);
+    GNNQC_CUDA(cudaMemset(ts->mom, 0, n * sizeof(float)));
+    GNNQC_CUDA(cudaMemset(ts->vel, 0, n * sizeof(float)));
+    ts->step = 0;
+  }
+  ts->kind = kind;
+  host.optimizer = kind;
+}
+
+long long DeviceModel::train_iterations() const { return train ? train->step : host.opt_iterations; }
+
+// Brings the optimizer state to the host copy (for gnnqc_model_save).
+void DeviceModel::sync_host_optimizer() {
+  if (!train || device < 0) return;
+  GNNQC_CUDA(cudaSetDevice(device));
+  GNNQC_CUDA(cudaDeviceSynchronize());
+  const size_t n = size_t(host.spec.n_params);
+  host.optimizer = train->kind;
+  host.opt_iterations = train->step;
+  host.opt_learning_rate = train->last_lr;
+  host.opt_m.assign(train->kind == 0 ? n : 0, 0.f);
+  host.opt_v.assign(train->kind != 1 ? n : 0, 0.f);
+  if (train->kind == 0) GNNQC_CUDA(cudaMemcpy(host.opt_m.data(), train->mom, n * sizeof(float), cudaMemcpyDeviceToHost));
+  if (train->kind != 1) GNNQC_CUDA(cudaMemcpy(host.opt_v.data(), train->vel, n * sizeof(float), cudaMemcpyDeviceToHost));
 }
 
 void DeviceModel::sync_host_params() {
@@ -411,11 +449,12 @@ void DeviceModel::train_apply(float* rvec, const double* moments, float lr, cuda
     skip_hi = s.off_bn_var + kGcnChannels;
   }
   ts->step += 1;
+  ts->last_lr = lr;
   const double b1 = 0.9, b2 = 0.999;
-  const float lr_t = static_cast<float>(lr * std::sqrt(1.0 - std::pow(b2, double(ts->step))) / (1.0 - std::pow(b1, double(ts->step))));
+  const float lr_t = ts->kind == 0 ? static_cast<float>(lr * std::sqrt(1.0 - std::pow(b2, double(ts->step))) / (1.0 - std::pow(b1, double(ts->step)))) : lr;
   mark_begin("adam", st);
   adam_kernel<<<static_cast<unsigned>((np + 255) / 256), 256, 0, st>>>(d_params, rvec, ts->mom, ts->vel, np, lr_t, 0.9f, 0.999f, 1e-7f, skip_lo,
-                                                                       skip_hi, ts->stats, 0.99f);
+                                                                       skip_hi, ts->stats, 0.99f, ts->kind);
   GNNQC_CUDA(cudaGetLastError());
   mark_end(st);
   for (int l = 0; l < s.n_lstm; ++l) {

@@ -593,10 +593,12 @@ static __global__ void gcn_finalize3_kernel(float* __restrict__ rvec, long long 
 // Keras Adam (beta1 0.9, beta2 0.999, epsilon 1e-7), lr_t = lr*sqrt(1-b2^t)/(1-b1^t).
 // Entries in [skip_lo, skip_hi) are the BatchNorm moving statistics: not trained, moved towards the
 // batch statistics with momentum 0.99 instead.
+// kind 1: plain SGD (Keras default momentum 0): p -= lr g.  kind 2: RMSprop (rho 0.9, epsilon 1e-7, no momentum, not
+// centered): v = rho v + (1 - rho) g^2, p -= lr g / (sqrt(v) + eps).  (libs/fit_model.py:71-74 accepts all three.)
 static __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ params, const float* __restrict__ grad, float* __restrict__ mom,
                                                           float* __restrict__ vel, long long n, float lr_t, float b1, float b2, float eps,
                                                           long long skip_lo, long long skip_hi, const BnBatch* __restrict__ stats,
-                                                          float bn_momentum) {
+                                                          float bn_momentum, int kind = 0) {
   const long long i = static_cast<long long>(blockIdx.x) * blockDim.x + threadIdx.x;
   if (i >= n) return;
   if (i >= skip_lo && i < skip_hi) {
@@ -606,6 +608,16 @@ static __global__ void __launch_bounds__(256) adam_kernel(float* __restrict__ pa
     return;
   }
   const float g = grad[i];
+  if (kind == 1) {
+    params[i] -= lr_t * g;
+    return;
+  }
+  if (kind == 2) {
+    const float v = 0.9f * vel[i] + 0.1f * g * g;
+    vel[i] = v;
+    params[i] -= lr_t * g / (sqrtf(v) + eps);
+    return;
+  }
   const float m = b1 * mom[i] + (1.f - b1) * g;
   const float v = b2 * vel[i] + (1.f - b2) * g * g;
   mom[i] = m;

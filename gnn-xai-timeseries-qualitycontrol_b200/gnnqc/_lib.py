@@ -94,6 +94,8 @@ def _load():
         "gnnqc_train_moments_soilnet": (C.c_int, [vp, vp, i64, vp, vp]),
         "gnnqc_train_grads_soilnet": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, i64, vp, C.c_float, C.c_float, i64, vp, vp]),
         "gnnqc_train_grads_seq": (C.c_int, [vp, vp, vp, i64, i32, C.c_float, C.c_float, i64, vp, vp]),
+        "gnnqc_train_set_optimizer": (C.c_int, [vp, C.c_int]),
+        "gnnqc_train_iterations": (i64, [vp]),
         "gnnqc_train_apply": (C.c_int, [vp, vp, vp, C.c_float, vp]),
         "gnnqc_score_scratch_bytes": (i64, [vp, i64, i32]),
         "gnnqc_launch_count": (i64, [vp]),

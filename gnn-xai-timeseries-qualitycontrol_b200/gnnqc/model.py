@@ -351,6 +351,16 @@ class NativeModel:
                                         float(class_weights[1]), int(global_batch or x.shape[0]), rvec.data_ptr(), self._stream()))
         return rvec
 
+    def set_optimizer(self, name):
+        """'adam' (default), 'sgd' or 'rmsprop' - the rules train_model accepts (libs/fit_model.py:71-74), Keras defaults."""
+        kinds = {"adam": 0, "sgd": 1, "rmsprop": 2}
+        if name not in kinds:
+            raise ValueError("optimizer must be one of %s" % sorted(kinds))
+        check(lib.gnnqc_train_set_optimizer(self._h, kinds[name]))
+
+    def train_iterations(self):
+        return int(lib.gnnqc_train_iterations(self._h))
+
     def train_apply(self, rvec, moments=None, learning_rate=1e-4):
         torch = _torch()
         rvec = self._dev_tensor(rvec, torch.float32, "rvec")

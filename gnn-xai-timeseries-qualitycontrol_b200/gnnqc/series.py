@@ -25,6 +25,39 @@ def neighbourhoods_from_distances(dist, max_distance):
             np.concatenate(edges).astype(np.int64).reshape(-1, 2))
 
 
+def shard_network_by_link(net, rank, world_size):
+    """Shards a network (dict with raw, rmed [S,Tt,2], nbr_off, nbr_idx, edge_off, edges as CmlSeries takes them) by
+    TARGET link for one rank of a multi-GPU job (scoring / IG shard by link with no collective, the
+    reference's analogue is the SLURM file split, xai/libs/integrated_gradients.py:432-448).  The rank keeps the series of
+    its own links plus the halo - every link that appears in one of their neighbourhoods - renumbered densely; halo links
+    get an empty neighbourhood (they are never targets here).  Returns the sharded dict plus
+      'owned_global'  global ids of this rank's target links (contiguous range)
+      'owned_local'   their row in the sharded arrays
+      'global_ids'    global id of every local row (targets + halo)"""
+    nbr_off, nbr_idx = np.asarray(net["nbr_off"]), np.asarray(net["nbr_idx"])
+    edge_off, edges = np.asarray(net["edge_off"]), np.asarray(net["edges"]).reshape(-1, 2)
+    S = nbr_off.size - 1
+    base, rem = divmod(S, world_size)
+    lo = rank * base + min(rank, rem)
+    hi = lo + base + (1 if rank < rem else 0)
+    owned = np.arange(lo, hi)
+    needed = np.unique(np.concatenate([nbr_idx[nbr_off[lo]: nbr_off[hi]], owned])).astype(np.int64)
+    remap = np.full(S, -1, dtype=np.int64)
+    remap[needed] = np.arange(needed.size)
+    is_owned = (needed >= lo) & (needed < hi)
+    n_nbr = np.where(is_owned, nbr_off[needed + 1] - nbr_off[needed], 0)
+    n_edge = np.where(is_owned, edge_off[needed + 1] - edge_off[needed], 0)
+    new_nbr_off = np.concatenate([[0], np.cumsum(n_nbr)]).astype(np.int32)
+    new_edge_off = np.concatenate([[0], np.cumsum(n_edge)]).astype(np.int64)
+    # the owned range is contiguous in the global arrays, and `needed` is sorted, so its owned rows keep their order
+    new_nbr_idx = remap[nbr_idx[nbr_off[lo]: nbr_off[hi]]].astype(np.int32)
+    new_edges = edges[edge_off[lo]: edge_off[hi]].astype(np.int64)
+    out = {"raw": np.ascontiguousarray(np.asarray(net["raw"])[needed]), "rmed": np.ascontiguousarray(np.asarray(net["rmed"])[needed]),
+           "nbr_off": new_nbr_off, "nbr_idx": new_nbr_idx, "edge_off": new_edge_off, "edges": new_edges,
+           "owned_global": owned, "owned_local": remap[owned].astype(np.int32), "global_ids": needed}
+    return out
+
+
 class CmlSeries:
     """raw, rmed: float32 [n_sensors, n_times, 2] (NaN = missing)."""
 

@@ -5,7 +5,7 @@ libgnnqc.so (gnnqc_train_*), data-parallel over torch.distributed when a process
 Differences that follow from not having Keras: batches are python iterables of
 (inputs, labels) with inputs in the offsets layout of include/gnnqc.h (dict) or the plain
 [B,T,2] tensor of the baseline; metrics are computed on the host with scikit-learn at epoch end;
-PlotLossesKeras is dropped.  The optimiser is Adam only (the shipped configs use 'adam').
+PlotLossesKeras is dropped.  Optimisers: adam, sgd, rmsprop with the Keras defaults, as in the reference.
 """
 import copy
 
@@ -122,8 +122,9 @@ def train_step(native, inputs, labels, class_weights, lr):
 def train_model(model, model_config, preproc_config, train_dataset_batched, val_dataset_batched=None, baseline=False,
                 classes_weights=None, labels=None, checkpoint_path=None):
     """Returns (history, model).  history: dict of per-epoch lists (loss, val_loss, lr, MCC_score_*)."""
-    if model_config.optimizer != "adam":
-        raise NotImplementedError("only optimizer='adam' is built")
+    if model_config.optimizer not in ("adam", "sgd", "rmsprop"):
+        raise ValueError("optimizer must be 'adam', 'sgd' or 'rmsprop' (libs/fit_model.py:71-74)")
+    model.native.set_optimizer(model_config.optimizer)
     classes_weights = calculate_weights(model_config, train_dataset_batched)
     train_batches = list(train_dataset_batched)
     val_batches = list(val_dataset_batched) if val_dataset_batched is not None else None

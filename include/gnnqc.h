@@ -321,6 +321,13 @@ int gnnqc_train_grads_soilnet(gnnqc_model* m, const float* features_dev, const i
 int gnnqc_train_grads_seq(gnnqc_model* m, const float* x_dev, const int64_t* labels_dev, int64_t n_seq,
                           int32_t T, float class_weight_0, float class_weight_1, int64_t global_batch,
                           float* rvec_dev, void* stream);
+/* model.compile(optimizer=...) of train_model (libs/fit_model.py:71-74): 0 = Adam (default), 1 = SGD, 2 = RMSprop, all with
+ * the Keras defaults and the learning rate given to gnnqc_train_apply.  Changing the rule clears the slots.
+ * gnnqc_model_save writes the optimizer state the way model.save does (optimizer/_iterations, optimizer/_learning_rate,
+ * optimizer/_variables/N) and gnnqc_model_load restores it, so a resumed run continues at the saved step;
+ * gnnqc_train_iterations returns that step. */
+int gnnqc_train_set_optimizer(gnnqc_model* m, int kind);
+int64_t gnnqc_train_iterations(const gnnqc_model* m);
 int gnnqc_train_apply(gnnqc_model* m, float* rvec_dev, const double* moments_dev,
                       float learning_rate, void* stream);
 

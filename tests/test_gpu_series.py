@@ -143,3 +143,27 @@ def test_series_integrated_gradients_equal_materialised_windows():
     finally:
         series.close()
         m.close()
+
+
+def test_link_sharded_series_scores_equal_the_whole_network():
+    """A rank that holds only its links plus the neighbour halo scores its targets exactly as the whole network does."""
+    from gnnqc.series import shard_network_by_link
+    net = synth.make_cml_network(48, 400, seed=9, mean_neighbours=7)
+    m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
+    full = CmlSeries(net["raw"], net["rmed"], net["nbr_off"], net["nbr_idx"], net["edge_off"], net["edges"], device=0)
+    try:
+        t = torch.full((48,), 250, dtype=torch.int32).cuda()
+        want = m.score_cml_series(full, torch.arange(48, dtype=torch.int32).cuda(), t, 120, 60).cpu().numpy()
+        got = np.full(48, np.nan, dtype=np.float32)
+        for rank in range(3):
+            sh = shard_network_by_link(net, rank, 3)
+            part = CmlSeries(sh["raw"], sh["rmed"], sh["nbr_off"], sh["nbr_idx"], sh["edge_off"], sh["edges"], device=0)
+            try:
+                tgt = torch.tensor(sh["owned_local"]).cuda()
+                got[sh["owned_global"]] = m.score_cml_series(part, tgt, t[: tgt.numel()], 120, 60).cpu().numpy()
+            finally:
+                part.close()
+        assert np.array_equal(got, want, equal_nan=True) and np.isfinite(want).sum() > 30
+    finally:
+        full.close()
+        m.close()

@@ -269,3 +269,60 @@ def test_soilnet_loss_goes_down_and_windows_shard():
         assert torch.isfinite(s).all()
     finally:
         m.close()
+
+
+def test_optimizer_state_round_trips_and_other_rules(tmp_path):
+    """model.save keeps the Adam slots and the iteration counter: a run resumed from the saved
+    directory takes exactly the step the uninterrupted run takes.  SGD and RMSprop follow the Keras update rules."""
+    x = synth.make_seq_batch(64, 2, 181, seed=21).cuda()
+    labels = make_labels(64, 9).cuda()
+
+    def step(model, lr=1e-3):
+        rvec = model.train_grads_seq(x, labels)
+        g = rvec[: model.n_params].cpu().numpy().astype(np.float64)
+        model.train_apply(rvec, None, lr)
+        return g
+
+    a = NativeModel.load(os.path.join(MODELS, "model_cml_baseline"), device=0)
+    try:
+        step(a); step(a)
+        a.save(tmp_path / "mid")
+        assert a.train_iterations() == 2
+        step(a)
+        want = a.get_params()
+    finally:
+        a.close()
+    import ckpt_reader as R
+    bundle = R.read_bundle(str(tmp_path / "mid" / "variables" / "variables"))
+    assert int(bundle["optimizer/_iterations/.ATTRIBUTES/VARIABLE_VALUE"]) == 2
+    assert sum(k.startswith("optimizer/_variables/") for k in bundle) == 2 * 27     # m and v of the 27 trainable tensors
+    names = {key: full for key, _, full in R.object_graph(bundle)}
+    assert names["optimizer/_variables/1/.ATTRIBUTES/VARIABLE_VALUE"].startswith("Adam/m/")
+    assert names["optimizer/_variables/2/.ATTRIBUTES/VARIABLE_VALUE"].startswith("Adam/v/")
+    b = NativeModel.load(tmp_path / "mid", device=0)
+    try:
+        assert b.train_iterations() == 2
+        step(b)
+        assert np.array_equal(b.get_params(), want)
+    finally:
+        b.close()
+
+    for name in ("sgd", "rmsprop"):
+        m = NativeModel.load(os.path.join(MODELS, "model_cml_baseline"), device=0)
+        try:
+            m.set_optimizer(name)
+            before = m.get_params().astype(np.float64)
+            g = step(m, 1e-3)
+            after = m.get_params()
+            want = before - 1e-3 * g if name == "sgd" else before - 1e-3 * g / (np.sqrt(0.1 * g * g) + 1e-7)
+            np.testing.assert_allclose(after, want, rtol=0, atol=3e-7)
+            if name == "rmsprop":
+                g2 = step(m, 1e-3)
+                v = 0.9 * 0.1 * g * g + 0.1 * g2 * g2
+                np.testing.assert_allclose(m.get_params(), want - 1e-3 * g2 / (np.sqrt(v) + 1e-7), rtol=0, atol=5e-7)
+                m.save(tmp_path / "rms")
+                again = NativeModel.load(tmp_path / "rms", device=0)
+                assert again.train_iterations() == 2
+                again.close()
+        finally:
+            m.close()

@@ -22,3 +22,30 @@ def test_disjoint_round_trip_with_trailing_empty_windows():
                 want = b["edges"][b["edge_off"][w]: b["edge_off"][w + 1]]
                 assert sorted(map(tuple, got.tolist())) == sorted(map(tuple, want.tolist()))
             assert torch.equal(layout.node_offsets(samp, n_windows, T), node_off)
+
+
+def test_link_shards_keep_every_target_neighbourhood():
+    """shard_network_by_link: the ranks' target ranges partition the links, every target's neighbourhood and adjacency
+    survive the renumbering, halo links carry their series but no neighbourhood."""
+    import numpy as np
+
+    from gnnqc.series import shard_network_by_link
+    net = synth.make_cml_network(60, 64, seed=5, mean_neighbours=6)
+    seen = []
+    for world in (1, 3, 8):
+        for rank in range(world):
+            sh = shard_network_by_link(net, rank, world)
+            g = sh["global_ids"]
+            assert np.array_equal(sh["raw"], net["raw"][g], equal_nan=True) and np.array_equal(sh["rmed"], net["rmed"][g])
+            for s_glob, s_loc in zip(sh["owned_global"], sh["owned_local"]):
+                assert g[s_loc] == s_glob
+                a, b = net["nbr_off"][s_glob], net["nbr_off"][s_glob + 1]
+                la, lb = sh["nbr_off"][s_loc], sh["nbr_off"][s_loc + 1]
+                assert np.array_equal(g[sh["nbr_idx"][la:lb]], net["nbr_idx"][a:b])          # same sensors, same order
+                ea, eb = net["edge_off"][s_glob], net["edge_off"][s_glob + 1]
+                assert np.array_equal(sh["edges"][sh["edge_off"][s_loc]: sh["edge_off"][s_loc + 1]], net["edges"][ea:eb])
+            halo = np.setdiff1d(np.arange(g.size), sh["owned_local"])
+            assert (np.diff(sh["nbr_off"])[halo] == 0).all()
+            if world == 8:
+                seen.append(sh["owned_global"])
+    assert np.array_equal(np.concatenate(seen), np.arange(60))

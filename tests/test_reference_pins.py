@@ -202,4 +202,4 @@ def test_cuda_side_constants_match_keras_metadata():
     assert int(re.search(r"kGcnChannels\s*=\s*(\d+)", spec).group(1)) == cfg["root.gcn_layer"]["config"]["channels"]
     train = open(os.path.join(PKG, "csrc", "train.cu")).read()
     call = re.search(r"adam_kernel<<<.*?>>>\((.*?)\);", train, re.S).group(1)
-    assert call.rstrip().endswith("%sf" % cfg["root.gcn_layer.batch_norm"]["config"]["momentum"])
+    assert re.search(r"ts->stats,\s*%sf\b" % cfg["root.gcn_layer.batch_norm"]["config"]["momentum"], call)   # BN momentum argument
