@@ -268,6 +268,22 @@ int gnnqc_ig_cml(gnnqc_model* m, const float* features_dev, const float* anom_de
   });
 }
 
+int gnnqc_ig_cml_raw(gnnqc_model* m, const float* features_dev, const float* anom_dev, const int64_t* edges_dev,
+                 const int32_t* node_off_dev, const int64_t* edge_off_dev, int64_t B, int32_t T, int64_t n_nodes_total,
+                 int32_t m_steps, float* attr_features_dev, float* attr_anom_dev, float* scores_dev, void* stream) {
+  if (int rc = need_device(m, "gnnqc_ig_cml_raw")) return rc;
+  if (!m->dm.host.spec.has_gcn || m->dm.host.spec.soilnet) return fail(GNNQC_ERR_STATE, "gnnqc_ig_cml_raw: model is not a CML GCNClassifier");
+  if (B < 0 || T <= 0 || n_nodes_total < 0 || m_steps < 1) return fail(GNNQC_ERR_ARG, "gnnqc_ig_cml_raw: bad B / T / n_nodes_total / m_steps");
+  if (B > 0 && (!features_dev || !anom_dev || !edges_dev || !node_off_dev || !edge_off_dev || !attr_features_dev || !attr_anom_dev || !scores_dev))
+    return fail(GNNQC_ERR_ARG, "gnnqc_ig_cml_raw: null buffer");
+  return guarded([&] {
+    m->dm.refresh_tc();
+    m->dm.ig_cml(features_dev, anom_dev, reinterpret_cast<const long long*>(edges_dev), node_off_dev,
+                 reinterpret_cast<const long long*>(edge_off_dev), B, T, n_nodes_total, m_steps, attr_features_dev, attr_anom_dev,
+                 scores_dev, static_cast<cudaStream_t>(stream), false);
+  });
+}
+
 int64_t gnnqc_train_vector_len(const gnnqc_model* m) { return m ? m->dm.host.spec.n_params + 97 : 0; }
 
 int gnnqc_train_moments_cml(gnnqc_model* m, const float* features_dev, int64_t n_rows, double* moments_dev, void* stream) {

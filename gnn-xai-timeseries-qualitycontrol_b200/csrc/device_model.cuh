@@ -147,7 +147,7 @@ struct DeviceModel {
                const std::function<void(float, float, int, long long, long long, const float*)>& bwd);
   void ig_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
               const long long* edge_off, long long B, int T, long long n_nodes, int m_steps, float* attr_feat,
-              float* attr_anom, float* scores, cudaStream_t stream);
+              float* attr_anom, float* scores, cudaStream_t stream, bool scale_by_input = true);
   void score_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
                  const long long* edge_off, long long B, int T, long long n_nodes, float* scores,
                  cudaStream_t stream);

@@ -467,7 +467,7 @@ static __global__ void __launch_bounds__(256) cml_frontend_bwd_kernel(const floa
                                                                       const GcnFolded p, const float* __restrict__ dx1,
                                                                       float2* __restrict__ attr_feat, float2* __restrict__ attr_anom,
                                                                       long long n_windows, int T, int t_run, float alpha, float wk,
-                                                                      int first) {
+                                                                      int first, int scale_by_input = 1) {
   // One CTA per window.  Lanes walk the window's feature rows in memory order ((t, n) pairs are
   // contiguous), so the feature reads and the attribution read-modify-writes are fully coalesced;
   // the 16 upstream gradients of a row depend on t only and come out of L1 as broadcasts.
@@ -499,8 +499,9 @@ static __global__ void __launch_bounds__(256) cml_frontend_bwd_kernel(const floa
       gy = fmaf(s, p.a[1][c], gy);
     }
     float2 a = first ? make_float2(0.f, 0.f) : attr_feat[row0 + r];
-    a.x = fmaf(wk * v.x * cf, gx, a.x);
-    a.y = fmaf(wk * v.y * cf, gy, a.y);
+    // scale_by_input = 0: the trapezoid mean of the raw gradients (xai_config scale_gradients: False, :1006-1012 without :1185-1191)
+    a.x = fmaf(scale_by_input ? wk * v.x * cf : wk * cf, gx, a.x);
+    a.y = fmaf(scale_by_input ? wk * v.y * cf : wk * cf, gy, a.y);
     attr_feat[row0 + r] = a;
   }
   for (int t = threadIdx.x; t < (first ? T : t_run); t += 256) {
@@ -511,8 +512,8 @@ static __global__ void __launch_bounds__(256) cml_frontend_bwd_kernel(const floa
     const float* g = gbase + static_cast<long long>(t) * CH * kTile;
     const float2 av = __ldg(anom + win * T + t);
     float2 a = first ? make_float2(0.f, 0.f) : attr_anom[win * T + t];
-    a.x = fmaf(wk * av.x, __ldg(g), a.x);
-    a.y = fmaf(wk * av.y, __ldg(g + kTile), a.y);
+    a.x = fmaf(scale_by_input ? wk * av.x : wk, __ldg(g), a.x);
+    a.y = fmaf(scale_by_input ? wk * av.y : wk, __ldg(g + kTile), a.y);
     attr_anom[win * T + t] = a;
   }
 }

@@ -243,7 +243,7 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
 
 void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
                          const long long* edge_off, long long B, int T, long long n_nodes, int m_steps, float* attr_feat,
-                         float* attr_anom, float* scores, cudaStream_t st) {
+                         float* attr_anom, float* scores, cudaStream_t st, bool scale_by_input) {
   if (B <= 0) return;
   GNNQC_CUDA(cudaSetDevice(device));
   const StackPlan plan(host.spec, T);
@@ -269,7 +269,7 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
             cml_frontend_bwd_kernel<<<static_cast<unsigned>(nw), 256, 0, st>>>(feat2, reinterpret_cast<const float2*>(anom) + win0 * T, coef,
                                                                              node_off + win0, folded, dx1, reinterpret_cast<float2*>(attr_feat),
                                                                              reinterpret_cast<float2*>(attr_anom) + win0 * T, nw, T, plan.t_run[0],
-                                                                             alpha, wk, first);
+                                                                             alpha, wk, first, scale_by_input ? 1 : 0);
           });
 }
 

@@ -87,6 +87,7 @@ def _load():
         "gnnqc_soilnet_records_dates": (C.c_char_p, [vp, i64]),
         "gnnqc_soilnet_records_free": (None, [vp]),
         "gnnqc_ig_cml_series": (C.c_int, [vp, vp, vp, vp, i64, i32, i32, i32, vp, vp, vp, vp, vp, vp]),
+        "gnnqc_ig_cml_raw": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, i32, vp, vp, vp, vp]),
         "gnnqc_ig_cml": (C.c_int, [vp, vp, vp, vp, vp, vp, i64, i32, i64, i32, vp, vp, vp, vp]),
         "gnnqc_train_vector_len": (i64, [vp]),
         "gnnqc_train_moments_cml": (C.c_int, [vp, vp, i64, vp, vp]),

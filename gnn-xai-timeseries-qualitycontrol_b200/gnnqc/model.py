@@ -257,8 +257,8 @@ class NativeModel:
                                       n_nodes.data_ptr(), self._stream()))
         return attr_nodes, attr_anom, scores, node_sensor, n_nodes
 
-    def ig_cml(self, features, anom, edges, node_off, edge_off, m_steps=50, n_nodes_total=None):
-        """Integrated gradients (zero baseline, trapezoid, scaled by the input) for the CML GCN
+    def ig_cml(self, features, anom, edges, node_off, edge_off, m_steps=50, n_nodes_total=None, scale_by_input=True):
+        """Integrated gradients (zero baseline, trapezoid, scaled by the input unless scale_by_input=False) for the CML GCN
         model.  Returns (attr_features [Ntot,2], attr_anom [B,T,2], scores [B]) as CUDA tensors."""
         torch = _torch()
         features = self._dev_tensor(features, torch.float32, "features")
@@ -274,7 +274,8 @@ class NativeModel:
         attr_f = torch.empty_like(features)
         attr_a = torch.empty_like(anom)
         scores = torch.empty(B, dtype=torch.float32, device=anom.device)
-        check(lib.gnnqc_ig_cml(self._h, features.data_ptr(), anom.data_ptr(), edges.data_ptr(), node_off.data_ptr(),
+        fn = lib.gnnqc_ig_cml if scale_by_input else lib.gnnqc_ig_cml_raw
+        check(fn(self._h, features.data_ptr(), anom.data_ptr(), edges.data_ptr(), node_off.data_ptr(),
                                edge_off.data_ptr(), B, T, n_nodes_total, int(m_steps), attr_f.data_ptr(), attr_a.data_ptr(),
                                scores.data_ptr(), self._stream()))
         return attr_f, attr_a, scores

@@ -114,6 +114,17 @@ class _Classifier:
         return self.native.n_params
 
 
+def _require(cfg, key, allowed, what):
+    """The native kernels hard-wire the hyper-parameters of the shipped checkpoints (csrc/model_spec.h, checked against
+    keras_metadata.pb in tests/test_reference_pins.py); a config that asks for anything else would silently build a
+    different model than the reference does, so it is refused."""
+    v = cfg.get(key) if hasattr(cfg, "get") else getattr(cfg, key, None)
+    if isinstance(v, float) and any(isinstance(a, float) and abs(v - a) < 1e-12 for a in allowed):
+        return
+    if v not in allowed:
+        raise NotImplementedError("%s.%s = %r is not built (supported: %s)" % (what, key, v, ", ".join(repr(a) for a in allowed)))
+
+
 class GCNClassifier(_Classifier):
     def __init__(self, model_config=None, preprocessing_config=None, device=0, seed=0, _native=None):
         if _native is None:
@@ -124,6 +135,14 @@ class GCNClassifier(_Classifier):
                 raise NotImplementedError("only mean aggregation is built")
             if mc.graph_convolution.units != 16:
                 raise NotImplementedError("graph_convolution.units must be 16")
+            _require(mc.graph_convolution, "activation", ("prelu",), "graph_convolution")
+            _require(mc.graph_convolution, "regularizer", (None,), "graph_convolution")
+            _require(mc.graph_convolution, "dropout_rate", (0, 0.0, None), "graph_convolution")
+            _require(mc.sequence_layer, "activation", ("tanh",), "sequence_layer")
+            _require(mc.sequence_layer, "pool_size", (3,), "sequence_layer")
+            _require(mc.sequence_layer, "regularizer", (None,), "sequence_layer")
+            _require(mc.dense, "alpha", (0.3,), "dense")
+            _require(mc.dense, "regularizer", (None,), "dense")
             soil = pc.ds_type == "soilnet"
             freq = 15 if soil else 1
             probe = NativeModel.create(True, soil, None, mc.sequence_layer.filter_1_size, mc.sequence_layer.n_stacks,
@@ -176,6 +195,9 @@ class BaselineClassifier(_Classifier):
                 raise NotImplementedError("only baseline_model.type='lstm' is built")
             if bm.regularizer is not None:
                 raise NotImplementedError("baseline_model.regularizer must be null (the reference's branch is broken, create_model.py:288-291)")
+            _require(bm, "activation", ("tanh",), "baseline_model")
+            _require(bm, "pool_size", (3,), "baseline_model")
+            _require(bm, "alpha", (0.3,), "baseline_model")
             soil = pc.ds_type == "soilnet"
             freq = 15 if soil else 1
             probe = NativeModel.create(False, soil, None, bm.filter_1_size, bm.n_stacks, bm.dense_layer_units, device=None)

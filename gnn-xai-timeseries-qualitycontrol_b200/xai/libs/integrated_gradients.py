@@ -45,10 +45,8 @@ class IntegratedGradientsExplainer:
         dev = torch.device("cuda", self.model.device)
         b = {k: (v.to(dev) if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
         af, aa, p = self.model.native.ig_cml(b["features"], b["anom"], b["edges"], b["node_off"].to(torch.int32), b["edge_off"],
-                                             m_steps=int(self.ig.m_steps), n_nodes_total=batch.get("n_nodes_total"))
-        if not self.ig.scale_gradients:            # :1185-1191 - the kernel accumulates x * IG
-            af = torch.where(b["features"] != 0, af / b["features"], torch.zeros_like(af))
-            aa = torch.where(b["anom"] != 0, aa / b["anom"], torch.zeros_like(aa))
+                                             m_steps=int(self.ig.m_steps), n_nodes_total=batch.get("n_nodes_total"),
+                                             scale_by_input=bool(self.ig.scale_gradients))    # :1185-1191 only when configured
         mode = self.ig.negative_values             # :1193-1207
         if mode == "abs":
             af, aa = af.abs(), aa.abs()

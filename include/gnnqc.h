@@ -261,6 +261,13 @@ int gnnqc_select_threshold(int device, const float* scores_dev, const int64_t* l
 int gnnqc_roc_auc(int device, const float* scores_dev, const int64_t* labels_dev, int64_t n,
                   double* auc_out, void* stream);
 
+/* gnnqc_ig_cml without the final "(x - baseline) *" scaling: the trapezoid mean of the raw gradients, as the reference returns
+ * it with integrated_gradients.scale_gradients: False (xai/libs/integrated_gradients.py:1006-1012 without :1185-1191). */
+int gnnqc_ig_cml_raw(gnnqc_model* m, const float* features_dev, const float* anom_dev,
+                     const int64_t* edges_dev, const int32_t* node_off_dev, const int64_t* edge_off_dev,
+                     int64_t B, int32_t T, int64_t n_nodes_total, int32_t m_steps,
+                     float* attr_features_dev, float* attr_anom_dev, float* scores_dev, void* stream);
+
 /* Integrated gradients for windows named by (target sensor, time index) on a resident network (BASELINE.json config 4:
  * the IG sweep over a network that stays in HBM; reference loop prepare_data -> get_gradients ->
  * _get_gradients_single_batch, xai/libs/integrated_gradients.py:590-703,1093-1246, with the window extraction of

@@ -205,7 +205,7 @@ def reference_batch_layout(windows, n_features):
 
 
 # ---- integrated gradients ---------------------------------------------------------------------
-def integrated_gradients_cml(features, anom, edge_index, sample_indices, w, m_steps=50):
+def integrated_gradients_cml(features, anom, edge_index, sample_indices, w, m_steps=50, scale_gradients=True):
     """Zero baseline, alphas = linspace(0,1,m_steps+1), both inputs interpolated with the same
     alpha, gradient of sum_b p_b per alpha, trapezoid mean, scaled by (x - 0).
     Returns (attr_features [Ntot,2], attr_anom [B,T,2], scores [B])."""
@@ -223,6 +223,8 @@ def integrated_gradients_cml(features, anom, edge_index, sample_indices, w, m_st
     iga = ((ga[:-1] + ga[1:]) / 2.0).mean(dim=0)
     with torch.no_grad():
         scores = gcn_forward_cml(features, anom, edge_index, sample_indices, w).reshape(-1)
+    if not scale_gradients:        # xai_config scale_gradients: False -> the trapezoid mean itself (:1006-1012)
+        return igf, iga, scores
     return features * igf, anom * iga, scores
 
 

@@ -116,3 +116,24 @@ def test_ig_large_batch_equals_its_chunks(model):
         bf, ba, bp = model.ig_cml(s["features"], s["anom"], s["edges"], s["node_off"], s["edge_off"], m_steps=1)
         n0, n1 = int(batch["node_off"][w0]), int(batch["node_off"][w1])
         assert torch.equal(bf, af[n0 * T:n1 * T]) and torch.equal(ba, aa[w0:w1]) and torch.equal(bp, p[w0:w1])
+
+
+def test_unscaled_gradients_with_zeros_in_the_input(model):
+    """scale_gradients: False (reference :1006-1012 without :1185-1191): the trapezoid mean of the raw gradients, which is
+    not zero where the input is exactly zero (rolling-median normalisation produces exact zeros)."""
+    batch = synth.make_cml_batch(5, seed=77, n_nodes=6)
+    batch["features"][::7] = 0.0
+    batch["anom"][:, ::5] = 0.0
+    b = {k: (v.cuda() if isinstance(v, torch.Tensor) else v) for k, v in batch.items()}
+    af, aa, p = model.ig_cml(b["features"], b["anom"], b["edges"], b["node_off"], b["edge_off"], m_steps=4, scale_by_input=False)
+    feat, idx, samp = O.reference_batch_layout(synth.cml_batch_to_windows(batch), 2)
+    w = O.to_torch_weights(oracle_named("model_cml"), torch.float64)
+    of, oa, op = O.integrated_gradients_cml(torch.tensor(feat).double(), batch["anom"].double(), torch.tensor(idx), torch.tensor(samp), w, m_steps=4,
+                                            scale_gradients=False)
+    live = np.zeros(batch["anom"].shape[1], bool)
+    live[:162] = True                                   # dead steps get 0 from the kernel; their true raw gradient is 0 as well
+    close(p.cpu().numpy(), op.numpy(), 1e-4, 1e-4)
+    close(aa.cpu().numpy(), oa.numpy(), 1e-5, 1e-3)
+    close(af.cpu().numpy(), of.numpy(), 1e-5, 1e-3)
+    zero_rows = (batch["features"] == 0).all(dim=1).numpy()
+    assert np.abs(af.cpu().numpy()[zero_rows]).max() > 0

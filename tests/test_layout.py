@@ -49,3 +49,26 @@ def test_link_shards_keep_every_target_neighbourhood():
             if world == 8:
                 seen.append(sh["owned_global"])
     assert np.array_equal(np.concatenate(seen), np.arange(60))
+
+
+def test_constructors_refuse_hyper_parameters_the_kernels_do_not_implement():
+    """ADVICE: dense.alpha, activation, pool_size, regularizers and dropout are hard-wired in the native code (and pinned to
+    keras_metadata.pb); a config that differs must not silently build another model."""
+    import pytest
+
+    from gnnqc.config import default_model_config, default_preproc_config
+    from libs.create_model import BaselineClassifier, GCNClassifier
+    pc = default_preproc_config("cml")
+    for section, key, value in (("dense", "alpha", 0.1), ("sequence_layer", "activation", "relu"), ("sequence_layer", "pool_size", 2),
+                                ("graph_convolution", "dropout_rate", 0.2), ("graph_convolution", "regularizer", 1e-4),
+                                ("sequence_layer", "regularizer", 1e-4), ("dense", "regularizer", 1e-4)):
+        mc = default_model_config()
+        mc[section][key] = value
+        with pytest.raises(NotImplementedError, match=key):
+            GCNClassifier(mc, pc, device=None)
+    for key, value in (("alpha", 0.2), ("activation", "relu"), ("pool_size", 4)):
+        mc = default_model_config()
+        mc.baseline_model[key] = value
+        with pytest.raises(NotImplementedError, match=key):
+            BaselineClassifier(mc, pc, device=None)
+    GCNClassifier(default_model_config(), pc, device=None)      # the shipped configuration itself builds (host-only handle)
