@@ -52,6 +52,7 @@ inline long long balanced_chunk(long long n_tiles, long long max_tiles) {
 }
 
 struct TrainState;
+struct IgGroup;     // a group of interpolation points for the front-end backward (csrc/ig_frontend_bwd.cuh)
 struct HostStage;   // staging slots and streams of gnnqc_score_cml_host (csrc/host_scoring.cu)
 void free_host_stage(HostStage* h);
 
@@ -144,7 +145,7 @@ struct DeviceModel {
   void ig_core(long long B, int T, int m_steps, float* scores, cudaStream_t stream, size_t extra_bytes,
                const std::function<void(char*)>& prepare,
                const std::function<void(float, long long, long long, long long, float*)>& fwd,
-               const std::function<void(float, float, int, long long, long long, const float*)>& bwd);
+               const std::function<void(const IgGroup&, long long, long long)>& bwd, bool scale_by_input = true);
   void ig_cml(const float* feat, const float* anom, const long long* edges, const int* node_off,
               const long long* edge_off, long long B, int T, long long n_nodes, int m_steps, float* attr_feat,
               float* attr_anom, float* scores, cudaStream_t stream, bool scale_by_input = true);

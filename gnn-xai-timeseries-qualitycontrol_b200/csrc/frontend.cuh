@@ -453,70 +453,7 @@ __global__ void __launch_bounds__(128) head_kernel(const float* __restrict__ y7,
   }
 }
 
-// ---- integrated gradients: backward through the CML front-end ---------------------------------
-// One interpolation step of xai/libs/integrated_gradients.py:955-1012 for the graph half of the
-// model: given dx1 = d(sum_b p_b)/d(x1 tile) at the input alpha*x, accumulates
-//   attr_feat[row][f] (+)= wk * x[row][f] * coef_n * sum_c dx1[2+c] * prelu'(z_c) * a[f][c]
-//   attr_anom[b][t][c] (+)= wk * anom[b][t][c] * dx1[c]
-// where wk is the trapezoid weight of this alpha (1/m, or 1/(2m) at the two ends; :1006-1012)
-// and the factor x is the "(x - baseline) * IG" scaling (:1185-1191, zero baseline).
-// `first` assigns instead of accumulating.  Steps t >= t_run cannot influence the score: their
-// attribution is exactly 0 and is written as such.
-static __global__ void __launch_bounds__(256) cml_frontend_bwd_kernel(const float2* __restrict__ feat, const float2* __restrict__ anom,
-                                                                      const float* __restrict__ coef, const int* __restrict__ node_off,
-                                                                      const GcnFolded p, const float* __restrict__ dx1,
-                                                                      float2* __restrict__ attr_feat, float2* __restrict__ attr_anom,
-                                                                      long long n_windows, int T, int t_run, float alpha, float wk,
-                                                                      int first, int scale_by_input = 1) {
-  // One CTA per window.  Lanes walk the window's feature rows in memory order ((t, n) pairs are
-  // contiguous), so the feature reads and the attribution read-modify-writes are fully coalesced;
-  // the 16 upstream gradients of a row depend on t only and come out of L1 as broadcasts.
-  const long long win = blockIdx.x;
-  if (win >= n_windows) return;
-  const long long tile = win / kTile;
-  const int b = static_cast<int>(win % kTile);
-  const int n0 = node_off[win];
-  const int nn = node_off[win + 1] - n0;
-  constexpr int CH = 2 + kGcnChannelsDev;
-  const long long row0 = static_cast<long long>(n0) * T;
-  const int live_rows = t_run * nn, all_rows = first ? T * nn : live_rows;
-  const float* gbase = dx1 + (tile * t_run) * CH * kTile + b;
-  for (int r = threadIdx.x; r < all_rows; r += 256) {
-    if (r >= live_rows) {                 // steps that cannot reach the score: attribution 0
-      attr_feat[row0 + r] = make_float2(0.f, 0.f);
-      continue;
-    }
-    const int t = r / nn, n = r - t * nn;
-    const float2 v = __ldg(feat + row0 + r);
-    const float cf = __ldg(coef + n0 + n);
-    const float* g = gbase + static_cast<long long>(t) * CH * kTile;
-    float gx = 0.f, gy = 0.f;
-#pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) {
-      const float z = fmaf(alpha * v.x, p.a[0][c], fmaf(alpha * v.y, p.a[1][c], p.c[c]));
-      const float s = __ldg(g + (2 + c) * kTile) * (z > 0.f ? 1.f : p.alpha[c]);
-      gx = fmaf(s, p.a[0][c], gx);
-      gy = fmaf(s, p.a[1][c], gy);
-    }
-    float2 a = first ? make_float2(0.f, 0.f) : attr_feat[row0 + r];
-    // scale_by_input = 0: the trapezoid mean of the raw gradients (xai_config scale_gradients: False, :1006-1012 without :1185-1191)
-    a.x = fmaf(scale_by_input ? wk * v.x * cf : wk * cf, gx, a.x);
-    a.y = fmaf(scale_by_input ? wk * v.y * cf : wk * cf, gy, a.y);
-    attr_feat[row0 + r] = a;
-  }
-  for (int t = threadIdx.x; t < (first ? T : t_run); t += 256) {
-    if (t >= t_run) {
-      attr_anom[win * T + t] = make_float2(0.f, 0.f);
-      continue;
-    }
-    const float* g = gbase + static_cast<long long>(t) * CH * kTile;
-    const float2 av = __ldg(anom + win * T + t);
-    float2 a = first ? make_float2(0.f, 0.f) : attr_anom[win * T + t];
-    a.x = fmaf(scale_by_input ? wk * av.x : wk, __ldg(g), a.x);
-    a.y = fmaf(scale_by_input ? wk * av.y : wk, __ldg(g + kTile), a.y);
-    attr_anom[win * T + t] = a;
-  }
-}
+// (the backward through this front-end for integrated gradients lives in ig_frontend_bwd.cuh)
 
 // ---- head forward + gradient of the score w.r.t. the last LSTM state ------------------------------
 // dy7[k] = d p / d h7[k] through Dense-LeakyReLU-Dense-LeakyReLU-Dense(sigmoid)

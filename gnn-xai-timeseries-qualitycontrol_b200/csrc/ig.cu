@@ -21,6 +21,7 @@
 
 #include "device_model.cuh"
 #include "frontend.cuh"
+#include "ig_frontend_bwd.cuh"
 #include "lstm_bwd.cuh"
 #include "lstm_fwd.cuh"
 
@@ -128,6 +129,7 @@ void DeviceModel::configure_ig_kernels() {
   const ModelSpec& s = host.spec;
   if (!s.has_gcn || s.soilnet) return;
   configure_cml_frontend();
+  GNNQC_CUDA(cudaFuncSetAttribute(cml_frontend_bwd_multi_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ig_bwd_smem_bytes(kIgMaxGroup))));
   GNNQC_CUDA(cudaGetLastError());
   LayerArgs none;
   for (int l = 0; l < s.n_lstm; ++l) {
@@ -143,7 +145,7 @@ void DeviceModel::configure_ig_kernels() {
 void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaStream_t st, size_t extra_bytes,
                           const std::function<void(char*)>& prepare,
                           const std::function<void(float, long long, long long, long long, float*)>& fwd,
-                          const std::function<void(float, float, int, long long, long long, const float*)>& bwd) {
+                          const std::function<void(const IgGroup&, long long, long long)>& bwd, bool scale_by_input) {
   if (B <= 0) return;
   const ModelSpec& s = host.spec;
   GNNQC_CUDA(cudaSetDevice(device));
@@ -171,7 +173,14 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
   const size_t per_tile = sa + sb + 2 * sg + s7 + per_tile_save;
   extra_bytes = align_up(extra_bytes, 256);
   const long long chunk = balanced_chunk(n_tiles, static_cast<long long>(ig_scratch_budget_bytes() / per_tile));
-  char* base = static_cast<char*>(scratch(extra_bytes + size_t(chunk) * per_tile));
+  // dx1 of a whole group of interpolation points stays resident, so the front-end backward reads the features and writes
+  // the attributions once per group instead of once per alpha (ig_frontend_bwd.cuh); GNNQC_IG_DX_MB bounds it (default 40 GiB)
+  static const size_t dx_budget = [] { const char* e = std::getenv("GNNQC_IG_DX_MB"); return (e ? std::strtoull(e, nullptr, 10) : size_t(40960)) << 20; }();
+  const long long group = std::max<long long>(1, std::min<long long>(std::min<long long>(m_steps + 1, kIgMaxGroup), static_cast<long long>(dx_budget / (size_t(chunk) * sg))));
+  const size_t dx_bytes = size_t(group) * size_t(chunk) * sg;
+  char* base = static_cast<char*>(scratch(extra_bytes + size_t(chunk) * per_tile + dx_bytes));
+  float* dx_all = reinterpret_cast<float*>(base + extra_bytes + size_t(chunk) * per_tile);
+  const long long dx_stride = static_cast<long long>(size_t(chunk) * sg / sizeof(float));
   char* p = base + extra_bytes;
   float* buf_a = reinterpret_cast<float*>(p); p += size_t(chunk) * sa;
   float* buf_b = reinterpret_cast<float*>(p); p += size_t(chunk) * sb;
@@ -224,6 +233,7 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
         const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
         LayerArgs a;
         a.in = dy; a.out = (l % 2 == 0) ? g0 : g1; a.w = d_packed_t + packed_t_off[l];
+        if (l == 0) a.out = dx_all + static_cast<long long>(k % group) * dx_stride;   // kept until its group is complete
         a.wtc = ig_tc_bwd ? d_packed_tcb + packed_tcb_off[l] : nullptr;
         a.save = reinterpret_cast<float*>(saves + size_t(chunk) * save_off[l]);
         a.amax = pool ? reinterpret_cast<float*>(saves + size_t(chunk) * amax_off[l]) : nullptr;
@@ -233,10 +243,21 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
         mark_end(st);
         dy = a.out;
       }
-      mark_begin("ig_frontend_bwd", st);
-      bwd(alpha, wk, k == 0 ? 1 : 0, win0, nw, dy);
-      GNNQC_CUDA(cudaGetLastError());
-      mark_end(st);
+      (void)wk;
+      if ((k + 1) % group == 0 || k == m_steps) {
+        IgGroup g;
+        g.k0 = static_cast<int>(k / group * group);
+        g.nk = k - g.k0 + 1;
+        g.m_steps = m_steps;
+        g.dx = dx_all;
+        g.stride = dx_stride;
+        g.first = g.k0 == 0 ? 1 : 0;
+        g.scale_by_input = scale_by_input ? 1 : 0;
+        mark_begin("ig_frontend_bwd", st);
+        bwd(g, win0, nw);
+        GNNQC_CUDA(cudaGetLastError());
+        mark_end(st);
+      }
     }
   }
 }
@@ -265,12 +286,13 @@ void DeviceModel::ig_cml(const float* feat, const float* anom, const long long* 
             launch_cml_frontend(feat2, n_nodes * T, reinterpret_cast<const float2*>(anom) + win0 * T, coef, node_off + win0, folded, x1, nw, T,
                                 plan.t_run[0], nt, alpha, sm_count, st);
           },
-          [&](float alpha, float wk, int first, long long win0, long long nw, const float* dx1) {
-            cml_frontend_bwd_kernel<<<static_cast<unsigned>(nw), 256, 0, st>>>(feat2, reinterpret_cast<const float2*>(anom) + win0 * T, coef,
-                                                                             node_off + win0, folded, dx1, reinterpret_cast<float2*>(attr_feat),
-                                                                             reinterpret_cast<float2*>(attr_anom) + win0 * T, nw, T, plan.t_run[0],
-                                                                             alpha, wk, first, scale_by_input ? 1 : 0);
-          });
+          [&](const IgGroup& g, long long win0, long long nw) {
+            const dim3 grid(static_cast<unsigned>((nw + kIgWin - 1) / kIgWin), static_cast<unsigned>(T));
+            cml_frontend_bwd_multi_kernel<<<grid, 256, ig_bwd_smem_bytes(g.nk), st>>>(feat2, reinterpret_cast<const float2*>(anom) + win0 * T, coef,
+                                                                                     node_off + win0, folded, g, reinterpret_cast<float2*>(attr_feat),
+                                                                                     reinterpret_cast<float2*>(attr_anom) + win0 * T, nw, T, plan.t_run[0]);
+          },
+          scale_by_input);
 }
 
 }  // namespace gnnqc

@@ -22,6 +22,7 @@
 #include "../../include/gnnqc.h"
 #include "capi_internal.h"
 #include "frontend.cuh"
+#include "ig_frontend_bwd.cuh"
 
 struct gnnqc_series {
   int device = 0;
@@ -191,69 +192,52 @@ __global__ void __launch_bounds__(256) series_frontend_kernel(const gnnqc_series
 }
 
 // Integrated gradients, backward through the front-end for windows that live in the resident series: the arithmetic of
-// cml_frontend_bwd_kernel (frontend.cuh) with x = raw - median read from the network.  Attributions go to dense,
-// zero-padded per-window blocks: attr_nodes [window][t][kMaxNbr][2] (node = position in the window's node list, which
-// node_sensor names), attr_anom [window][t][2].  One CTA per window.
+// cml_frontend_bwd_multi_kernel (ig_frontend_bwd.cuh, a whole group of interpolation points per pass) with x = raw - median
+// read from the network.  Attributions go to dense, zero-padded per-window blocks: attr_nodes [window][t][kMaxNbr][2]
+// (node = position in the window's node list, which node_sensor names), attr_anom [window][t][2].
+// Grid (ceil(windows / 8), T), 256 threads = 8 windows x kMaxNbr node slots.
 __global__ void __launch_bounds__(256) series_frontend_bwd_kernel(const gnnqc_series sr, const int* __restrict__ t_anom, int before,
                                                                   const int* __restrict__ w_sensor, const float* __restrict__ w_coef,
                                                                   const float2* __restrict__ w_med, const int* __restrict__ w_count,
-                                                                  const int* __restrict__ w_tgt_slot, const GcnFolded p, const float* __restrict__ dx1,
+                                                                  const int* __restrict__ w_tgt_slot, const GcnFolded p, const IgGroup g,
                                                                   float2* __restrict__ attr_nodes, float2* __restrict__ attr_anom,
-                                                                  long long n_windows, int T, int t_run, float alpha, float wk, int first) {
-  const long long win = blockIdx.x;
-  if (win >= n_windows) return;
-  __shared__ int sens_s[kMaxNbr];
-  __shared__ float coef_s[kMaxNbr];
-  __shared__ float2 med_s[kMaxNbr];
-  const int nn = w_count[win];
-  if (threadIdx.x < kMaxNbr) {
-    sens_s[threadIdx.x] = w_sensor[win * kMaxNbr + threadIdx.x];
-    coef_s[threadIdx.x] = w_coef[win * kMaxNbr + threadIdx.x];
-    med_s[threadIdx.x] = w_med[win * kMaxNbr + threadIdx.x];
-  }
+                                                                  long long n_windows, int T, int t_run) {
+  extern __shared__ __align__(16) unsigned char ig_raw[];
+  const IgSmem sm = ig_smem(ig_raw, g.nk);
+  const long long win0 = static_cast<long long>(blockIdx.x) * kIgWin;
+  const int t = blockIdx.y;
+  if (t >= t_run && !g.first) return;
+  ig_stage(p, g, win0, t, t_run, sm);
   __syncthreads();
-  const long long tile = win / kTile;
-  const int b = static_cast<int>(win % kTile);
-  constexpr int CH = 2 + kGcnChannelsDev;
+  const int w_l = threadIdx.x / kMaxNbr, n = threadIdx.x % kMaxNbr;
+  const long long win = win0 + w_l;
+  if (win >= n_windows) return;
+  const int nn = w_count[win];
   const long long base_t = static_cast<long long>(t_anom[win]) - before;
-  const float* gbase = dx1 + (tile * t_run) * CH * kTile + b;
-  float2* an = attr_nodes + win * T * kMaxNbr;
-  const int live_rows = t_run * kMaxNbr, all_rows = first ? T * kMaxNbr : live_rows;
-  for (int r = threadIdx.x; r < all_rows; r += 256) {
-    const int t = r / kMaxNbr, n = r - t * kMaxNbr;
-    if (r >= live_rows || n >= nn) {              // padding, skipped windows and steps that cannot reach the score: 0
-      if (first) an[r] = make_float2(0.f, 0.f);
-      continue;
-    }
-    const float2 raw = __ldg(sr.raw + static_cast<long long>(sens_s[n]) * sr.Tt + base_t + t);
-    const float2 v = make_float2(raw.x - med_s[n].x, raw.y - med_s[n].y);
-    const float cf = coef_s[n];
-    const float* g = gbase + static_cast<long long>(t) * CH * kTile;
-    float gx = 0.f, gy = 0.f;
-#pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) {
-      const float z = fmaf(alpha * v.x, p.a[0][c], fmaf(alpha * v.y, p.a[1][c], p.c[c]));
-      const float s = __ldg(g + (2 + c) * kTile) * (z > 0.f ? 1.f : p.alpha[c]);
-      gx = fmaf(s, p.a[0][c], gx);
-      gy = fmaf(s, p.a[1][c], gy);
-    }
-    float2 a = first ? make_float2(0.f, 0.f) : an[r];
-    a.x = fmaf(wk * v.x * cf, gx, a.x);
-    a.y = fmaf(wk * v.y * cf, gy, a.y);
-    an[r] = a;
+  float2* out = attr_nodes + (win * T + t) * kMaxNbr + n;
+  if (t >= t_run || n >= nn) {                    // padding, skipped windows and steps that cannot reach the score: 0
+    if (g.first) *out = make_float2(0.f, 0.f);
+  } else {
+    const float2 raw = __ldg(sr.raw + static_cast<long long>(w_sensor[win * kMaxNbr + n]) * sr.Tt + base_t + t);
+    const float2 med = w_med[win * kMaxNbr + n];
+    const float2 v = make_float2(raw.x - med.x, raw.y - med.y);
+    const float cf = w_coef[win * kMaxNbr + n];
+    const float2 s = ig_row(p, g, v.x, v.y, sm, w_l);
+    float2 a = g.first ? make_float2(0.f, 0.f) : *out;
+    a.x = fmaf(g.scale_by_input ? v.x * cf : cf, s.x, a.x);
+    a.y = fmaf(g.scale_by_input ? v.y * cf : cf, s.y, a.y);
+    *out = a;
   }
-  const int tslot = w_tgt_slot[win];
-  for (int t = threadIdx.x; t < (first ? T : t_run); t += 256) {
-    if (t >= t_run || nn == 0) {
-      if (first) attr_anom[win * T + t] = make_float2(0.f, 0.f);
-      continue;
+  if (n == 0) {
+    float2 a = make_float2(0.f, 0.f);
+    if (t < t_run && nn > 0) {
+      const int tslot = w_tgt_slot[win];
+      const float2 raw = __ldg(sr.raw + static_cast<long long>(w_sensor[win * kMaxNbr + tslot]) * sr.Tt + base_t + t);
+      const float2 med = w_med[win * kMaxNbr + tslot];
+      if (!g.first) a = attr_anom[win * T + t];
+      a.x = fmaf(g.scale_by_input ? raw.x - med.x : 1.f, sm.aux[w_l * 4 + 2], a.x);
+      a.y = fmaf(g.scale_by_input ? raw.y - med.y : 1.f, sm.aux[w_l * 4 + 3], a.y);
     }
-    const float* g = gbase + static_cast<long long>(t) * CH * kTile;
-    const float2 raw = __ldg(sr.raw + static_cast<long long>(sens_s[tslot]) * sr.Tt + base_t + t);
-    const float2 av = make_float2(raw.x - med_s[tslot].x, raw.y - med_s[tslot].y);
-    float2 a = first ? make_float2(0.f, 0.f) : attr_anom[win * T + t];
-    a.x = fmaf(wk * av.x, __ldg(g), a.x);
-    a.y = fmaf(wk * av.y, __ldg(g + kTile), a.y);
     attr_anom[win * T + t] = a;
   }
 }
@@ -473,11 +457,16 @@ int gnnqc_ig_cml_series(gnnqc_model* m, const gnnqc_series* series, const int32_
                  series_frontend_kernel<<<grid, 256, 0, st>>>(*series, t_anom_dev + win0, timestep_before, w_sensor + win0 * kMaxNbr, w_coef + win0 * kMaxNbr,
                                                               w_med + win0 * kMaxNbr, w_count + win0, w_tgt + win0, folded, x1, nw, plan.t_run[0], alpha);
                },
-               [&](float alpha, float wk, int first, long long win0, long long nw, const float* dx1) {
-                 series_frontend_bwd_kernel<<<static_cast<unsigned>(nw), 256, 0, st>>>(
+               [&](const IgGroup& g, long long win0, long long nw) {
+                 static const bool configured = [] {
+                   return cudaFuncSetAttribute(series_frontend_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(ig_bwd_smem_bytes(kIgMaxGroup))) == cudaSuccess;
+                 }();
+                 (void)configured;
+                 const dim3 grid(static_cast<unsigned>((nw + kIgWin - 1) / kIgWin), static_cast<unsigned>(T));
+                 series_frontend_bwd_kernel<<<grid, 256, ig_bwd_smem_bytes(g.nk), st>>>(
                      *series, t_anom_dev + win0, timestep_before, w_sensor + win0 * kMaxNbr, w_coef + win0 * kMaxNbr, w_med + win0 * kMaxNbr, w_count + win0,
-                     w_tgt + win0, folded, dx1, reinterpret_cast<float2*>(attr_nodes_dev) + win0 * T * kMaxNbr, reinterpret_cast<float2*>(attr_anom_dev) + win0 * T,
-                     nw, T, plan.t_run[0], alpha, wk, first);
+                     w_tgt + win0, folded, g, reinterpret_cast<float2*>(attr_nodes_dev) + win0 * T * kMaxNbr, reinterpret_cast<float2*>(attr_anom_dev) + win0 * T,
+                     nw, T, plan.t_run[0]);
                });
     series_mask_scores_kernel<<<static_cast<unsigned>((B + 255) / 256), 256, 0, st>>>(scores_dev, w_count, n_nodes_dev, B);
     GNNQC_CUDA(cudaGetLastError());
