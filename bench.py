@@ -513,7 +513,7 @@ class Workload:
         if b == "ig_series":
             return None      # bit-identical to gnnqc_ig_cml on the materialised windows (tests/test_gpu_series.py), which the "ig" workload checks
         if b in ("cml_gcn", "ig", "train"):
-            n = {"cml_gcn": 1024, "ig": 1, "train": min(128, self.units)}[b]
+            n = {"cml_gcn": 1024 if self.ctx.world == 1 else 256, "ig": 1, "train": min(128, self.units)}[b]   # rank 0 checks while the other ranks wait
             eo, no = self.batch["edge_off"][: n + 1].cpu(), self.batch["node_off"][: n + 1].cpu()
             cpu = {"features": self.batch["features"][: n * T_CML * N_NODES].cpu(), "anom": self.batch["anom"][:n].cpu(),
                    "edges": self.batch["edges"][: int(eo[-1])].cpu(), "node_off": no, "edge_off": eo, "T": T_CML}
@@ -585,10 +585,22 @@ class Ctx:
     pass
 
 
+_T0 = time.time()
+
+
+def log(ctx, msg):
+    """Progress on stderr (GNNQC_BENCH_VERBOSE=1): which rank is where, for diagnosing multi-rank runs."""
+    if os.environ.get("GNNQC_BENCH_VERBOSE"):
+        sys.stderr.write("[bench %6.1fs rank %d] %s\n" % (time.time() - _T0, ctx.rank, msg))
+        sys.stderr.flush()
+
+
 def measure(wl, ctx, args, steps, warmup, with_cpu=True):
     """Runs one workload; returns the line (rank 0) or None."""
     torch, dist, np = ctx.torch, ctx.dist, ctx.np
+    log(ctx, "%s: building inputs" % wl)
     W = Workload(wl, ctx, args)
+    log(ctx, "%s: warm-up" % wl)
     model, dev, world, rank = W.model, ctx.dev, ctx.world, ctx.rank
     units = W.units
 
@@ -615,6 +627,7 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
     pass_s = max_over_ranks(e0.elapsed_time(e1) * 1e-3)
     passes = max(1, int(math.ceil(MIN_TIMED_SECONDS / (steps * pass_s))))
     barrier()
+    log(ctx, "%s: timed region, %d passes per step" % (wl, passes))
     launches0 = model.launch_count()
     sampler = ClockSampler(ctx.local_rank)
     if rank == 0:
@@ -630,6 +643,7 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
     clocks = sampler.stop() if rank == 0 else None
     value = world * units * passes / (ms_step * 1e-3)
 
+    log(ctx, "%s: per-kernel profile" % wl)
     # ---- per-kernel times (CUDA events around every launch, on the launching stream) ---------------------
     prof_passes = 1 if W.base in ("ig", "ig_series") else max(1, min(passes * steps, 10))
     model.profile(True)
@@ -644,6 +658,7 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
         comm = sum(W.comm_ms) / len(W.comm_ms)
 
     # ---- end to end from pinned host buffers ------------------------------------------------------------------
+    log(ctx, "%s: end to end" % wl)
     for _ in range(2):
         out = W.e2e_step()
     barrier()
@@ -662,9 +677,12 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
     gathered = [per_rank.clone() for _ in range(world)]
     if world > 1:
         dist.all_gather(gathered, per_rank)
-    parity = W.parity(result) if rank == 0 and not args.no_parity else None
+    log(ctx, "%s: parity / barrier" % wl)
+    # at N > 1 only the primary workload is checked (the nested ones are checked by the N = 1 run; the other ranks wait here)
+    parity = W.parity(result) if rank == 0 and not args.no_parity and (world == 1 or not ctx.nested) else None
     if world > 1:
         dist.barrier()
+    log(ctx, "%s: measured" % wl)
     if rank != 0:
         W.close()
         return None
@@ -759,7 +777,7 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
     if comm is not None:
         line["collectives"] = {"ms_per_step": comm, "share_of_step": comm / (ms_step / passes),
                                "what": "the two all-reduces (6 f64 moments, %d-float reduction vector) incl. waiting for the slowest rank" % model.train_vector_len()}
-    if with_cpu and not args.no_cpu_baseline:
+    if with_cpu and not args.no_cpu_baseline and world == 1:      # the CPU baseline is timed at N = 1 only
         line["cpu_baseline"] = cpu_baseline(wl, W.unit, W.m_steps)
     W.close()
     return line
@@ -784,6 +802,11 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if rank == 0:
+        # torchrun exports OMP_NUM_THREADS=1 to its workers; rank 0 also runs the CPU oracle (parity check, CPU baseline,
+        # the reference arm), which is meant to use every host core - set before torch is imported
+        for var in ("OMP_NUM_THREADS", "MKL_NUM_THREADS"):
+            os.environ[var] = str(os.cpu_count() or 1)
     if args.impl == "reference":
         run_reference(args, rank)
         return
