@@ -144,11 +144,8 @@ lstm_tc_pair_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
     umma::fence_before_sync();
     __syncwarp();
     uint32_t old = 0;
-    if (lane == 0) {
-      __threadfence_block();
-      old = atomicAdd(cnt, 1u);
-      __threadfence_block();
-    }
+    if (lane == 0)   // one acquire-release atomic: this warp's operand writes are published, the last arriver sees everyone's
+      asm volatile("atom.acq_rel.cta.shared::cta.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(ptx::smem_addr(cnt)) : "memory");
     old = __shfl_sync(0xffffffffu, old, 0);
     return (old + 1u) % C::WPG == 0u;
   };
