@@ -7,10 +7,10 @@
 //   * the INPUT half of the contraction (x_t W, K = I) does not depend on h_{t-1}: it is issued one step ahead, into a
 //     second accumulator buffer (2 x 256 TMEM columns), while the cell update of the previous step runs - only the
 //     recurrent half (h_{t-1} U, K = 64) stays on the step's critical path;
-//   * sixteen cell-update warps (one window per thread, 16 units each) instead of eight, so the CUDA-core part runs at
-//     the rate the arithmetic allows (tools/micro/cell_rate.cu: ~50 cycles per warp-cell and scheduler with 4 warps);
-//   * the gate columns stay cut into two chunks of 32 units with their own completion barriers, so the cell update of
-//     chunk 0 overlaps the recurrent MMAs of chunk 1.
+//   * sixteen cell-update warps instead of eight (four threads per window), so the CUDA-core part runs at the rate the
+//     arithmetic allows (tools/micro/cell_rate.cu: ~50 cycles per warp-cell and scheduler with 4 warps);
+//   * the gate columns stay cut into two chunks of 32 units with their own completion barriers, and every thread takes
+//     8 units of EACH chunk: all sixteen warps update chunk 0 while the recurrent MMAs of chunk 1 are still running.
 // One more warp issues the TMA loads and the MMAs (warp-uniform operands, one elected lane).
 #pragma once
 #include "lstm_tc_big.cuh"

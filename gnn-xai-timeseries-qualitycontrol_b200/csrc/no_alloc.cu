@@ -10,7 +10,7 @@
 //
 // Cost and limits: the array is part of the library image, so every GPU that loads
 // libgnnqc.so carries kNoAllocScratchBytes (32 MiB) until the process exits, used or not.  A
-// call is rejected when its tiles do not fit (about 2,300 windows of 181 steps, about 1,150 of
+// call is rejected when its tiles do not fit (about 1,600 windows of 181 steps, about 800 of
 // 337 steps).  All calls on a device share the one array and it keeps whatever the last call
 // left in it: calls that overlap on the GPU (different streams, handles or threads) race and
 // give garbage, so serialise them.  Nothing in the array has to start at zero - every tile is

@@ -9,7 +9,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("GNNQC_LIB") or os.path.join(_HERE, "libgnnqc.so")   # GNNQC_LIB: an A/B build (build_native.py --variant=...)
 
-OK, ERR_ARG, ERR_CKPT, ERR_CUDA, ERR_NCCL, ERR_STATE = 0, -1, -2, -3, -4, -5
+OK, ERR_ARG, ERR_CKPT, ERR_CUDA, ERR_STATE = 0, -1, -2, -3, -5
 
 
 class GnnqcError(RuntimeError):

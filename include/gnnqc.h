@@ -32,7 +32,8 @@ extern "C" {
 #define GNNQC_ERR_ARG (-1)    /* bad argument / shape */
 #define GNNQC_ERR_CKPT (-2)   /* unreadable or unsupported checkpoint */
 #define GNNQC_ERR_CUDA (-3)   /* CUDA runtime error */
-#define GNNQC_ERR_NCCL (-4)   /* NCCL error */
+/* (-4 is unused: the library issues no collective itself - the training exchange steps are the caller's all-reduces
+ * between gnnqc_train_moments_*, gnnqc_train_grads_* and gnnqc_train_apply, see "training" below) */
 #define GNNQC_ERR_STATE (-5)  /* call not valid for this handle */
 
 typedef struct gnnqc_model gnnqc_model;
@@ -346,8 +347,8 @@ int gnnqc_train_apply(gnnqc_model* m, float* rvec_dev, const double* moments_dev
  * in a 32 MiB array that is part of the library image (each GPU that loads the library holds
  * those 32 MiB until the process exits), performs no cudaMalloc / cudaFree and calls no
  * allocating library routine.  Same arguments and results as gnnqc_score_seq.
- *  - Limit: the tiles of one call must fit the array - about 2,300 sequences of 181 steps or
- *    1,150 of 337 steps; larger calls fail with GNNQC_ERR_ARG and a message naming the limit.
+ *  - Limit: the tiles of one call must fit the array - about 1,600 sequences of 181 steps or
+ *    800 of 337 steps; larger calls fail with GNNQC_ERR_ARG and a message naming the limit.
  *  - The first call on a device looks up the array's device address (cudaGetSymbolAddress);
  *    make that first call before starting any stream capture.
  *  - All calls on a device share the array, which keeps the previous call's contents.  Nothing
