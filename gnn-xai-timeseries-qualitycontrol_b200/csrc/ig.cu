@@ -85,6 +85,7 @@ struct LayerArgs {
   const unsigned char* wtc = nullptr;   // tensor-core operand tiles of this direction (null: fp32 kernel)
   float* save = nullptr;
   float* amax = nullptr;
+  int nsave = 5;               // kSaveCompact: 16-bit fixed-point gates (tensor-core kernels on both sides only)
   int T = 0, t_in = 0, t_out = 0;
   long long n_tiles = 0;
   int sm_count = 0;
@@ -99,11 +100,11 @@ void layer_op(Op op, const LayerArgs& a) {
     if (tc_bwd_supported(I, H, POOL, LAST)) tc_bwd_configure(I, H, POOL, LAST);
   } else if (op == Op::Forward) {
     if (a.wtc && tc_layer_supported(I, H, POOL, LAST))   // gate contraction on the tensor cores (lstm_tc.cuh, SAVE mode)
-      return tc_launch(I, H, POOL, LAST, a.in, a.out, a.wtc, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax);
+      return tc_launch(I, H, POOL, LAST, a.in, a.out, a.wtc, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.st, a.save, a.amax, a.nsave);
     FwdSave<I, H, POOL, LAST>::launch(a.in, a.out, a.w, a.T, a.t_in, a.t_out, a.n_tiles, a.sm_count, a.save, a.amax, a.st);
   } else {
     if (a.wtc && tc_bwd_supported(I, H, POOL, LAST))   // contraction on the tensor cores (lstm_tc_bwd.cuh)
-      return tc_bwd_launch(I, H, POOL, LAST, a.in, a.save, a.amax, a.wtc, a.out, a.T, a.n_tiles, a.sm_count, a.st);
+      return tc_bwd_launch(I, H, POOL, LAST, a.in, a.save, a.amax, a.wtc, a.out, a.T, a.n_tiles, a.sm_count, a.st, a.nsave);
     Bwd<I, H, POOL, LAST>::launch(a.in, a.save, a.amax, a.w, a.out, a.T, a.n_tiles, a.sm_count, a.st);
   }
 }
@@ -156,6 +157,15 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
   StackPlan plan(s, T);
   const int L = s.n_lstm;
   const long long n_tiles = (B + kTile - 1) / kTile;
+  // Saved gates as 16-bit fixed point + fp32 c (12 instead of 20 bytes per cell, lstm_tc.cuh: save_cells2) when both the
+  // forward and the backward of every layer run on the tensor-core kernels; GNNQC_IG_COMPACT=0 keeps fp32 gates (A/B).
+  static const bool ig_compact_env = [] { const char* e = std::getenv("GNNQC_IG_COMPACT"); return !(e && std::strcmp(e, "0") == 0); }();
+  bool compact = ig_compact_env && ig_tc && ig_tc_bwd && d_packed_tc && d_packed_tcb;
+  for (int l = 0; l < L && compact; ++l) {
+    const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
+    compact = tc_layer_supported(s.lstm_in[l], s.lstm_hid[l], pool, last) && tc_bwd_supported(s.lstm_in[l], s.lstm_hid[l], pool, last);
+  }
+  const int nsave = compact ? 3 : 5;
 
   // Per-tile scratch: forward ping/pong, gradient ping/pong, dy7, saved gates and pool argmax.
   const size_t sa = align_up(plan.bytes_a, 256), sb = align_up(plan.bytes_b, 256);
@@ -165,7 +175,7 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
   size_t save_off[kMaxLstmLayers], amax_off[kMaxLstmLayers], per_tile_save = 0;
   for (int l = 0; l < L; ++l) {
     save_off[l] = per_tile_save;
-    per_tile_save += size_t(plan.t_run[l]) * s.lstm_hid[l] * 5 * kTile * sizeof(float);
+    per_tile_save += size_t(plan.t_run[l]) * s.lstm_hid[l] * nsave * kTile * sizeof(float);
     amax_off[l] = per_tile_save;
     if (l % 2 == 1 && l != L - 1) per_tile_save += size_t(plan.t_out[l]) * s.lstm_hid[l] * kTile * sizeof(float);
   }
@@ -214,6 +224,7 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
         a.wtc = ig_tc ? d_packed_tc + packed_tc_off[l] : nullptr;
         a.save = reinterpret_cast<float*>(saves + size_t(chunk) * save_off[l]);
         a.amax = pool ? reinterpret_cast<float*>(saves + size_t(chunk) * amax_off[l]) : nullptr;
+        a.nsave = nsave;
         a.T = plan.t_run[l]; a.t_in = t_in; a.t_out = plan.t_out[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
         mark_begin(kFwd[l], st);
         dispatch(Op::Forward, s.lstm_in[l], s.lstm_hid[l], pool, last, a);
@@ -237,6 +248,7 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
         a.wtc = ig_tc_bwd ? d_packed_tcb + packed_tcb_off[l] : nullptr;
         a.save = reinterpret_cast<float*>(saves + size_t(chunk) * save_off[l]);
         a.amax = pool ? reinterpret_cast<float*>(saves + size_t(chunk) * amax_off[l]) : nullptr;
+        a.nsave = nsave;
         a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
         mark_begin(kBwd[l], st);
         dispatch(Op::Backward, s.lstm_in[l], s.lstm_hid[l], pool, last, a);

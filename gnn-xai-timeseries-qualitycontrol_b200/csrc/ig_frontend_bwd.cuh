@@ -7,11 +7,13 @@
 // The first version ran one kernel per alpha: features read and attributions read-modify-written 51 times, ~210
 // instructions per row and alpha (ncu: issue slots 73 %).  Here the dx1 tiles of a whole group of alphas are kept (HBM is
 // large enough: 11.7 kB per window and alpha), and one pass handles them all:
-//   * a CTA takes 8 consecutive windows at one timestep, so the dx1 values it stages are whole 32-byte sectors of the
-//     [..][64 windows] tiles; per (window, k, c) it keeps G_kc = w_k dx1_k[t][2+c] a[f][c], split by the PReLU slope s_c into
-//     base = sum_kc s_c G_kc (what every row gets) and Q_kc = (1 - s_c) G_kc (what rows with z_kc > 0 get on top);
-//   * a row keeps u_c = x0 a[0][c] + x1 a[1][c] in registers, so per (k, c) it does one FMA, one compare and two
-//     predicated adds; features are read once and attributions written once per group.
+//   * a CTA takes 8 consecutive windows at one timestep, so the dx1 values it reads are whole 32-byte sectors of the
+//     [..][64 windows] tiles.  One thread per (window, channel) walks the group's alphas and leaves the PREFIX SUMS
+//     P_c[k] = sum_{k' < k} w_k' dx1_k'[c] in shared memory (18 channels: the two target-series channels only need the total);
+//   * z_kc = alpha_k u_c + c_c is monotone in k, so the alphas with z_kc > 0 are a prefix (u_c < 0) or a suffix (u_c > 0) of
+//     the group.  A row finds the crossing point per channel - the analytic estimate, corrected by one step with the very
+//     predicate fmaf(alpha_k, u_c, c_c) > 0 - and takes one difference of prefix sums: ~25 instructions per channel where
+//     the version before did ~5 per (k, c) x 51.  Features are read once and attributions written once per group.
 // Shared by the materialised-window path (ig.cu) and the resident-series path (series.cu), so both give the same bits.
 #pragma once
 #include "frontend.cuh"
@@ -19,10 +21,13 @@
 namespace gnnqc {
 
 constexpr int kIgWin = 8;         // windows per CTA (one 32-byte sector of a 64-window tile row)
-constexpr int kIgMaxGroup = 51;   // alphas per pass (shared-memory staging: 8 x 51 x 16 float2 = 52 kB)
+constexpr int kIgMaxGroup = 51;   // alphas per pass
+constexpr int kIgCh = 2 + kGcnChannelsDev;   // channels of the x1 tile: target series (2), GCN output (16)
 
+// prefix sums of one (window, channel): nk + 1 entries, padded to an odd count (bank spread of the per-thread walk)
+__host__ __device__ inline int ig_row_len(int nk) { return (nk + 1) | 1; }
 __host__ __device__ inline size_t ig_bwd_smem_bytes(int nk) {
-  return size_t(kIgWin) * nk * kGcnChannelsDev * sizeof(float2) + size_t(kIgWin) * 4 * sizeof(float) * 9 + size_t(nk) * sizeof(float);
+  return (size_t(kIgWin) * kIgCh * ig_row_len(nk) + 2 * size_t(nk)) * sizeof(float);
 }
 
 struct IgGroup {
@@ -34,81 +39,85 @@ struct IgGroup {
 };
 
 struct IgSmem {
-  float2* Q;      // [kIgWin][nk][16]: (1 - s_c) w_k dx1_k[2+c] (a[0][c], a[1][c])
-  float* aux;     // [kIgWin][4]: base0, base1, and the target-series sums sum_k w_k dx1_k[0], [1]
-  float* part;    // [8 warps][kIgWin][4]: per-warp partial sums of aux (summed in a fixed order: deterministic)
+  float* P;       // [kIgWin][18][row_len]: P[k] = sum_{k' < k} w_k' dx1_k'[channel]
   float* alpha;   // [nk]
+  float* wk;      // [nk] trapezoid weights
 };
 __device__ __forceinline__ IgSmem ig_smem(unsigned char* raw, int nk) {
   IgSmem s;
-  s.Q = reinterpret_cast<float2*>(raw);
-  s.aux = reinterpret_cast<float*>(s.Q + size_t(kIgWin) * nk * kGcnChannelsDev);
-  s.part = s.aux + kIgWin * 4;
-  s.alpha = s.part + 8 * kIgWin * 4;
+  s.P = reinterpret_cast<float*>(raw);
+  s.alpha = s.P + size_t(kIgWin) * kIgCh * ig_row_len(nk);
+  s.wk = s.alpha + nk;
   return s;
 }
 
-// Stages the group's dx1 values of timestep t for windows win0 .. win0 + 7 (win0 a multiple of 8).  256 threads.
-__device__ __forceinline__ void ig_stage(const GcnFolded& p, const IgGroup& g, long long win0, int t, int t_run, const IgSmem& sm) {
-  constexpr int CH = 2 + kGcnChannelsDev;
+// Prefix sums of the group's dx1 values of timestep t for windows win0 .. win0 + 7 (win0 a multiple of 8).  256 threads;
+// the caller synchronises before the rows read them.
+__device__ __forceinline__ void ig_stage(const IgGroup& g, long long win0, int t, int t_run, const IgSmem& sm) {
   const float m = static_cast<float>(g.m_steps);
-  for (int k = threadIdx.x; k < g.nk; k += blockDim.x) sm.alpha[k] = static_cast<float>(g.k0 + k) / m;
-  if (t >= t_run) return;                        // uniform over the CTA
-  const long long tile = win0 / kTile;
-  const int b0 = static_cast<int>(win0 % kTile);
-  const int w_l = threadIdx.x & (kIgWin - 1);
-  float b_0 = 0.f, b_1 = 0.f, ga0 = 0.f, ga1 = 0.f;
-  for (int i = threadIdx.x >> 3; i < g.nk * kGcnChannelsDev; i += static_cast<int>(blockDim.x >> 3)) {
-    const int k = i / kGcnChannelsDev, c = i % kGcnChannelsDev;
-    const float* gp = g.dx + static_cast<long long>(k) * g.stride + ((tile * t_run + t) * CH) * kTile + b0 + w_l;
+  for (int k = threadIdx.x; k < g.nk; k += blockDim.x) {
     const int kk = g.k0 + k;
-    const float wk = ((kk == 0 || kk == g.m_steps) ? 0.5f : 1.0f) / m;
-    const float gv = wk * __ldg(gp + (2 + c) * kTile);
-    const float g0 = gv * p.a[0][c], g1 = gv * p.a[1][c], s = p.alpha[c];
-    sm.Q[(w_l * g.nk + k) * kGcnChannelsDev + c] = make_float2(g0 * (1.f - s), g1 * (1.f - s));
-    b_0 = fmaf(s, g0, b_0);
-    b_1 = fmaf(s, g1, b_1);
-    if (c == 0) {
-      ga0 = fmaf(wk, __ldg(gp), ga0);
-      ga1 = fmaf(wk, __ldg(gp + kTile), ga1);
+    sm.alpha[k] = static_cast<float>(kk) / m;
+    sm.wk[k] = ((kk == 0 || kk == g.m_steps) ? 0.5f : 1.0f) / m;
+  }
+  if (t >= t_run) return;                        // uniform over the CTA
+  __syncthreads();
+  if (threadIdx.x < kIgWin * kIgCh) {
+    const int w_l = threadIdx.x & (kIgWin - 1), ch = threadIdx.x >> 3;
+    const int L = ig_row_len(g.nk);
+    const float* gp = g.dx + (((win0 / kTile) * t_run + t) * kIgCh + ch) * kTile + (win0 % kTile) + w_l;
+    float* row = sm.P + (w_l * kIgCh + ch) * L;
+    float run = 0.f;
+    row[0] = 0.f;
+    int k = 0;
+    for (; k + 4 <= g.nk; k += 4) {              // the loads of four alphas in flight, the sum in order
+      const float v0 = __ldg(gp + static_cast<long long>(k) * g.stride), v1 = __ldg(gp + static_cast<long long>(k + 1) * g.stride),
+                  v2 = __ldg(gp + static_cast<long long>(k + 2) * g.stride), v3 = __ldg(gp + static_cast<long long>(k + 3) * g.stride);
+      run = fmaf(sm.wk[k], v0, run); row[k + 1] = run;
+      run = fmaf(sm.wk[k + 1], v1, run); row[k + 2] = run;
+      run = fmaf(sm.wk[k + 2], v2, run); row[k + 3] = run;
+      run = fmaf(sm.wk[k + 3], v3, run); row[k + 4] = run;
+    }
+    for (; k < g.nk; ++k) {
+      run = fmaf(sm.wk[k], __ldg(gp + static_cast<long long>(k) * g.stride), run);
+      row[k + 1] = run;
     }
   }
-  // lanes with the same window: 8 apart
-  b_0 += __shfl_xor_sync(0xffffffffu, b_0, 8); b_0 += __shfl_xor_sync(0xffffffffu, b_0, 16);
-  b_1 += __shfl_xor_sync(0xffffffffu, b_1, 8); b_1 += __shfl_xor_sync(0xffffffffu, b_1, 16);
-  ga0 += __shfl_xor_sync(0xffffffffu, ga0, 8); ga0 += __shfl_xor_sync(0xffffffffu, ga0, 16);
-  ga1 += __shfl_xor_sync(0xffffffffu, ga1, 8); ga1 += __shfl_xor_sync(0xffffffffu, ga1, 16);
-  if ((threadIdx.x & 31) < kIgWin) {
-    float* o = sm.part + ((threadIdx.x >> 5) * kIgWin + w_l) * 4;
-    o[0] = b_0; o[1] = b_1; o[2] = ga0; o[3] = ga1;
-  }
-  __syncthreads();
-  if (threadIdx.x < kIgWin * 4) {
-    float v = 0.f;
-    for (int w = 0; w < 8; ++w) v += sm.part[w * kIgWin * 4 + threadIdx.x];
-    sm.aux[threadIdx.x] = v;
-  }
+}
+
+// sum_k w_k dx1_k[0], [1] of window slot w_l: the gradient with respect to the target series
+__device__ __forceinline__ float2 ig_anom(const IgGroup& g, const IgSmem& sm, int w_l) {
+  const int L = ig_row_len(g.nk);
+  return make_float2(sm.P[(w_l * kIgCh + 0) * L + g.nk], sm.P[(w_l * kIgCh + 1) * L + g.nk]);
 }
 
 // sum over the group's (k, c) of w_k dx1_k[2+c] prelu'(z_kc) a[f][c] for one row with features (x0, x1) of window slot w_l
 __device__ __forceinline__ float2 ig_row(const GcnFolded& p, const IgGroup& g, float x0, float x1, const IgSmem& sm, int w_l) {
-  float u[kGcnChannelsDev];
+  const int nk = g.nk, L = ig_row_len(nk);
+  const float* pw = sm.P + (w_l * kIgCh + 2) * L;
+  const float m = static_cast<float>(g.m_steps), k0 = static_cast<float>(g.k0);
+  float sx[2] = {0.f, 0.f}, sy[2] = {0.f, 0.f};
 #pragma unroll
-  for (int c = 0; c < kGcnChannelsDev; ++c) u[c] = fmaf(x0, p.a[0][c], x1 * p.a[1][c]);
-  float sx[4] = {sm.aux[w_l * 4 + 0], 0.f, 0.f, 0.f}, sy[4] = {sm.aux[w_l * 4 + 1], 0.f, 0.f, 0.f};   // four chains: the adds are dependent otherwise
-  const float2* q = sm.Q + size_t(w_l) * g.nk * kGcnChannelsDev;
-  for (int k = 0; k < g.nk; ++k) {
-    const float alpha = sm.alpha[k];
-#pragma unroll
-    for (int c = 0; c < kGcnChannelsDev; ++c) {
-      const float2 qv = q[k * kGcnChannelsDev + c];
-      if (fmaf(alpha, u[c], p.c[c]) > 0.f) {
-        sx[c & 3] += qv.x;
-        sy[c & 3] += qv.y;
-      }
-    }
+  for (int c = 0; c < kGcnChannelsDev; ++c) {
+    const float u = fmaf(x0, p.a[0][c], x1 * p.a[1][c]), cc = p.c[c];
+    const bool up = u > 0.f;
+    // q(k) = up ? z_k > 0 : !(z_k > 0) does not decrease with k; ks = the first k with q(k), nk if there is none.
+    // z crosses zero at k = -c m / u - k0: that estimate is off by one at most, the predicate itself settles it.
+    float ru;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ru) : "f"(u));
+    int ks = min(max(__float2int_ru(fmaf(-cc * m, ru, -k0)), 0), nk);
+    const bool q_lo = (fmaf(sm.alpha[max(ks - 1, 0)], u, cc) > 0.f) == up;
+    const bool q_hi = (fmaf(sm.alpha[min(ks, nk - 1)], u, cc) > 0.f) == up;
+    if (ks > 0 && q_lo) --ks;
+    else if (ks < nk && !q_hi) ++ks;
+    if (u == 0.f) ks = cc > 0.f ? nk : 0;
+    const float pk = pw[c * L + ks], pn = pw[c * L + nk];
+    const float d = up ? pn - pk : pk;           // the alphas on the positive side: from ks on / before ks
+    const float e = fmaf(p.alpha[c], pn - d, d); // slope 1 there, the PReLU slope on the others
+    sx[c & 1] = fmaf(p.a[0][c], e, sx[c & 1]);
+    sy[c & 1] = fmaf(p.a[1][c], e, sy[c & 1]);
   }
-  return make_float2((sx[0] + sx[1]) + (sx[2] + sx[3]), (sy[0] + sy[1]) + (sy[2] + sy[3]));
+  return make_float2(sx[0] + sx[1], sy[0] + sy[1]);
 }
 
 // Materialised windows: feat rows (window, t, n), attr_feat the same layout.  Grid (ceil(windows / 8), T), 256 threads:
@@ -122,7 +131,7 @@ static __global__ void __launch_bounds__(256) cml_frontend_bwd_multi_kernel(cons
   const long long win0 = static_cast<long long>(blockIdx.x) * kIgWin;
   const int t = blockIdx.y;
   if (t >= t_run && !g.first) return;                  // dead steps are zeroed by the first group only
-  ig_stage(p, g, win0, t, t_run, sm);
+  ig_stage(g, win0, t, t_run, sm);
   __syncthreads();
   const int w_l = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const long long win = win0 + w_l;
@@ -147,8 +156,9 @@ static __global__ void __launch_bounds__(256) cml_frontend_bwd_multi_kernel(cons
     if (t < t_run) {
       const float2 av = __ldg(anom + win * T + t);
       if (!g.first) a = attr_anom[win * T + t];
-      a.x = fmaf(g.scale_by_input ? av.x : 1.f, sm.aux[w_l * 4 + 2], a.x);
-      a.y = fmaf(g.scale_by_input ? av.y : 1.f, sm.aux[w_l * 4 + 3], a.y);
+      const float2 ga = ig_anom(g, sm, w_l);
+      a.x = fmaf(g.scale_by_input ? av.x : 1.f, ga.x, a.x);
+      a.y = fmaf(g.scale_by_input ? av.y : 1.f, ga.y, a.y);
     }
     attr_anom[win * T + t] = a;
   }

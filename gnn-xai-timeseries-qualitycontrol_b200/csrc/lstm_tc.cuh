@@ -214,6 +214,46 @@ __device__ __forceinline__ f32x2 lstm_cell2(f32x2 zi, f32x2 zf, f32x2 zg, f32x2 
   return mul2(sub2(one, e), r2);
 }
 
+// What the gate-saving forward keeps of a unit pair (j, j + 1) for the backward pass; so = the pair's slot in plane 0 of
+// its (tile, step) block, planes H * 64 floats apart.
+//   nsave 5 / 6: fp32 planes i, f, g, o, c (and h_t: training, whose weight gradients need it).
+//   nsave 3 (integrated gradients): 12 instead of 20 bytes per cell - the saved-gate stream is what bounds an
+//     interpolation step (written once and read once per alpha, 83 % of HBM peak in the first layers' forward).  The gates
+//     are bounded, so they are kept as 16-bit FIXED point: plane 0 = i | f << 16 (unorm16, absolute error 7.6e-6),
+//     plane 1 = g (snorm16, 1.5e-5) | o << 16; c stays fp32 in plane 2.  (fp16 would have 2.4e-4 in [0.5, 1].)
+constexpr int kSaveCompact = 3;
+__device__ __forceinline__ uint32_t pack_gates_uu(float lo, float hi) {
+  return __byte_perm(__float2uint_rn(lo * 65535.f), __float2uint_rn(hi * 65535.f), 0x5410);
+}
+__device__ __forceinline__ uint32_t pack_gates_su(float lo, float hi) {
+  return __byte_perm(static_cast<uint32_t>(__float2int_rn(lo * 32767.f)), __float2uint_rn(hi * 65535.f), 0x5410);
+}
+__device__ __forceinline__ void unpack_gates(uint32_t w0, uint32_t w1, float& ig, float& fg, float& gg, float& og) {
+  ig = __uint2float_rn(w0 & 0xffffu) * (1.f / 65535.f);
+  fg = __uint2float_rn(w0 >> 16) * (1.f / 65535.f);
+  gg = __int2float_rn(static_cast<int>(static_cast<short>(w1 & 0xffffu))) * (1.f / 32767.f);
+  og = __uint2float_rn(w1 >> 16) * (1.f / 65535.f);
+}
+__device__ __forceinline__ void save_cells2(float* so, int nsave, int H, const f32x2 (&sv)[5], float h0, float h1) {
+  if (nsave == kSaveCompact) {
+    float i0, i1, f0, f1, g0, g1, o0, o1;
+    up2(sv[0], i0, i1); up2(sv[1], f0, f1); up2(sv[2], g0, g1); up2(sv[3], o0, o1);
+    uint32_t* su = reinterpret_cast<uint32_t*>(so);
+    su[0] = pack_gates_uu(i0, f0);
+    su[kTile] = pack_gates_uu(i1, f1);
+    su[H * kTile] = pack_gates_su(g0, o0);
+    su[(H + 1) * kTile] = pack_gates_su(g1, o1);
+    up2(sv[4], so[2 * H * kTile], so[(2 * H + 1) * kTile]);
+  } else {
+#pragma unroll
+    for (int v = 0; v < 5; ++v) up2(sv[v], so[v * H * kTile], so[(v * H + 1) * kTile]);
+    if (nsave > 5) {
+      so[5 * H * kTile] = h0;
+      so[(5 * H + 1) * kTile] = h1;
+    }
+  }
+}
+
 // Which of the three pooled steps held the maximum (first one on ties, as lstm_fwd.cuh), two bits per unit.
 __device__ __forceinline__ void pool_arg_update(unsigned long long& bits, int unit, int ph, bool greater) {
   const unsigned long long m = 3ull << (2 * unit);
@@ -229,7 +269,7 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
                int T, int t_in_stride, int t_out_stride, int n_tiles,
                float* __restrict__ save = nullptr,       // SAVE: [n_tiles][T][5][H][64] gates i, f, g, o and c
                float* __restrict__ amax = nullptr,       // SAVE && POOL: [n_tiles][t_out_stride][H][64] argmax step
-               int nsave = 5) {                          // SAVE: 5, or 6 to store h_t as well (training)
+               int nsave = 5) {                          // SAVE: 5, 6 (h_t as well: training) or kSaveCompact (save_cells2)
   using C = TcCfg<I, H>;
   extern __shared__ __align__(128) unsigned char sm[];
   float* bias = reinterpret_cast<float*>(sm + C::OFF_BIAS);
@@ -385,13 +425,7 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
           f32x2 sv[5];
           up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[(j0 + i) / 2], sv), hv[i], hv[i + 1]);
           if (SAVE) {
-            float* so = save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b;
-#pragma unroll
-            for (int v = 0; v < 5; ++v) up2(sv[v], so[v * H * kTile], so[(v * H + 1) * kTile]);
-            if (nsave > 5) {
-              so[5 * H * kTile] = hv[i];
-              so[(5 * H + 1) * kTile] = hv[i + 1];
-            }
+            save_cells2(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
           }
         }
         if (POOL) {

@@ -63,7 +63,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
                    int T, int t_in_stride, int t_out_stride, int n_tiles,
                    float* __restrict__ save = nullptr,       // SAVE: [n_tiles][T][5][H][64] gates i, f, g, o and c
                    float* __restrict__ amax = nullptr,       // SAVE && POOL: [n_tiles][t_out_stride][H][64] argmax step
-               int nsave = 5) {                          // SAVE: 5, or 6 to store h_t as well (training)
+               int nsave = 5) {                          // SAVE: 5, 6 (h_t as well: training) or kSaveCompact (save_cells2)
   using C = TcBigCfg<I, H, STREAM>;
   extern __shared__ __align__(128) unsigned char sm[];
   uint4* Ahi = reinterpret_cast<uint4*>(sm + C::OFF_AHI);   // 16-byte chunk index: kb * ROWS + row
@@ -270,13 +270,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
             }
             up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[(l0 + i) / 2], sv), hv[i], hv[i + 1]);
             if (SAVE && valid) {
-              float* so = save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b;
-#pragma unroll
-              for (int v = 0; v < 5; ++v) up2(sv[v], so[v * H * kTile], so[(v * H + 1) * kTile]);
-              if (nsave > 5) {
-                so[5 * H * kTile] = hv[i];
-                so[(5 * H + 1) * kTile] = hv[i + 1];
-              }
+              save_cells2(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
             }
           }
           if (POOL) {

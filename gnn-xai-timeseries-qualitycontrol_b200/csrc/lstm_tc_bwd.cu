@@ -19,9 +19,11 @@ struct TcBwdLaunch {
   using Cfg = TcBwdCfg<I, H, GRP, SPLIT, STREAM>;
   static auto kernel() { return lstm_tc_bwd_kernel<I, H, POOL, LAST, GRP, SPLIT, STREAM, false>; }
   static auto kernel_train() { return lstm_tc_bwd_kernel<I, H, POOL, LAST, GRP, SPLIT, STREAM, true>; }
+  static auto kernel_compact() { return lstm_tc_bwd_kernel<I, H, POOL, LAST, GRP, SPLIT, STREAM, false, true>; }
   static void configure() {
     GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
     GNNQC_CUDA(cudaFuncSetAttribute(kernel_train(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+    GNNQC_CUDA(cudaFuncSetAttribute(kernel_compact(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
   }
   static void launch(const float* dy, const float* save, const float* amax, const unsigned char* wpk, float* dx, int T, long long n_tiles,
                      int sm_count, cudaStream_t st, int nsave, float* dz_out) {
@@ -36,6 +38,8 @@ struct TcBwdLaunch {
       kernel_train()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wpk, dx, T, static_cast<int>(n_tiles), dz_out);
     else if (nsave == 5 && !dz_out)
       kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wpk, dx, T, static_cast<int>(n_tiles), nullptr);
+    else if (nsave == kSaveCompact && !dz_out)
+      kernel_compact()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(dy, save, amax, wpk, dx, T, static_cast<int>(n_tiles), nullptr);
     else
       throw std::invalid_argument("tensor-core backward: nsave/dz_out combination not built");
     GNNQC_CUDA(cudaGetLastError());

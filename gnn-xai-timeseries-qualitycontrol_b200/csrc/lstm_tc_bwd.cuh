@@ -53,17 +53,19 @@ struct TcBwdCfg {
 };
 
 // TRAIN: the forward saved six quantities per step (h_t too) and dz is also written for the weight-gradient kernel.
-template <int I, int H, bool POOL, bool LAST, int GRP, int SPLIT, bool STREAM, bool TRAIN = false>
+// COMPACT: the forward saved the gates as 16-bit fixed point + c (three planes per step, save_cells2 in lstm_tc.cuh).
+template <int I, int H, bool POOL, bool LAST, int GRP, int SPLIT, bool STREAM, bool TRAIN = false, bool COMPACT = false>
 __global__ void __launch_bounds__((TcBwdCfg<I, H, GRP, SPLIT, STREAM>::NT), 1)
 lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this layer's output (layouts of lstm_bwd.cuh)
-                   const float* __restrict__ save,          // [n_tiles][T][5][H][64]
+                   const float* __restrict__ save,          // [n_tiles][T][5 | 6 | 3][H][64]
                    const float* __restrict__ amax,          // POOL: [n_tiles][T/3][H][64]
                    const unsigned char* __restrict__ wpk,   // B pieces per chunk (TcBwdCfg::PACKED_BYTES)
                    float* __restrict__ dx,                  // [n_tiles][T][I][64]
                    int T, int n_tiles,
                    float* __restrict__ dz_out = nullptr) {  // TRAIN: [n_tiles][T][4H][64] gate pre-activation gradients
   using C = TcBwdCfg<I, H, GRP, SPLIT, STREAM>;
-  constexpr int nsave = TRAIN ? 6 : 5;
+  constexpr int nsave = TRAIN ? 6 : (COMPACT ? kSaveCompact : 5);
+  static_assert(!(TRAIN && COMPACT), "training keeps fp32 gates");
   extern __shared__ __align__(128) unsigned char sm[];
   __shared__ uint32_t tmem_slot;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -225,9 +227,17 @@ lstm_tc_bwd_kernel(const float* __restrict__ dy,            // grad wrt this lay
           const float* sv = save + (((tile * T + t) * nsave) * H + j0) * kTile + b;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            const float ig = __ldg(sv + (0 * H + i) * kTile), fg = __ldg(sv + (1 * H + i) * kTile), gg = __ldg(sv + (2 * H + i) * kTile),
-                        og = __ldg(sv + (3 * H + i) * kTile), ct = __ldg(sv + (4 * H + i) * kTile);
-            const float cp = (t > 0) ? __ldg(sv + (i - (nsave - 4) * H) * kTile) : 0.f;   // c of step t-1: quantity 4 of the previous step's block
+            float ig, fg, gg, og, ct, cp;
+            if (COMPACT) {
+              const uint32_t* su = reinterpret_cast<const uint32_t*>(sv);
+              unpack_gates(__ldg(su + (0 * H + i) * kTile), __ldg(su + (1 * H + i) * kTile), ig, fg, gg, og);
+              ct = __ldg(sv + (2 * H + i) * kTile);
+              cp = (t > 0) ? __ldg(sv + (i - H) * kTile) : 0.f;   // c of step t-1: plane 2 of the previous step's block
+            } else {
+              ig = __ldg(sv + (0 * H + i) * kTile); fg = __ldg(sv + (1 * H + i) * kTile); gg = __ldg(sv + (2 * H + i) * kTile);
+              og = __ldg(sv + (3 * H + i) * kTile); ct = __ldg(sv + (4 * H + i) * kTile);
+              cp = (t > 0) ? __ldg(sv + (i - (nsave - 4) * H) * kTile) : 0.f;           // c of step t-1: quantity 4 of the previous step's block
+            }
             float d = dh[i];
             if (POOL) {
               const long long o = ((tile * t_dy + t / 3) * H + j0 + i) * kTile + b;

@@ -246,13 +246,7 @@ lstm_tc_wide_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
             }
             up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[b8 * 4 + i / 2], sv), hv[i], hv[i + 1]);
             if (SAVE) {
-              float* so = save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b;
-#pragma unroll
-              for (int v = 0; v < 5; ++v) up2(sv[v], so[v * H * kTile], so[(v * H + 1) * kTile]);
-              if (nsave > 5) {
-                so[5 * H * kTile] = hv[i];
-                so[(5 * H + 1) * kTile] = hv[i + 1];
-              }
+              save_cells2(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
             }
           }
           if (POOL) {

@@ -207,7 +207,7 @@ __global__ void __launch_bounds__(256) series_frontend_bwd_kernel(const gnnqc_se
   const long long win0 = static_cast<long long>(blockIdx.x) * kIgWin;
   const int t = blockIdx.y;
   if (t >= t_run && !g.first) return;
-  ig_stage(p, g, win0, t, t_run, sm);
+  ig_stage(g, win0, t, t_run, sm);
   __syncthreads();
   const int w_l = threadIdx.x / kMaxNbr, n = threadIdx.x % kMaxNbr;
   const long long win = win0 + w_l;
@@ -235,8 +235,9 @@ __global__ void __launch_bounds__(256) series_frontend_bwd_kernel(const gnnqc_se
       const float2 raw = __ldg(sr.raw + static_cast<long long>(w_sensor[win * kMaxNbr + tslot]) * sr.Tt + base_t + t);
       const float2 med = w_med[win * kMaxNbr + tslot];
       if (!g.first) a = attr_anom[win * T + t];
-      a.x = fmaf(g.scale_by_input ? raw.x - med.x : 1.f, sm.aux[w_l * 4 + 2], a.x);
-      a.y = fmaf(g.scale_by_input ? raw.y - med.y : 1.f, sm.aux[w_l * 4 + 3], a.y);
+      const float2 ga = ig_anom(g, sm, w_l);
+      a.x = fmaf(g.scale_by_input ? raw.x - med.x : 1.f, ga.x, a.x);
+      a.y = fmaf(g.scale_by_input ? raw.y - med.y : 1.f, ga.y, a.y);
     }
     attr_anom[win * T + t] = a;
   }
