@@ -11,9 +11,10 @@
 //     [..][64 windows] tiles.  One thread per (window, channel) walks the group's alphas and leaves the PREFIX SUMS
 //     P_c[k] = sum_{k' < k} w_k' dx1_k'[c] in shared memory (18 channels: the two target-series channels only need the total);
 //   * z_kc = alpha_k u_c + c_c is monotone in k, so the alphas with z_kc > 0 are a prefix (u_c < 0) or a suffix (u_c > 0) of
-//     the group.  A row finds the crossing point per channel - the analytic estimate, corrected by one step with the very
-//     predicate fmaf(alpha_k, u_c, c_c) > 0 - and takes one difference of prefix sums: ~25 instructions per channel where
-//     the version before did ~5 per (k, c) x 51.  Features are read once and attributions written once per group.
+//     the group.  A row computes the crossing point per channel analytically and takes one difference of prefix sums:
+//     ~20 instructions per channel where the version before did ~5 per (k, c) x 51.  (Where z_kc is within rounding of
+//     zero the side is arbitrary - as it is between any two evaluations of z, the forward kernel's included.)
+//     Features are read once and attributions written once per group.
 // Shared by the materialised-window path (ig.cu) and the resident-series path (series.cu), so both give the same bits.
 #pragma once
 #include "frontend.cuh"
@@ -27,7 +28,7 @@ constexpr int kIgCh = 2 + kGcnChannelsDev;   // channels of the x1 tile: target 
 // prefix sums of one (window, channel): nk + 1 entries, padded to an odd count (bank spread of the per-thread walk)
 __host__ __device__ inline int ig_row_len(int nk) { return (nk + 1) | 1; }
 __host__ __device__ inline size_t ig_bwd_smem_bytes(int nk) {
-  return (size_t(kIgWin) * kIgCh * ig_row_len(nk) + 2 * size_t(nk)) * sizeof(float);
+  return (size_t(kIgWin) * kIgCh * ig_row_len(nk) + size_t(nk)) * sizeof(float);
 }
 
 struct IgGroup {
@@ -40,14 +41,12 @@ struct IgGroup {
 
 struct IgSmem {
   float* P;       // [kIgWin][18][row_len]: P[k] = sum_{k' < k} w_k' dx1_k'[channel]
-  float* alpha;   // [nk]
   float* wk;      // [nk] trapezoid weights
 };
 __device__ __forceinline__ IgSmem ig_smem(unsigned char* raw, int nk) {
   IgSmem s;
   s.P = reinterpret_cast<float*>(raw);
-  s.alpha = s.P + size_t(kIgWin) * kIgCh * ig_row_len(nk);
-  s.wk = s.alpha + nk;
+  s.wk = s.P + size_t(kIgWin) * kIgCh * ig_row_len(nk);
   return s;
 }
 
@@ -57,7 +56,6 @@ __device__ __forceinline__ void ig_stage(const IgGroup& g, long long win0, int t
   const float m = static_cast<float>(g.m_steps);
   for (int k = threadIdx.x; k < g.nk; k += blockDim.x) {
     const int kk = g.k0 + k;
-    sm.alpha[k] = static_cast<float>(kk) / m;
     sm.wk[k] = ((kk == 0 || kk == g.m_steps) ? 0.5f : 1.0f) / m;
   }
   if (t >= t_run) return;                        // uniform over the CTA
@@ -95,22 +93,19 @@ __device__ __forceinline__ float2 ig_anom(const IgGroup& g, const IgSmem& sm, in
 __device__ __forceinline__ float2 ig_row(const GcnFolded& p, const IgGroup& g, float x0, float x1, const IgSmem& sm, int w_l) {
   const int nk = g.nk, L = ig_row_len(nk);
   const float* pw = sm.P + (w_l * kIgCh + 2) * L;
-  const float m = static_cast<float>(g.m_steps), k0 = static_cast<float>(g.k0);
+  const float m = static_cast<float>(g.m_steps), half_k0 = 0.5f - static_cast<float>(g.k0), nkf = static_cast<float>(nk);
   float sx[2] = {0.f, 0.f}, sy[2] = {0.f, 0.f};
 #pragma unroll
   for (int c = 0; c < kGcnChannelsDev; ++c) {
     const float u = fmaf(x0, p.a[0][c], x1 * p.a[1][c]), cc = p.c[c];
     const bool up = u > 0.f;
-    // q(k) = up ? z_k > 0 : !(z_k > 0) does not decrease with k; ks = the first k with q(k), nk if there is none.
-    // z crosses zero at k = -c m / u - k0: that estimate is off by one at most, the predicate itself settles it.
+    // z_k = alpha_k u + c crosses zero at k* = -c m / u - k0: for u > 0 the alphas k > k* are on the positive side, for
+    // u < 0 those with k < k*; either way the boundary index is ks = round(k* + 1/2), clamped to the group.  (u = 0 is
+    // pushed to a tiny negative value: all or none, by the sign of c.)
     float ru;
-    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ru) : "f"(u));
-    int ks = min(max(__float2int_ru(fmaf(-cc * m, ru, -k0)), 0), nk);
-    const bool q_lo = (fmaf(sm.alpha[max(ks - 1, 0)], u, cc) > 0.f) == up;
-    const bool q_hi = (fmaf(sm.alpha[min(ks, nk - 1)], u, cc) > 0.f) == up;
-    if (ks > 0 && q_lo) --ks;
-    else if (ks < nk && !q_hi) ++ks;
-    if (u == 0.f) ks = cc > 0.f ? nk : 0;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(ru) : "f"(up ? u : fminf(u, -1e-30f)));
+    const float kc = fminf(fmaxf(fmaf(-cc * m, ru, half_k0), 0.f), nkf);
+    const int ks = __float_as_int(kc + 12582912.f) - 0x4B400000;   // round to nearest through the 1.5 * 2^23 constant
     const float pk = pw[c * L + ks], pn = pw[c * L + nk];
     const float d = up ? pn - pk : pk;           // the alphas on the positive side: from ks on / before ks
     const float e = fmaf(p.alpha[c], pn - d, d); // slope 1 there, the PReLU slope on the others

@@ -22,7 +22,11 @@ template <int I, int H, bool POOL, bool SAVE>
 struct TcLaunch {
   using Cfg = TcCfg<I, H>;
   static auto kernel() { return lstm_tc_kernel<I, H, POOL, SAVE>; }
-  static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
+  static auto kernel_compact() { return lstm_tc_kernel<I, H, POOL, SAVE, SAVE>; }   // 16-bit fixed-point gates (save_cells2)
+  static void configure() {
+    GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+    if (SAVE) GNNQC_CUDA(cudaFuncSetAttribute(kernel_compact(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+  }
   static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st,
                      float* save, float* amax, int nsave) {
     // One persistent CTA per SM (four window groups inside, lstm_tc.cuh); tiles are dealt evenly.
@@ -32,7 +36,7 @@ struct TcLaunch {
       std::fprintf(stderr, "[gnnqc] tc I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
     }
     const long long grid = std::min<long long>(n_tiles, sm_count);
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
+    (SAVE && nsave == kSaveCompact ? kernel_compact() : kernel())<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
     GNNQC_CUDA(cudaGetLastError());
   }
 };
@@ -43,7 +47,11 @@ struct TcBigLaunch {
   static constexpr bool STREAM = (H > 64);
   using Cfg = TcBigCfg<I, H, STREAM>;
   static auto kernel() { return lstm_tc_big_kernel<I, H, POOL, LAST, STREAM, SAVE>; }
-  static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
+  static auto kernel_compact() { return lstm_tc_big_kernel<I, H, POOL, LAST, STREAM, SAVE, SAVE>; }
+  static void configure() {
+    GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+    if (SAVE) GNNQC_CUDA(cudaFuncSetAttribute(kernel_compact(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+  }
   static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st,
                      float* save, float* amax, int nsave) {
     const long long n_pairs = (n_tiles + 1) / 2;
@@ -53,7 +61,7 @@ struct TcBigLaunch {
       GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
       std::fprintf(stderr, "[gnnqc] tc-big I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
     }
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
+    (SAVE && nsave == kSaveCompact ? kernel_compact() : kernel())<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
     GNNQC_CUDA(cudaGetLastError());
   }
 };
@@ -63,11 +71,15 @@ template <int I, int H, bool POOL, bool SAVE>
 struct TcWideLaunch {
   using Cfg = TcWideCfg<I, H>;
   static auto kernel() { return lstm_tc_wide_kernel<I, H, POOL, SAVE>; }
-  static void configure() { GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES))); }
+  static auto kernel_compact() { return lstm_tc_wide_kernel<I, H, POOL, SAVE, SAVE>; }
+  static void configure() {
+    GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+    if (SAVE) GNNQC_CUDA(cudaFuncSetAttribute(kernel_compact(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+  }
   static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st,
                      float* save, float* amax, int nsave) {
     const long long grid = std::min<long long>((n_tiles + 1) / 2, sm_count);
-    kernel()<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
+    (SAVE && nsave == kSaveCompact ? kernel_compact() : kernel())<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
     GNNQC_CUDA(cudaGetLastError());
   }
 };

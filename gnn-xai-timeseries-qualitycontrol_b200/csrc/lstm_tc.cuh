@@ -234,8 +234,9 @@ __device__ __forceinline__ void unpack_gates(uint32_t w0, uint32_t w1, float& ig
   gg = __int2float_rn(static_cast<int>(static_cast<short>(w1 & 0xffffu))) * (1.f / 32767.f);
   og = __uint2float_rn(w1 >> 16) * (1.f / 65535.f);
 }
+template <bool COMPACT>
 __device__ __forceinline__ void save_cells2(float* so, int nsave, int H, const f32x2 (&sv)[5], float h0, float h1) {
-  if (nsave == kSaveCompact) {
+  if (COMPACT) {
     float i0, i1, f0, f1, g0, g1, o0, o1;
     up2(sv[0], i0, i1); up2(sv[1], f0, f1); up2(sv[2], g0, g1); up2(sv[3], o0, o1);
     uint32_t* su = reinterpret_cast<uint32_t*>(so);
@@ -261,7 +262,7 @@ __device__ __forceinline__ void pool_arg_update(unsigned long long& bits, int un
   else if (greater) bits = (bits & ~m) | (static_cast<unsigned long long>(ph) << (2 * unit));
 }
 
-template <int I, int H, bool POOL, bool SAVE = false>
+template <int I, int H, bool POOL, bool SAVE = false, bool COMPACT = false>   // COMPACT: nsave == kSaveCompact
 __global__ void __launch_bounds__((TcCfg<I, H>::NT), 1)
 lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_stride][I][64]
                float* __restrict__ yout,                 // [n_tiles][t_out_stride][H][64]
@@ -425,7 +426,7 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
           f32x2 sv[5];
           up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[(j0 + i) / 2], sv), hv[i], hv[i + 1]);
           if (SAVE) {
-            save_cells2(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
+            save_cells2<COMPACT>(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
           }
         }
         if (POOL) {

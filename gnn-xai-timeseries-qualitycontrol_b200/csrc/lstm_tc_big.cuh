@@ -55,7 +55,7 @@ struct TcBigCfg {
   static_assert(SMEM_BYTES <= 227 * 1024, "operands do not fit in shared memory");
 };
 
-template <int I, int H, bool POOL, bool LAST, bool STREAM, bool SAVE = false>
+template <int I, int H, bool POOL, bool LAST, bool STREAM, bool SAVE = false, bool COMPACT = false>
 __global__ void __launch_bounds__((TcBigCfg<I, H, STREAM>::NT), 1)
 lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_stride][I][64]
                    float* __restrict__ yout,                 // [n_tiles][t_out_stride][H][64], LAST: [n_tiles][H][64]
@@ -270,7 +270,7 @@ lstm_tc_big_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_s
             }
             up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[(l0 + i) / 2], sv), hv[i], hv[i + 1]);
             if (SAVE && valid) {
-              save_cells2(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
+              save_cells2<COMPACT>(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
             }
           }
           if (POOL) {

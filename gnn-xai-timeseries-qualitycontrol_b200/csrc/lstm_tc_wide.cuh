@@ -45,7 +45,7 @@ struct TcWideCfg {
   static_assert(SMEM_BYTES <= 227 * 1024, "operands do not fit in shared memory");
 };
 
-template <int I, int H, bool POOL, bool SAVE>
+template <int I, int H, bool POOL, bool SAVE, bool COMPACT = false>
 __global__ void __launch_bounds__((TcWideCfg<I, H>::NT), 1)
 lstm_tc_wide_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_stride][I][64]
                     float* __restrict__ yout,                 // [n_tiles][t_out_stride][H][64]
@@ -246,7 +246,7 @@ lstm_tc_wide_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_
             }
             up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[b8 * 4 + i / 2], sv), hv[i], hv[i + 1]);
             if (SAVE) {
-              save_cells2(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
+              save_cells2<COMPACT>(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
             }
           }
           if (POOL) {

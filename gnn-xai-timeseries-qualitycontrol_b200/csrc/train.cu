@@ -18,6 +18,7 @@
 #include "lstm_bwd.cuh"
 #include "soil_kernels.cuh"
 #include "train_kernels.cuh"
+#include "wgrad_tc.cuh"
 
 namespace gnnqc {
 namespace {
@@ -128,6 +129,7 @@ void DeviceModel::configure_train_kernels() {
     dispatch(Op::Configure, s.lstm_in[l], s.lstm_hid[l], !last && (l % 2 == 1), last, none);
   }
   GNNQC_CUDA(cudaFuncSetAttribute(wgrad_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, int(kWgradSmem)));
+  GNNQC_CUDA(cudaFuncSetAttribute(wgrad_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
 }
 
 TrainState* DeviceModel::train_state() {
@@ -391,11 +393,37 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     GNNQC_CUDA(cudaGetLastError());
     mark_end(st);
   };
+  // GNNQC_TRAIN_TC_WGRAD=0: the LSTM weight gradients on the CUDA-core kernel (A/B)
+  static const bool wgrad_tc = [] { const char* e = std::getenv("GNNQC_TRAIN_TC_WGRAD"); return !(e && std::strcmp(e, "0") == 0); }();
   for (int l = 0; l < L; ++l) {
     const int I = s.lstm_in[l], H = s.lstm_hid[l], Tl = plan.t_run[l];
     const float* xin = (l == 0) ? F(o_x1) : F(o_y[l - 1]);
     const int t_in_l = (l == 0) ? plan.t_run[0] : plan.t_out[l - 1];
     const long long dz_tile = static_cast<long long>(Tl) * 4 * H * kTile, dz_step = 4LL * H * kTile;
+    if (train_tc && wgrad_tc && I + H + 1 <= 256 && Tl > 0) {   // dW, dU, db of the layer in one tensor-core launch (wgrad_tc.cuh)
+      WgradTcArgs g;
+      g.x = xin; g.x_tile = static_cast<long long>(t_in_l) * I * kTile; g.x_step = static_cast<long long>(I) * kTile;
+      g.h = F(o_save[l]) + 5LL * H * kTile; g.h_tile = static_cast<long long>(Tl) * 6 * H * kTile; g.h_step = 6LL * H * kTile;
+      g.dz = F(o_dz[l]); g.dz_tile = dz_tile; g.dz_step = dz_step;
+      g.I = I; g.H = H; g.T = Tl; g.n_items = nt * Tl;
+      g.n16 = (I + H + 1 + 15) / 16 * 16;
+      g.n_stages = wgrad_tc_stages(g.n16);
+      g.partial = F(o_part);
+      const int m_chunks = (4 * H + 127) / 128, rows = I + H + 1;
+      long long slices = std::max<long long>(1, sm_count / m_chunks);
+      slices = std::min<long long>(slices, g.n_items);
+      slices = std::min<long long>(slices, static_cast<long long>(kPartialBytes / (size_t(rows) * 4 * H * 4)));
+      mark_begin("wgrad_tc", st);
+      wgrad_tc_kernel<<<dim3(static_cast<unsigned>(slices), m_chunks), kWgTcThreads, wgrad_tc_smem_bytes(g.n16, g.n_stages), st>>>(g);
+      GNNQC_CUDA(cudaGetLastError());
+      mark_end(st);
+      mark_begin("wgrad_reduce", st);
+      wgrad_tc_reduce_kernel<<<(rows * 4 * H * 32 + 255) / 256, 256, 0, st>>>(F(o_part), static_cast<int>(slices), I, H, rvec + s.off_lstm_w[l],
+                                                                             rvec + s.off_lstm_u[l], rvec + s.off_lstm_b[l]);
+      GNNQC_CUDA(cudaGetLastError());
+      mark_end(st);
+      continue;
+    }
     wgrad("wgrad_w", xin, static_cast<long long>(t_in_l) * I * kTile, static_cast<long long>(I) * kTile, I, F(o_dz[l]), dz_tile, dz_step, 4 * H, Tl,
           1, rvec + s.off_lstm_w[l], rvec + s.off_lstm_b[l]);
     // recurrent kernel: h_{t-1} (saved quantity 5) against dz_t, t = 1..T-1
