@@ -119,6 +119,10 @@ struct TrainState {
   long long step = 0;
   int kind = 0;            // 0 adam | 1 sgd | 2 rmsprop
   float last_lr = 0.f;
+  // the weight gradients of layer l run on a side stream while the backward pass goes on with layer l - 1
+  cudaStream_t side = nullptr;
+  cudaEvent_t ev_layer[kMaxLstmLayers] = {};
+  cudaEvent_t ev_done = nullptr;
 };
 
 void DeviceModel::configure_train_kernels() {
@@ -159,6 +163,10 @@ void DeviceModel::free_train_state() {
   cudaFree(train->vel);
   cudaFree(train->folded);
   cudaFree(train->stats);
+  if (train->side) cudaStreamDestroy(train->side);
+  for (cudaEvent_t e : train->ev_layer)
+    if (e) cudaEventDestroy(e);
+  if (train->ev_done) cudaEventDestroy(train->ev_done);
   delete train;
   train = nullptr;
 }
@@ -353,24 +361,6 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   GNNQC_CUDA(cudaGetLastError());
   mark_end(st);
 
-  // ---- backward through the LSTM stack -------------------------------------------------------------
-  const float* dy = F(o_dy7);
-  for (int l = L - 1; l >= 0; --l) {
-    const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
-    LayerArgs a;
-    a.in = dy; a.out = (l % 2 == 0) ? F(o_g0) : F(o_g1); a.w = d_packed_t + packed_t_off[l]; a.save = F(o_save[l]);
-    // the tensor-core backward needs many tile pairs in flight to cover its per-chunk MMA round trips; a small
-    // training batch (4,096 windows = 32 pairs) is faster on the fp32 kernel
-    a.wtc = (train_tc && nt >= tc_bwd_min_tiles) ? d_packed_tcb + packed_tcb_off[l] : nullptr;
-    a.amax = pool ? F(o_amax[l]) : nullptr; a.dz = F(o_dz[l]);
-    a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
-    mark_begin(kBwd[l], st);
-    dispatch(Op::Backward, s.lstm_in[l], s.lstm_hid[l], pool, last, a);
-    mark_end(st);
-    dy = a.out;
-  }
-  const float* dx1 = dy;
-
   // ---- weight gradients ------------------------------------------------------------------------------
   auto wgrad = [&](const char* name, const float* A, long long a_tile, long long a_step, int NA, const float* Bm, long long b_tile,
                    long long b_step, int NC, int n_steps, int bias, float* out_main, float* out_bias) {
@@ -395,7 +385,7 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   };
   // GNNQC_TRAIN_TC_WGRAD=0: the LSTM weight gradients on the CUDA-core kernel (A/B)
   static const bool wgrad_tc = [] { const char* e = std::getenv("GNNQC_TRAIN_TC_WGRAD"); return !(e && std::strcmp(e, "0") == 0); }();
-  for (int l = 0; l < L; ++l) {
+  auto layer_wgrad = [&](int l) {
     const int I = s.lstm_in[l], H = s.lstm_hid[l], Tl = plan.t_run[l];
     const float* xin = (l == 0) ? F(o_x1) : F(o_y[l - 1]);
     const int t_in_l = (l == 0) ? plan.t_run[0] : plan.t_out[l - 1];
@@ -422,21 +412,61 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
                                                                              rvec + s.off_lstm_u[l], rvec + s.off_lstm_b[l]);
       GNNQC_CUDA(cudaGetLastError());
       mark_end(st);
-      continue;
+      return;
     }
     wgrad("wgrad_w", xin, static_cast<long long>(t_in_l) * I * kTile, static_cast<long long>(I) * kTile, I, F(o_dz[l]), dz_tile, dz_step, 4 * H, Tl,
           1, rvec + s.off_lstm_w[l], rvec + s.off_lstm_b[l]);
     // recurrent kernel: h_{t-1} (saved quantity 5) against dz_t, t = 1..T-1
     wgrad("wgrad_u", F(o_save[l]) + 5LL * H * kTile, static_cast<long long>(Tl) * 6 * H * kTile, 6LL * H * kTile, H, F(o_dz[l]) + dz_step, dz_tile,
           dz_step, 4 * H, Tl - 1, 0, rvec + s.off_lstm_u[l], nullptr);
+  };
+
+  // ---- backward through the LSTM stack -------------------------------------------------------------
+  // GNNQC_TRAIN_OVERLAP=0: everything on the caller's stream (A/B).  The partial-sum scratch is shared by the layers'
+  // weight-gradient launches, which stay in order on the one side stream.
+  static const bool overlap_env = [] { const char* e = std::getenv("GNNQC_TRAIN_OVERLAP"); return !(e && std::strcmp(e, "0") == 0); }();
+  const bool overlap = overlap_env;
+  const cudaStream_t main_st = st;
+  if (overlap && !ts->side) {
+    GNNQC_CUDA(cudaStreamCreateWithFlags(&ts->side, cudaStreamNonBlocking));
+    for (int l = 0; l < kMaxLstmLayers; ++l) GNNQC_CUDA(cudaEventCreateWithFlags(&ts->ev_layer[l], cudaEventDisableTiming));
+    GNNQC_CUDA(cudaEventCreateWithFlags(&ts->ev_done, cudaEventDisableTiming));
   }
+  const float* dy = F(o_dy7);
+  for (int l = L - 1; l >= 0; --l) {
+    const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
+    LayerArgs a;
+    a.in = dy; a.out = (l % 2 == 0) ? F(o_g0) : F(o_g1); a.w = d_packed_t + packed_t_off[l]; a.save = F(o_save[l]);
+    // the tensor-core backward needs many tile pairs in flight to cover its per-chunk MMA round trips; a small
+    // training batch (4,096 windows = 32 pairs) is faster on the fp32 kernel
+    a.wtc = (train_tc && nt >= tc_bwd_min_tiles) ? d_packed_tcb + packed_tcb_off[l] : nullptr;
+    a.amax = pool ? F(o_amax[l]) : nullptr; a.dz = F(o_dz[l]);
+    a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
+    mark_begin(kBwd[l], st);
+    dispatch(Op::Backward, s.lstm_in[l], s.lstm_hid[l], pool, last, a);
+    mark_end(st);
+    dy = a.out;
+    if (overlap) {   // dz of layer l is complete: its weight gradients start on the side stream
+      GNNQC_CUDA(cudaEventRecord(ts->ev_layer[l], main_st));
+      GNNQC_CUDA(cudaStreamWaitEvent(ts->side, ts->ev_layer[l], 0));
+      st = ts->side;
+      layer_wgrad(l);
+      st = main_st;
+    }
+  }
+  const float* dx1 = dy;
+  if (!overlap)
+    for (int l = 0; l < L; ++l) layer_wgrad(l);
+
   {
+    if (overlap) st = ts->side;   // the dense layers' gradients share the partial-sum scratch: same stream as the layers'
     const long long ht = kHeadTrainFloats;
     const int D = s.dense_units, HL = s.lstm_hid[L - 1];
     wgrad("wgrad_dense", F(o_y[L - 1]), static_cast<long long>(HL) * kTile, 0, HL, F(o_head) + 2LL * D * kTile, ht, 0, D, 1, 1, rvec + s.off_d1_w,
           rvec + s.off_d1_b);
     wgrad("wgrad_dense", F(o_head), ht, 0, D, F(o_head) + 3LL * D * kTile, ht, 0, D, 1, 1, rvec + s.off_d2_w, rvec + s.off_d2_b);
     wgrad("wgrad_dense", F(o_head) + 1LL * D * kTile, ht, 0, D, F(o_head) + 4LL * D * kTile, ht, 0, 1, 1, 1, rvec + s.off_out_w, rvec + s.off_out_b);
+    st = main_st;
   }
   if (soil) {
     mark_begin("train_frontend_bwd", st);
@@ -459,6 +489,10 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   }
   sum_partials_kernel<<<1, 128, 0, st>>>(F(o_lossp), nt, 1, rvec + np + kRvecGcn);
   GNNQC_CUDA(cudaGetLastError());
+  if (overlap) {   // the caller's stream owns the reduction vector again only when the side stream is done with it
+    GNNQC_CUDA(cudaEventRecord(ts->ev_done, ts->side));
+    GNNQC_CUDA(cudaStreamWaitEvent(main_st, ts->ev_done, 0));
+  }
 }
 
 void DeviceModel::train_apply(float* rvec, const double* moments, float lr, cudaStream_t st) {
