@@ -437,9 +437,10 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
     LayerArgs a;
     a.in = dy; a.out = (l % 2 == 0) ? F(o_g0) : F(o_g1); a.w = d_packed_t + packed_t_off[l]; a.save = F(o_save[l]);
-    // the tensor-core backward needs many tile pairs in flight to cover its per-chunk MMA round trips; a small
-    // training batch (4,096 windows = 32 pairs) is faster on the fp32 kernel
-    a.wtc = (train_tc && nt >= tc_bwd_min_tiles) ? d_packed_tcb + packed_tcb_off[l] : nullptr;
+    // the tensor-core backward needs many tile pairs in flight to cover its per-chunk MMA round trips; for the narrow
+    // layers a small training batch (4,096 windows = 32 pairs) is faster on the fp32 kernel, the 64- and 128-unit layers
+    // are faster on the tensor cores at any size (measured at 128 and 4,096 windows)
+    a.wtc = (train_tc && (nt >= tc_bwd_min_tiles || s.lstm_hid[l] >= 64)) ? d_packed_tcb + packed_tcb_off[l] : nullptr;
     a.amax = pool ? F(o_amax[l]) : nullptr; a.dz = F(o_dz[l]);
     a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
     mark_begin(kBwd[l], st);
