@@ -721,9 +721,9 @@ def measure(wl, ctx, args, steps, warmup, with_cpu=True):
                     "algorithmic_flops_per_unit": alg_flops_per_unit(wl, W.m_steps), "fp32_cuda_core_peak_tflops": fp32.value,
                     "frac_of_fp32_cuda_core_peak": ach / fp32.value if fp32.value else None,
                     "note": "SURVEY 8(d) FLOPs per unit x units / pass time; the contractions run on tcgen05 with split-bf16 operands "
-                            "(3 MMA passes per product), the weight gradients on the CUDA cores"}
+                            "(3 MMA passes per product), the weight gradients included"}
         if W.base in ("ig", "ig_series"):
-            saved = 234e3 * (W.m_steps + 1) * 2   # bytes of saved gates written + read per attribution
+            saved = 140.5e3 * (W.m_steps + 1) * 2   # saved gates (12 B per cell, 11,712 cells per window) written + read per attribution
             roofline["saved_gate_stream"] = {"bound": "hbm", "achieved": saved * units / sec / 1e9, "peak": pk["hbm"], "unit": "GB/s",
                                              "frac": saved * units / sec / 1e9 / pk["hbm"]}
     else:
