@@ -306,7 +306,10 @@ int gnnqc_ig_cml_series(gnnqc_model* m, const gnnqc_series* series, const int32_
  *      everything is already divided by global_batch            -> all-reduce(sum) over ranks
  *   3. gnnqc_train_apply: closes the BatchNorm backward with the global sums, applies Adam to the
  *      device copy of the parameters, moves the BN statistics, refreshes the packed weights.
- * Single GPU: call 1-2-3 without the all-reduces (global_batch = B).  labels_dev: i64 [B]. */
+ * Single GPU: call 1-2-3 without the all-reduces (global_batch = B).  labels_dev: i64 [B].
+ * gnnqc_train_grads_* also uses a side stream owned by the handle (weight gradients of a layer while the backward pass
+ * continues below it); it forks from and joins `stream` inside the call, so for the caller everything stays ordered on
+ * `stream` as usual. */
 int64_t gnnqc_train_vector_len(const gnnqc_model* m);
 int gnnqc_train_moments_cml(gnnqc_model* m, const float* features_dev, int64_t n_rows,
                             double* moments_dev, void* stream);
