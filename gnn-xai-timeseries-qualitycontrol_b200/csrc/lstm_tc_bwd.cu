@@ -70,11 +70,24 @@ bool bwd_case(BwdOp op, const BwdArgs& a) {
 }
 
 bool bwd_dispatch(BwdOp op, int in, int hid, bool pool, bool last, const BwdArgs& a) {
-  if (in == 2 && hid == 16 && !pool && !last) return bwd_case<2, 16, false, false, 4, 1>(op, a);
-  if (in == 18 && hid == 16 && !pool && !last) return bwd_case<18, 16, false, false, 4, 1>(op, a);
-  if (in == 16 && hid == 16 && pool && !last) return bwd_case<16, 16, true, false, 4, 1>(op, a);
-  if (in == 16 && hid == 32 && !pool && !last) return bwd_case<16, 32, false, false, 4, 1>(op, a);
-  if (in == 32 && hid == 32 && pool && !last) return bwd_case<32, 32, true, false, 4, 1>(op, a);
+  // Narrow layers come in two shapes: four groups of 128 threads per SM (one thread per window, all units), which
+  // keeps the most windows in flight, and two groups of 256 threads (two threads per window, half the units each),
+  // whose step is shorter (~4 us against ~6 us).  The second is faster as long as all tile pairs fit in one wave of
+  // it (measured: training steps of 128 and 4,096 windows; a 65,536-window IG chunk is 25 % slower with it).
+  // GNNQC_TC_BWD_SPLIT2=0 / 1 forces one of them (A/B).
+  static const int force = [] { const char* e = std::getenv("GNNQC_TC_BWD_SPLIT2"); return e ? std::atoi(e) : -1; }();
+  const bool split2 = force >= 0 ? force != 0 : (a.n_tiles + 1) / 2 <= 2LL * a.sm_count;
+#define GNNQC_NARROW(I_, H_, POOL_)                                                    \
+  if (in == I_ && hid == H_ && pool == POOL_ && !last) {                               \
+    if (op == BwdOp::Configure) return bwd_case<I_, H_, POOL_, false, 4, 1>(op, a) && bwd_case<I_, H_, POOL_, false, 2, 2>(op, a); \
+    return split2 ? bwd_case<I_, H_, POOL_, false, 2, 2>(op, a) : bwd_case<I_, H_, POOL_, false, 4, 1>(op, a);                   \
+  }
+  GNNQC_NARROW(2, 16, false)
+  GNNQC_NARROW(18, 16, false)
+  GNNQC_NARROW(16, 16, true)
+  GNNQC_NARROW(16, 32, false)
+  GNNQC_NARROW(32, 32, true)
+#undef GNNQC_NARROW
   if (in == 32 && hid == 64 && !pool && !last) return bwd_case<32, 64, false, false, 2, 1>(op, a);
   if (in == 64 && hid == 64 && pool && !last) return bwd_case<64, 64, true, false, 2, 1>(op, a);
   if (in == 64 && hid == 128 && !pool && last) return bwd_case<64, 128, false, true, 1, 2>(op, a);

@@ -241,7 +241,7 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
   static const bool train_tc = [] { const char* e = std::getenv("GNNQC_TRAIN_TC"); return !(e && std::strcmp(e, "0") == 0); }();
   // GNNQC_TRAIN_TC_BWD_MIN_TILES: smallest step (in 64-window tiles) whose backward runs on the tensor-core kernels
   // (default 2 per SM); read per call so a test can send a small batch down that path
-  long long tc_bwd_min_tiles = 2LL * sm_count;
+  long long tc_bwd_min_tiles = 1;
   if (const char* e = std::getenv("GNNQC_TRAIN_TC_BWD_MIN_TILES")) tc_bwd_min_tiles = std::max(1LL, std::atoll(e));
   StackPlan plan(s, T);
   const int L = s.n_lstm;
@@ -437,9 +437,8 @@ void DeviceModel::train_grads(const float* feat, const float* anom, const long l
     const bool last = (l == L - 1), pool = !last && (l % 2 == 1);
     LayerArgs a;
     a.in = dy; a.out = (l % 2 == 0) ? F(o_g0) : F(o_g1); a.w = d_packed_t + packed_t_off[l]; a.save = F(o_save[l]);
-    // the tensor-core backward needs many tile pairs in flight to cover its per-chunk MMA round trips; for the narrow
-    // layers a small training batch (4,096 windows = 32 pairs) is faster on the fp32 kernel, the 64- and 128-unit layers
-    // are faster on the tensor cores at any size (measured at 128 and 4,096 windows)
+    // tensor-core backward at every batch size (lstm_tc_bwd.cu picks the two-threads-per-window shape of the narrow
+    // layers for small steps); GNNQC_TRAIN_TC_BWD_MIN_TILES=<n> sends smaller steps of the narrow layers to the fp32 kernel
     a.wtc = (train_tc && (nt >= tc_bwd_min_tiles || s.lstm_hid[l] >= 64)) ? d_packed_tcb + packed_tcb_off[l] : nullptr;
     a.amax = pool ? F(o_amax[l]) : nullptr; a.dz = F(o_dz[l]);
     a.T = plan.t_run[l]; a.n_tiles = nt; a.sm_count = sm_count; a.st = st;
