@@ -88,8 +88,18 @@ bool bwd_dispatch(BwdOp op, int in, int hid, bool pool, bool last, const BwdArgs
   GNNQC_NARROW(16, 32, false)
   GNNQC_NARROW(32, 32, true)
 #undef GNNQC_NARROW
-  if (in == 32 && hid == 64 && !pool && !last) return bwd_case<32, 64, false, false, 2, 1>(op, a);
-  if (in == 64 && hid == 64 && pool && !last) return bwd_case<64, 64, true, false, 2, 1>(op, a);
+  // 64-unit layers: two threads per window as well (32 units each; 96 instead of 168 registers, twice the warps per
+  // scheduler).  IG backward 26.6 -> 21.4 ms (layer 5) and 32.5 -> 25.2 ms (layer 6) per 51 x 65,536 windows.
+  // GNNQC_TC_BWD_WIDE2=0: one thread per window (A/B).
+  static const bool wide2 = [] { const char* e = std::getenv("GNNQC_TC_BWD_WIDE2"); return !(e && std::atoi(e) == 0); }();
+  if (in == 32 && hid == 64 && !pool && !last) {
+    if (op == BwdOp::Configure) return bwd_case<32, 64, false, false, 2, 1>(op, a) && bwd_case<32, 64, false, false, 2, 2>(op, a);
+    return wide2 ? bwd_case<32, 64, false, false, 2, 2>(op, a) : bwd_case<32, 64, false, false, 2, 1>(op, a);
+  }
+  if (in == 64 && hid == 64 && pool && !last) {
+    if (op == BwdOp::Configure) return bwd_case<64, 64, true, false, 2, 1>(op, a) && bwd_case<64, 64, true, false, 2, 2>(op, a);
+    return wide2 ? bwd_case<64, 64, true, false, 2, 2>(op, a) : bwd_case<64, 64, true, false, 2, 1>(op, a);
+  }
   if (in == 64 && hid == 128 && !pool && last) return bwd_case<64, 128, false, true, 1, 2>(op, a);
   return false;
 }

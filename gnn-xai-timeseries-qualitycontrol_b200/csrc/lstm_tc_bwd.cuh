@@ -49,6 +49,9 @@ struct TcBwdCfg {
   static constexpr int TMEM_GROUP = 2 * N;                // D[2] per group
   static constexpr size_t PACKED_BYTES = size_t(NCHUNK) * PIECE;
   static_assert(H % (UB * SPLIT) == 0 && GRP * TMEM_GROUP <= 512 && N <= 256 && (!STREAM || GRP == 1), "shape not covered");
+  // a thread's successive chunks must use successive phases of its ring buffer's barriers (parity waits cannot tell
+  // phases two apart): one split walks both buffers in turn, two splits own one buffer each - four splits would alias
+  static_assert(SPLIT == 1 || SPLIT == NBUF, "ring depth must match the unit split");
   static_assert(SMEM_BYTES <= 227 * 1024, "operands do not fit in shared memory");
 };
 
