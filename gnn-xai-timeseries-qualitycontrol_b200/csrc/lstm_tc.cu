@@ -18,25 +18,45 @@
 namespace gnnqc {
 namespace {
 
+// Whether the gate-saving narrow kernel runs with two threads per window (filled in from measurements).
+bool tc_fwd_split2(int hid, long long n_tiles, int sm_count) {
+  (void)hid;
+  return (n_tiles + 1) / 2 <= 2LL * sm_count;   // all tile pairs in one wave of the two-group shape
+}
+
 template <int I, int H, bool POOL, bool SAVE>
 struct TcLaunch {
   using Cfg = TcCfg<I, H>;
+  using Cfg2 = TcCfg<I, H, 2>;   // two threads per window (gate-saving kernels only: IG and training forward)
   static auto kernel() { return lstm_tc_kernel<I, H, POOL, SAVE>; }
   static auto kernel_compact() { return lstm_tc_kernel<I, H, POOL, SAVE, SAVE>; }   // 16-bit fixed-point gates (save_cells2)
+  static auto kernel2() { return lstm_tc_kernel<I, H, POOL, SAVE, false, SAVE ? 2 : 1>; }
+  static auto kernel2_compact() { return lstm_tc_kernel<I, H, POOL, SAVE, SAVE, SAVE ? 2 : 1>; }
   static void configure() {
     GNNQC_CUDA(cudaFuncSetAttribute(kernel(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
-    if (SAVE) GNNQC_CUDA(cudaFuncSetAttribute(kernel_compact(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+    if (SAVE) {
+      GNNQC_CUDA(cudaFuncSetAttribute(kernel_compact(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg::SMEM_BYTES)));
+      GNNQC_CUDA(cudaFuncSetAttribute(kernel2(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg2::SMEM_BYTES)));
+      GNNQC_CUDA(cudaFuncSetAttribute(kernel2_compact(), cudaFuncAttributeMaxDynamicSharedMemorySize, int(Cfg2::SMEM_BYTES)));
+    }
   }
   static void launch(const float* x, float* y, const unsigned char* wpk, int T, int t_in, int t_out, long long n_tiles, int sm_count, cudaStream_t st,
                      float* save, float* amax, int nsave) {
-    // One persistent CTA per SM (four window groups inside, lstm_tc.cuh); tiles are dealt evenly.
+    // One persistent CTA per SM (window groups inside, lstm_tc.cuh); tiles are dealt evenly.
     if (std::getenv("GNNQC_DEBUG")) {
       cudaFuncAttributes fa;
       GNNQC_CUDA(cudaFuncGetAttributes(&fa, kernel()));
       std::fprintf(stderr, "[gnnqc] tc I=%d H=%d regs=%d local=%zu smem=%zu tmem_cols=%d\n", I, H, fa.numRegs, fa.localSizeBytes, size_t(Cfg::SMEM_BYTES), Cfg::TMEM_COLS);
     }
     const long long grid = std::min<long long>(n_tiles, sm_count);
-    (SAVE && nsave == kSaveCompact ? kernel_compact() : kernel())<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
+    // Two threads per window shorten the per-step chain and halve the windows in flight: GNNQC_TC_FWD_SPLIT2 = 0 / 1
+    // forces a shape, otherwise the rule measured for this layer shape applies (tc_fwd_split2).
+    static const int force = [] { const char* e = std::getenv("GNNQC_TC_FWD_SPLIT2"); return e ? std::atoi(e) : -1; }();
+    const bool split2 = SAVE && (force >= 0 ? force != 0 : tc_fwd_split2(H, n_tiles, sm_count));
+    if (split2)
+      (nsave == kSaveCompact ? kernel2_compact() : kernel2())<<<static_cast<unsigned>(grid), Cfg2::NT, Cfg2::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
+    else
+      (SAVE && nsave == kSaveCompact ? kernel_compact() : kernel())<<<static_cast<unsigned>(grid), Cfg::NT, Cfg::SMEM_BYTES, st>>>(x, y, wpk, T, t_in, t_out, static_cast<int>(n_tiles), save, amax, nsave);
     GNNQC_CUDA(cudaGetLastError());
   }
 };

@@ -49,14 +49,17 @@ __device__ __forceinline__ void fill_ones_tile(unsigned char* dst, int tid, int 
 }
 __host__ __device__ constexpr size_t tc_bias_tile_bytes(int n) { return size_t(2) * n * 16; }   // [2][n][8] fp16
 
-template <int I, int H>
+// SPLIT = threads per window: 1 (four groups of 128 windows per CTA, every thread all H units) or 2 (two groups, a thread
+// takes every other block of 8 units: half the cell arithmetic on the per-step chain, half the windows in flight).
+template <int I, int H, int SPLIT = 1>
 struct TcCfg {
   static constexpr int IP = (I + 7) / 8 * 8;              // input channels padded to a core-matrix column
   static constexpr int KP = (IP + H + 15) / 16 * 16;      // contraction length per MMA chain
   static constexpr int N = 4 * H;                         // gate columns (Keras order i | f | c | o)
   static constexpr int ROWS = 128;                        // windows per group = TMEM lanes
-  static constexpr int GROUPS = 4;
-  static constexpr int NT = GROUPS * ROWS;
+  static constexpr int GROUPS = 4 / SPLIT;
+  static constexpr int NT = GROUPS * SPLIT * ROWS;
+  static constexpr int UPT = H / SPLIT;                   // units per thread
   static constexpr int NST = (I >= 32 && H >= 32) ? 1 : 2;   // x ring depth per group
   static constexpr int TMEM_COLS = GROUPS * N;            // 256 or 512
   static constexpr int XBYTES = I * kTile * 4;            // one 64-window half of one step
@@ -77,6 +80,7 @@ struct TcCfg {
   // packed weights in global memory: B_hi | B_lo | bias tile (fp16 hi / lo rows, Keras column order)
   static constexpr size_t PACKED_BYTES = 2 * B_BYTES + BT_BYTES;
   static_assert(N <= 256 && (N & (N - 1)) == 0 && TMEM_COLS <= 512, "one MMA covers at most 256 gate columns");
+  static_assert((SPLIT == 1 || SPLIT == 2) && H % (8 * SPLIT) == 0, "unit split not covered");
   static_assert(SMEM_BYTES <= 227 * 1024, "operands do not fit in shared memory");
 };
 
@@ -262,8 +266,8 @@ __device__ __forceinline__ void pool_arg_update(unsigned long long& bits, int un
   else if (greater) bits = (bits & ~m) | (static_cast<unsigned long long>(ph) << (2 * unit));
 }
 
-template <int I, int H, bool POOL, bool SAVE = false, bool COMPACT = false>   // COMPACT: nsave == kSaveCompact
-__global__ void __launch_bounds__((TcCfg<I, H>::NT), 1)
+template <int I, int H, bool POOL, bool SAVE = false, bool COMPACT = false, int SPLIT = 1>   // COMPACT: nsave == kSaveCompact
+__global__ void __launch_bounds__((TcCfg<I, H, SPLIT>::NT), 1)
 lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_stride][I][64]
                float* __restrict__ yout,                 // [n_tiles][t_out_stride][H][64]
                const unsigned char* __restrict__ wpk,    // B_hi | B_lo | bias (TcCfg::PACKED_BYTES)
@@ -271,7 +275,7 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
                float* __restrict__ save = nullptr,       // SAVE: [n_tiles][T][5][H][64] gates i, f, g, o and c
                float* __restrict__ amax = nullptr,       // SAVE && POOL: [n_tiles][t_out_stride][H][64] argmax step
                int nsave = 5) {                          // SAVE: 5, 6 (h_t as well: training) or kSaveCompact (save_cells2)
-  using C = TcCfg<I, H>;
+  using C = TcCfg<I, H, SPLIT>;
   extern __shared__ __align__(128) unsigned char sm[];
   float* bias = reinterpret_cast<float*>(sm + C::OFF_BIAS);
   __shared__ uint32_t tmem_slot;
@@ -279,8 +283,8 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
   // tile, loop bounds, operand addresses) is warp-uniform: uniform branches, and the tcgen05.mma / cp.async.bulk
   // operands stay in uniform registers instead of being broadcast lane by lane around every instruction.
   const int tid = threadIdx.x, lane = tid & 31, warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
-  const int g = warp >> 2, quarter = warp & 3, half = quarter >> 1;
-  const int r = quarter * 32 + lane, b = (quarter & 1) * 32 + lane;   // group, TMEM lane, tile of the pair, window in tile
+  const int g = warp / (4 * SPLIT), sp = (warp >> 2) % SPLIT, quarter = warp & 3, half = quarter >> 1;
+  const int r = quarter * 32 + lane, b = (quarter & 1) * 32 + lane;   // group, unit split, TMEM lane, tile of the pair, window in tile
 
   unsigned char* gsm = sm + C::OFF_GROUPS + size_t(g) * C::GROUP_BYTES;
   uint4* Ahi = reinterpret_cast<uint4*>(gsm + C::G_AHI);   // 16-byte chunk index: kb * ROWS + row
@@ -304,9 +308,9 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
 
   // ---- set-up --------------------------------------------------------------------------------
   if (warp == 0) umma::tmem_alloc(&tmem_slot, C::TMEM_COLS);
-  if (r == 0) {
+  if (r == 0 && sp == 0) {
     for (int s = 0; s < C::NST; ++s) ptx::mbar_init(&x_full[s], 1);
-    ptx::mbar_init(a_ready, C::ROWS);
+    ptx::mbar_init(a_ready, C::ROWS * SPLIT);
     ptx::mbar_init(d_full, 1);
     ptx::mbar_init_fence();
   }
@@ -322,14 +326,14 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
       for (int i = tid; i < C::N; i += C::NT) bias[i] = __half2float(bt[i * 8]) + __half2float(bt[i * 8 + 1]);
     }
     uint4* gz = reinterpret_cast<uint4*>(gsm);
-    for (int i = r; i < static_cast<int>(C::GROUP_BYTES / 16); i += C::ROWS) gz[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (int i = r + sp * C::ROWS; i < static_cast<int>(C::GROUP_BYTES / 16); i += C::ROWS * SPLIT) gz[i] = make_uint4(0u, 0u, 0u, 0u);
   }
   umma::fence_async_smem();
   umma::fence_before_sync();
   __syncthreads();
   umma::fence_after_sync();
   const uint32_t tbase = tmem_slot + static_cast<uint32_t>(g * C::N);
-  const bool issuer = quarter == 0;
+  const bool issuer = quarter == 0 && sp == 0;
   const int g_u = g;
   const uint32_t sm_u = ptx::smem_addr(sm);
   const uint32_t gsm_u = sm_u + static_cast<uint32_t>(C::OFF_GROUPS + size_t(g_u) * C::GROUP_BYTES);
@@ -347,13 +351,13 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
     ptx::bulk_load(xs + (s * 2 + 0) * I * kTile, xin + (t_a * t_in_stride + t) * (I * kTile), C::XBYTES, &x_full[s]);
     if (second) ptx::bulk_load(xs + (s * 2 + 1) * I * kTile, xin + ((t_a + R) * t_in_stride + t) * (I * kTile), C::XBYTES, &x_full[s]);
   };
-  if (r == 0)
+  if (r == 0 && sp == 0)
     for (long long q = 0; q < C::NST && q < total; ++q) issue_load(q);
 
   constexpr uint32_t idesc = umma::instr_desc_f16(C::ROWS, C::N);
   const uint32_t lane_base = static_cast<uint32_t>((warp & 3) * 32) << 16;
-  f32x2 cst[H / 2];                                           // cell states, two units per register pair
-  float pmax[POOL ? H : 1];
+  f32x2 cst[C::UPT / 2];                                      // cell states, two units per register pair
+  float pmax[POOL ? C::UPT : 1];
   unsigned long long parg = 0ull;
   int rho = 0, t = 0;
   for (long long q = 0; q < total; ++q) {
@@ -361,15 +365,16 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
     const bool valid = rho + (2 * g + half) * R < my_tiles;    // uniform over the two warps of a half
     if (t == 0) {
 #pragma unroll
-      for (int j = 0; j < H / 2; ++j) cst[j] = 0ull;
+      for (int j = 0; j < C::UPT / 2; ++j) cst[j] = 0ull;
     }
-    // x_t -> bf16 hi/lo operand chunks
+    // x_t -> fp16 hi/lo operand chunks (the column blocks dealt over the threads of a window)
     const int s = static_cast<int>(q % C::NST);
     if (valid) {
       ptx::mbar_wait(&x_full[s], static_cast<uint32_t>((q / C::NST) & 1));
       const float* xrow = xs + (s * 2 + half) * I * kTile + b;
 #pragma unroll
       for (int kb = 0; kb < C::IP / 8; ++kb) {
+        if (SPLIT > 1 && kb % SPLIT != sp) continue;
         float v[8];
 #pragma unroll
         for (int i = 0; i < 8; ++i) v[i] = (kb * 8 + i < I) ? xrow[(kb * 8 + i) * kTile] : 0.f;
@@ -409,7 +414,8 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
     if (valid) {
       const bool last_step = (t == T - 1);
 #pragma unroll
-      for (int b8 = 0; b8 < H / 8; ++b8) {
+      for (int lb = 0; lb < C::UPT / 8; ++lb) {
+        const int b8 = lb * SPLIT + sp, l0 = lb * 8;     // unit block of this thread, its slot in cst / pmax
         float zi[8], zf[8], zg[8], zo[8], hv[8];
         const uint32_t col0 = tbase + lane_base + b8 * 8;
         umma::tmem_ld8x4(col0, col0 + H, col0 + 2 * H, col0 + 3 * H, zi, zf, zg, zo);
@@ -424,7 +430,7 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
             po = add2(po, *reinterpret_cast<const f32x2*>(bias + 3 * H + j0 + i));
           }
           f32x2 sv[5];
-          up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[(j0 + i) / 2], sv), hv[i], hv[i + 1]);
+          up2(lstm_cell2<SAVE>(pi, pf, pg, po, cst[(l0 + i) / 2], sv), hv[i], hv[i + 1]);
           if (SAVE) {
             save_cells2<COMPACT>(save + (((tile * T + t) * nsave) * H + j0 + i) * kTile + b, nsave, H, sv, hv[i], hv[i + 1]);
           }
@@ -433,17 +439,17 @@ lstm_tc_kernel(const float* __restrict__ xin,            // [n_tiles][t_in_strid
           const int ph = t % 3;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
-            if (SAVE) pool_arg_update(parg, j0 + i, ph, hv[i] > pmax[j0 + i]);
-            pmax[j0 + i] = (ph == 0) ? hv[i] : fmaxf(pmax[j0 + i], hv[i]);
+            if (SAVE) pool_arg_update(parg, l0 + i, ph, hv[i] > pmax[l0 + i]);
+            pmax[l0 + i] = (ph == 0) ? hv[i] : fmaxf(pmax[l0 + i], hv[i]);
           }
           if (ph == 2) {
             float* yo = yout + ((tile * t_out_stride + t / 3) * H + j0) * kTile + b;
 #pragma unroll
-            for (int i = 0; i < 8; ++i) yo[i * kTile] = pmax[j0 + i];
+            for (int i = 0; i < 8; ++i) yo[i * kTile] = pmax[l0 + i];
             if (SAVE) {
               float* ao = amax + ((tile * t_out_stride + t / 3) * H + j0) * kTile + b;
 #pragma unroll
-              for (int i = 0; i < 8; ++i) ao[i * kTile] = static_cast<float>((parg >> (2 * (j0 + i))) & 3ull);
+              for (int i = 0; i < 8; ++i) ao[i * kTile] = static_cast<float>((parg >> (2 * (l0 + i))) & 3ull);
             }
           }
         } else {
