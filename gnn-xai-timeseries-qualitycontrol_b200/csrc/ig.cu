@@ -184,8 +184,8 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
   extra_bytes = align_up(extra_bytes, 256);
   const long long chunk = balanced_chunk(n_tiles, static_cast<long long>(ig_scratch_budget_bytes() / per_tile));
   // dx1 of a whole group of interpolation points stays resident, so the front-end backward reads the features and writes
-  // the attributions once per group instead of once per alpha (ig_frontend_bwd.cuh); GNNQC_IG_DX_MB bounds it (default 40 GiB)
-  static const size_t dx_budget = [] { const char* e = std::getenv("GNNQC_IG_DX_MB"); return (e ? std::strtoull(e, nullptr, 10) : size_t(40960)) << 20; }();
+  // the attributions once per group instead of once per alpha (ig_frontend_bwd.cuh); GNNQC_IG_DX_MB bounds it (default 48 GiB: 51 alphas of a 75,776-window wave)
+  static const size_t dx_budget = [] { const char* e = std::getenv("GNNQC_IG_DX_MB"); return (e ? std::strtoull(e, nullptr, 10) : size_t(49152)) << 20; }();
   const long long group = std::max<long long>(1, std::min<long long>(std::min<long long>(m_steps + 1, kIgMaxGroup), static_cast<long long>(dx_budget / (size_t(chunk) * sg))));
   const size_t dx_bytes = size_t(group) * size_t(chunk) * sg;
   char* base = static_cast<char*>(scratch(extra_bytes + size_t(chunk) * per_tile + dx_bytes));
