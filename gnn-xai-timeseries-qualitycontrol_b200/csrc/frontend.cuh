@@ -473,11 +473,16 @@ __global__ void __launch_bounds__(256) head_grad_kernel(const float* __restrict_
   float acc[DQ];
 #pragma unroll
   for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b1 + q * DQ + o);
-#pragma unroll 8
+  // the weights are warp-uniform: 16-byte loads, four FMAs each (the kernel was bound by one 4-byte load per FMA)
+#pragma unroll 4
   for (int k = 0; k < HL; ++k) {
     const float h = __ldg(y7 + (tile * HL + k) * kTile + b);
+    const float4* wr = reinterpret_cast<const float4*>(w1 + k * D + q * DQ);
 #pragma unroll
-    for (int o = 0; o < DQ; ++o) acc[o] = fmaf(h, __ldg(w1 + k * D + q * DQ + o), acc[o]);
+    for (int o = 0; o < DQ; o += 4) {
+      const float4 w = __ldg(wr + o / 4);
+      acc[o] = fmaf(h, w.x, acc[o]); acc[o + 1] = fmaf(h, w.y, acc[o + 1]); acc[o + 2] = fmaf(h, w.z, acc[o + 2]); acc[o + 3] = fmaf(h, w.w, acc[o + 3]);
+    }
   }
 #pragma unroll
   for (int o = 0; o < DQ; ++o) {
@@ -487,11 +492,15 @@ __global__ void __launch_bounds__(256) head_grad_kernel(const float* __restrict_
   __syncthreads();
 #pragma unroll
   for (int o = 0; o < DQ; ++o) acc[o] = __ldg(b2 + q * DQ + o);
-#pragma unroll 8
+#pragma unroll 4
   for (int k = 0; k < D; ++k) {
     const float h = d1_s[k * kTile + b];
+    const float4* wr = reinterpret_cast<const float4*>(w2 + k * D + q * DQ);
 #pragma unroll
-    for (int o = 0; o < DQ; ++o) acc[o] = fmaf(h, __ldg(w2 + k * D + q * DQ + o), acc[o]);
+    for (int o = 0; o < DQ; o += 4) {
+      const float4 w = __ldg(wr + o / 4);
+      acc[o] = fmaf(h, w.x, acc[o]); acc[o + 1] = fmaf(h, w.y, acc[o + 1]); acc[o + 2] = fmaf(h, w.z, acc[o + 2]); acc[o + 3] = fmaf(h, w.w, acc[o + 3]);
+    }
   }
   float m2[DQ];
 #pragma unroll
@@ -512,22 +521,34 @@ __global__ void __launch_bounds__(256) head_grad_kernel(const float* __restrict_
   __syncthreads();
   // grad at dense-1 pre-activation: sum_o dd2[o] * w2[k][o] * slope1[k]
 #pragma unroll
-  for (int kk = 0; kk < DQ; ++kk) {
-    const int k = q * DQ + kk;
-    float s = 0.f;
-    for (int o = 0; o < D; ++o) s = fmaf(d2_s[o * kTile + b], __ldg(w2 + k * D + o), s);
-    acc[kk] = s * m1_s[k * kTile + b];
+  for (int kk = 0; kk < DQ; ++kk) acc[kk] = 0.f;
+  for (int o = 0; o < D; o += 4) {   // four gradients from shared memory serve all 16 rows of this thread; same summation order as before
+    const float g0 = d2_s[o * kTile + b], g1 = d2_s[(o + 1) * kTile + b], g2 = d2_s[(o + 2) * kTile + b], g3 = d2_s[(o + 3) * kTile + b];
+#pragma unroll
+    for (int kk = 0; kk < DQ; ++kk) {
+      const float4 w = __ldg(reinterpret_cast<const float4*>(w2 + (q * DQ + kk) * D + o));
+      acc[kk] = fmaf(g3, w.w, fmaf(g2, w.z, fmaf(g1, w.y, fmaf(g0, w.x, acc[kk]))));
+    }
   }
+#pragma unroll
+  for (int kk = 0; kk < DQ; ++kk) acc[kk] *= m1_s[(q * DQ + kk) * kTile + b];
   __syncthreads();   // all reads of d1_s (none pending) - reuse it for the dense-1 gradients
 #pragma unroll
   for (int kk = 0; kk < DQ; ++kk) d1_s[(q * DQ + kk) * kTile + b] = acc[kk];
   __syncthreads();
-  for (int kk = 0; kk < HL / 4; ++kk) {
-    const int k = q * (HL / 4) + kk;
-    float s = 0.f;
-    for (int o = 0; o < D; ++o) s = fmaf(d1_s[o * kTile + b], __ldg(w1 + k * D + o), s);
-    dy7[(tile * HL + k) * kTile + b] = s;
+  float dy[HL / 4];
+#pragma unroll
+  for (int kk = 0; kk < HL / 4; ++kk) dy[kk] = 0.f;
+  for (int o = 0; o < D; o += 4) {
+    const float g0 = d1_s[o * kTile + b], g1 = d1_s[(o + 1) * kTile + b], g2 = d1_s[(o + 2) * kTile + b], g3 = d1_s[(o + 3) * kTile + b];
+#pragma unroll
+    for (int kk = 0; kk < HL / 4; ++kk) {
+      const float4 w = __ldg(reinterpret_cast<const float4*>(w1 + (q * (HL / 4) + kk) * D + o));
+      dy[kk] = fmaf(g3, w.w, fmaf(g2, w.z, fmaf(g1, w.y, fmaf(g0, w.x, dy[kk]))));
+    }
   }
+#pragma unroll
+  for (int kk = 0; kk < HL / 4; ++kk) dy7[(tile * HL + q * (HL / 4) + kk) * kTile + b] = dy[kk];
 }
 
 }  // namespace gnnqc

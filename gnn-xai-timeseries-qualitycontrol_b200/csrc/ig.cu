@@ -232,6 +232,7 @@ void DeviceModel::ig_core(long long B, int T, int m_steps, float* scores, cudaSt
         in = a.out;
         t_in = plan.t_out[l];
       }
+      if ((s.off_d1_w | s.off_d2_w) & 3) throw std::invalid_argument("integrated gradients: dense kernels must start on a 16-byte boundary of the parameter vector");
       mark_begin("ig_head", st);
       head_grad_kernel<128, 64><<<static_cast<unsigned>(nt), 256, 0, st>>>(in, prm + s.off_d1_w, prm + s.off_d1_b, prm + s.off_d2_w,
                                                                             prm + s.off_d2_b, prm + s.off_out_w, prm + s.off_out_b,
