@@ -480,7 +480,7 @@ class Workload:
             self.step = lambda: model.score_seq(x)
             self.in_bytes = x.numel() * 4
             host_x = x.cpu().pin_memory()
-            scorer = SeqHostScorer(model, chunk_seqs=16384)
+            scorer = SeqHostScorer(model)   # chunks of one wave of the LSTM kernels
 
             def e2e():
                 out = scorer.score(host_x)

@@ -83,10 +83,12 @@ class CmlHostScorer:
 class SeqHostScorer:
     """Same for [n_seq, T, C] host sequences (baseline models)."""
 
-    def __init__(self, native, chunk_seqs=65536):
+    def __init__(self, native, chunk_seqs=None):
         self.m = native
         self.dev = torch.device("cuda", native.device)
-        self.chunk = int(chunk_seqs)
+        # default: one wave of the LSTM kernels (SMs x 4 window groups x 128 sequences) - the recurrences are serial
+        # chains per group, so a smaller chunk takes the same kernel time and only adds passes
+        self.chunk = int(chunk_seqs) if chunk_seqs else torch.cuda.get_device_properties(self.dev).multi_processor_count * 512
         self.copy_stream = torch.cuda.Stream(self.dev)
         self.compute_stream = torch.cuda.Stream(self.dev)
         self.slots = [None, None]
