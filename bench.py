@@ -399,12 +399,28 @@ class Workload:
                 host = {k: batch[k].cpu().pin_memory() for k in keys}
                 host_labels = labels.cpu().pin_memory()
 
+                copy_stream, pending = torch.cuda.Stream(dev), []
+
+                def upload():   # as libs/fit_model.py's epoch loop: the next step's batch travels on a copy stream while this step runs
+                    with torch.cuda.stream(copy_stream):
+                        d = {k: host[k].to(dev, non_blocking=True) for k in keys}
+                        lab = host_labels.to(dev, non_blocking=True)
+                        ev = torch.cuda.Event()
+                        ev.record(copy_stream)
+                    return d, lab, ev
+
                 def e2e():
-                    d = {k: host[k].to(dev, non_blocking=True) for k in keys}
-                    return train(d, host_labels.to(dev, non_blocking=True)).cpu()
+                    d, lab, ev = pending.pop() if pending else upload()
+                    pending.append(upload())
+                    cur = torch.cuda.current_stream(dev)
+                    cur.wait_event(ev)
+                    for v in list(d.values()) + [lab]:
+                        v.record_stream(cur)
+                    return train(d, lab).cpu()
                 self.e2e_step = e2e
                 self.h2d, self.d2h = self.in_bytes + B * 8, 4
-                self.e2e_path = "pinned host -> H2D of the batch and labels -> gnnqc_train_moments_cml / all-reduce / gnnqc_train_grads_cml / all-reduce / gnnqc_train_apply -> D2H of the loss"
+                self.e2e_path = ("pinned host -> H2D of the NEXT step's batch and labels on a copy stream (one upload per step) | gnnqc_train_moments_cml / all-reduce / "
+                                 "gnnqc_train_grads_cml / all-reduce / gnnqc_train_apply -> D2H of the loss")
         elif b == "cml_series":
             from gnnqc.series import CmlSeries
             np = ctx.np

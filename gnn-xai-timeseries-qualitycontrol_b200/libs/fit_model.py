@@ -68,55 +68,119 @@ def _device_of(native):
     return torch.device("cuda", native.device) if native.device is not None and native.device >= 0 else torch.device("cpu")
 
 
-def train_step(native, inputs, labels, class_weights, lr):
-    """One optimisation step on one global batch; returns the (global) loss.  Works for one process
-    or for every rank of a torch.distributed group (each rank passes the same global batch and
-    works on its own shard).  A rank whose shard is empty (the last, partial batch of an epoch can hold
-    fewer windows than there are ranks; Keras' fit trains on it too) skips the device calls and
-    contributes zeros to both all-reduces, so the collectives stay matched on every rank."""
+def shard_for_rank(native, inputs, labels):
+    """This rank's part of one global batch, still wherever the batch lives (host or device): (kind, shard, labels,
+    global batch size).  Splitting first lets train_model upload only the shard, one batch ahead of the step."""
     rank, world_size = dp.world()
-    dev = _device_of(native)
-    cw = (class_weights[0], class_weights[1]) if class_weights else (1.0, 1.0)
     labels = torch.as_tensor(labels).to(torch.int64)
     if native.has_gcn and native.soilnet:
         n_seq = int(inputs["node_off"][-1])                      # the loss is the mean over all sensor-sequences of the batch
         sub, lab = dp.shard_soil_batch(inputs, labels, rank, world_size)
+        return "soilnet", sub, lab, n_seq
+    if native.has_gcn:
+        sub, lab = dp.shard_cml_batch(inputs, labels, rank, world_size)
+        return "cml", sub, lab, inputs["anom"].shape[0]
+    x = torch.as_tensor(inputs)
+    xs, lab = dp.shard_seq_batch(x, labels, rank, world_size)
+    return "seq", {"x": xs}, lab, x.shape[0]
+
+
+def upload_shard(native, sub, lab, non_blocking=True):
+    dev = _device_of(native)
+    sub = {k: (v.to(dev, non_blocking=non_blocking) if isinstance(v, torch.Tensor) else v) for k, v in sub.items()}
+    return sub, lab.to(dev, non_blocking=non_blocking)
+
+
+def step_on_shard(native, kind, sub, lab, global_batch, class_weights, lr):
+    """The optimisation step on a shard that is on the device already; returns the global loss as a 1-element device
+    tensor (reading it is the caller's synchronisation point).  A rank whose shard is empty (the last, partial batch
+    of an epoch can hold fewer windows than there are ranks; Keras' fit trains on it too) skips the device calls and
+    contributes zeros to both all-reduces, so the collectives stay matched on every rank."""
+    dev = _device_of(native)
+    cw = (class_weights[0], class_weights[1]) if class_weights else (1.0, 1.0)
+    if kind == "soilnet":
         empty = sub["n_nodes_total"] == 0
-        sub = {k: (v.to(dev, non_blocking=True) if isinstance(v, torch.Tensor) else v) for k, v in sub.items()}
         moments = torch.zeros(10, dtype=torch.float64, device=dev) if empty else native.train_moments_soilnet(sub["features"])
         dp.all_reduce_sum(moments)
         if empty:
             rvec = torch.zeros(native.train_vector_len(), dtype=torch.float32, device=dev)
         else:
-            rvec = native.train_grads_soilnet(sub["features"], sub["edges"], sub["node_off"].to(torch.int32), sub["edge_off"], lab.to(dev),
-                                              sub["T"], moments, cw, global_batch=n_seq, n_nodes_total=sub["n_nodes_total"])
+            rvec = native.train_grads_soilnet(sub["features"], sub["edges"], sub["node_off"].to(torch.int32), sub["edge_off"], lab,
+                                              sub["T"], moments, cw, global_batch=global_batch, n_nodes_total=sub["n_nodes_total"])
         dp.all_reduce_sum(rvec)
         native.train_apply(rvec, moments, lr)
-    elif native.has_gcn:
-        B = inputs["anom"].shape[0]
-        sub, lab = dp.shard_cml_batch(inputs, labels, rank, world_size)
+    elif kind == "cml":
         empty = sub["anom"].shape[0] == 0
-        sub = {k: (v.to(dev, non_blocking=True) if isinstance(v, torch.Tensor) else v) for k, v in sub.items()}
         moments = torch.zeros(6, dtype=torch.float64, device=dev) if empty else native.train_moments_cml(sub["features"])
         dp.all_reduce_sum(moments)
         if empty:
             rvec = torch.zeros(native.train_vector_len(), dtype=torch.float32, device=dev)
         else:
             rvec = native.train_grads_cml(sub["features"], sub["anom"], sub["edges"], sub["node_off"].to(torch.int32), sub["edge_off"],
-                                          lab.to(dev), moments, cw, global_batch=B, n_nodes_total=sub["n_nodes_total"])
+                                          lab, moments, cw, global_batch=global_batch, n_nodes_total=sub["n_nodes_total"])
         dp.all_reduce_sum(rvec)
         native.train_apply(rvec, moments, lr)
     else:
-        x = torch.as_tensor(inputs)
-        B = x.shape[0]
-        xs, lab = dp.shard_seq_batch(x, labels, rank, world_size)
+        xs = sub["x"]
         if xs.shape[0] == 0:
             rvec = torch.zeros(native.train_vector_len(), dtype=torch.float32, device=dev)
         else:
-            rvec = native.train_grads_seq(xs.to(dev, dtype=torch.float32), lab.to(dev), cw, global_batch=B)
+            rvec = native.train_grads_seq(xs.to(dtype=torch.float32), lab, cw, global_batch=global_batch)
         dp.all_reduce_sum(rvec)
         native.train_apply(rvec, None, lr)
-    return float(rvec[-1].item())
+    return rvec[-1:]
+
+
+def train_step(native, inputs, labels, class_weights, lr):
+    """One optimisation step on one global batch; returns the (global) loss.  Works for one process
+    or for every rank of a torch.distributed group (each rank passes the same global batch and
+    works on its own shard)."""
+    kind, sub, lab, global_batch = shard_for_rank(native, inputs, labels)
+    sub, lab = upload_shard(native, sub, lab)
+    return float(step_on_shard(native, kind, sub, lab, global_batch, class_weights, lr).item())
+
+
+class _Uploads:
+    """The shard of batch i + 1 travels to the device on a copy stream while the step on batch i runs (what
+    dataset.prefetch does for the reference's model.fit).  Host tensors are pinned once so the copies are asynchronous."""
+
+    def __init__(self, native, batches):
+        self.native, self.batches = native, batches
+        self.dev = _device_of(native)
+        self.cuda = self.dev.type == "cuda"
+        self.stream = torch.cuda.Stream(self.dev) if self.cuda else None
+        self.pinned = {}
+
+    def _pin(self, i, sub, lab):
+        if i not in self.pinned:
+            pin = lambda v: v.pin_memory() if isinstance(v, torch.Tensor) and not v.is_cuda and not v.is_pinned() and v.numel() > 0 else v
+            self.pinned[i] = ({k: pin(v) for k, v in sub.items()}, pin(lab))
+        return self.pinned[i]
+
+    def _start(self, i):
+        inputs, labels = self.batches[i]
+        kind, sub, lab, gb = shard_for_rank(self.native, inputs, labels)
+        if not self.cuda:
+            return kind, sub, lab, gb, None
+        sub, lab = self._pin(i, sub, lab)
+        with torch.cuda.stream(self.stream):
+            sub, lab = upload_shard(self.native, sub, lab)
+            ready = torch.cuda.Event()
+            ready.record(self.stream)
+        return kind, sub, lab, gb, ready
+
+    def __iter__(self):
+        nxt = self._start(0) if self.batches else None
+        for i in range(len(self.batches)):
+            kind, sub, lab, gb, ready = nxt
+            nxt = self._start(i + 1) if i + 1 < len(self.batches) else None
+            if ready is not None:
+                cur = torch.cuda.current_stream(self.dev)
+                cur.wait_event(ready)
+                for v in list(sub.values()) + [lab]:       # allocated on the copy stream, used on this one
+                    if isinstance(v, torch.Tensor) and v.is_cuda:
+                        v.record_stream(cur)
+            yield kind, sub, lab, gb
 
 
 def train_model(model, model_config, preproc_config, train_dataset_batched, val_dataset_batched=None, baseline=False,
@@ -132,10 +196,11 @@ def train_model(model, model_config, preproc_config, train_dataset_batched, val_
     lr = float(model_config.learning_rate)
     best, best_params, since_best = np.inf, None, 0
     mcc = MCC_custom(train_batches, val_batches) if model_config.get("mcc_callback", False) else None
+    uploads = _Uploads(model.native, train_batches)
     for epoch in range(int(model_config.epochs)):
         lr = learning_rate_for_epoch(model_config, epoch, lr)
-        losses = [train_step(model.native, inputs, lab, classes_weights, lr) for inputs, lab in train_batches]
-        logs = {"loss": float(np.mean(losses)), "lr": lr}
+        losses = [step_on_shard(model.native, kind, sub, lab, gb, classes_weights, lr) for kind, sub, lab, gb in uploads]
+        logs = {"loss": float(torch.cat(losses).mean().item()) if losses else float("nan"), "lr": lr}   # one read per epoch
         if val_batches:
             p = model.predict(val_batches)
             y = np.concatenate([np.asarray(torch.as_tensor(b[1]).cpu()).reshape(-1) for b in val_batches])
