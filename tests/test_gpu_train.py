@@ -144,23 +144,26 @@ def test_loss_goes_down_on_a_fixed_batch():
         m.close()
 
 
-def test_large_batch_gradients_equal_the_sum_of_their_parts():
-    """19,200 windows = 300 tiles: the backward pass runs on the tensor-core kernels (with dz for the weight
-    gradients), 6,400-window calls on the fp32 ones.  With the same global batch size and BN moments the
-    reduction vectors are additive, so the two must agree to rounding."""
+@pytest.mark.parametrize("B,part", [(19200, 6400), (40960, 8192)])
+def test_large_batch_gradients_equal_the_sum_of_their_parts(B, part):
+    """With the same global batch size and BN moments the reduction vectors are additive, so one call and the sum of
+    smaller calls must agree to rounding.  19,200 windows (150 tile pairs) and its 6,400-window parts all run the
+    two-threads-per-window shape of the narrow LSTM kernels; 40,960 windows (320 pairs, more than one wave of that
+    shape) run the four-group shape while their 8,192-window parts do not, and the weight-gradient kernel goes from 8
+    to 45 items per slice."""
     from test_gpu_scoring import _slice_cml
     m = NativeModel.load(os.path.join(MODELS, "model_cml"), device=0)
     try:
-        B, T = 19200, 181
+        T = 181
         batch = synth.make_cml_batch(B, seed=8, n_nodes=4, device="cuda")
         labels = make_labels(B, 8).cuda()
         mom = m.train_moments_cml(batch["features"])
         full = m.train_grads_cml(batch["features"], batch["anom"], batch["edges"], batch["node_off"], batch["edge_off"], labels, mom,
                                  global_batch=B).double()
         parts = torch.zeros_like(full)
-        for w0 in range(0, B, 6400):
-            s = _slice_cml(batch, w0, w0 + 6400, T)
-            parts += m.train_grads_cml(s["features"], s["anom"], s["edges"], s["node_off"], s["edge_off"], labels[w0:w0 + 6400], mom,
+        for w0 in range(0, B, part):
+            s = _slice_cml(batch, w0, w0 + part, T)
+            parts += m.train_grads_cml(s["features"], s["anom"], s["edges"], s["node_off"], s["edge_off"], labels[w0:w0 + part], mom,
                                        global_batch=B).double()
         for name, off, shape, _ in m.segments():
             n = int(np.prod(shape))
