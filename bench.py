@@ -287,6 +287,30 @@ def run_reference(args, rank):
 
 
 # ---- NUMA placement of the host staging buffers ----------------------------------------------------------------
+def numa_node_from_nvml(local_rank, info):
+    """The NUMA node that holds most of the CPUs NVML names as close to this GPU (None if it cannot be told)."""
+    import glob
+    import pynvml
+    pynvml.nvmlInit()
+    h = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+    words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+    cpus = {64 * w + b for w, word in enumerate(words) for b in range(64) if (int(word) >> b) & 1}
+    info["nvml_cpus"] = len(cpus)
+    best, best_n = None, 0
+    nodes = glob.glob("/sys/devices/system/node/node[0-9]*")
+    info["numa_nodes_visible"] = len(nodes)
+    for path in nodes:
+        members = set()
+        for part in open(os.path.join(path, "cpulist")).read().strip().split(","):
+            if part:
+                lo, _, hi = part.partition("-")
+                members.update(range(int(lo), int(hi or lo) + 1))
+        n = len(members & cpus)
+        if n > best_n:
+            best, best_n = int(os.path.basename(path)[4:]), n
+    return best if len(nodes) > 1 else None
+
+
 def bind_near_gpu(torch, local_rank):
     """Pinned staging buffers should live on the NUMA node the GPU hangs off.  Returns what was found / done."""
     info = {"numa_node": None, "cpus_allowed": len(os.sched_getaffinity(0))}
@@ -295,8 +319,11 @@ def bind_near_gpu(torch, local_rank):
         bus = "%04x:%02x:%02x.0" % (getattr(props, "pci_domain_id", 0), props.pci_bus_id, props.pci_device_id)
         node = int(open("/sys/bus/pci/devices/%s/numa_node" % bus).read().strip())
         info["numa_node"] = node
-        if node < 0:
-            return info
+        if node < 0:   # containers often hide the PCI device's node: ask NVML for the GPU's CPU set and look up the node of those CPUs
+            node = numa_node_from_nvml(local_rank, info)
+            if node is None or node < 0:
+                return info
+            info["numa_node"] = node
         # prefer this node for the pages of the pinned buffers allocated from here on (MPOL_PREFERRED = 1); the CPU
         # affinity is left alone (the CPU baseline and the parity oracle use every core)
         mask = ctypes.c_ulong(1 << node)
