@@ -16,8 +16,11 @@
 // so the cell arithmetic of chunk c+1 overlaps the MMAs of chunk c.  D is double-buffered across
 // steps: while step t accumulates into D[t&1], the threads read dh_rec (their own lane, 8 columns per
 // chunk) and flush dx_{t+1} from D[(t+1)&1].  For H = 128 the 384 KB of weights are streamed from
-// L2 through a ring by a producer thread (TMA), and the units are split over two thread groups that
-// share the lanes (a thread then carries dc for 64 units).
+// L2 through a ring by a producer thread (TMA).
+// SPLIT = 2 deals the chunks of a window over two threads (two warps share each 32 lanes, a thread carries dc for half
+// the units): the step's serial chain gets shorter (~4 us instead of ~6 us for a 16-unit layer) at half the windows in
+// flight per SM.  lstm_tc_bwd.cu picks the shape per launch: always split for H >= 64, split for H <= 32 when all tile
+// pairs fit in one wave of it.
 #pragma once
 #include <cuda_bf16.h>
 
