@@ -158,3 +158,19 @@ def test_a_batch_smaller_than_the_world_does_not_hang():
         np.testing.assert_allclose(m[[0, 5]], [batch["features"].sum().item(), batch["features"].shape[0]], rtol=1e-6)
         np.testing.assert_allclose(b, [batch["anom"].sum().item(), 1, 1, 1.0], rtol=1e-6)
         assert loss_g == loss_b == 1.0
+
+
+def test_epoch_iterator_yields_every_batch_once_and_matches_train_step():
+    """libs/fit_model._Uploads (shard -> upload one batch ahead -> step) on the CPU stand-in: every batch comes out once,
+    in order, and step_on_shard on what it yields applies what train_step applies."""
+    batches = [(synth.make_cml_batch(n, seed=10 + n), torch.arange(n) % 2) for n in (3, 1, 2)]
+    a, b = _FakeNative(True), _FakeNative(True)
+    seen = []
+    for (inputs, labels), (kind, sub, lab, gb) in zip(batches, fit_model._Uploads(a, batches)):
+        assert kind == "cml" and gb == inputs["anom"].shape[0] and torch.equal(lab, labels.to(torch.int64))
+        loss = fit_model.step_on_shard(a, kind, sub, lab, gb, {0: 1, 1: 5}, 1e-4)
+        ref = fit_model.train_step(b, inputs, labels, {0: 1, 1: 5}, 1e-4)
+        assert float(loss.item()) == ref and torch.equal(a.applied[0], b.applied[0]) and torch.equal(a.applied[1], b.applied[1])
+        seen.append(gb)
+    assert seen == [3, 1, 2]
+    assert list(fit_model._Uploads(a, [])) == []
